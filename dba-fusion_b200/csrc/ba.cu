@@ -1,0 +1,827 @@
+// Dense bundle adjustment for sm_100a: graph bookkeeping, per-depth-frame linearisation
+// (Jacobians, pose Hessian blocks, depth blocks), Schur complement, float64 Cholesky,
+// depth back-substitution and SE3 / disparity retraction.  Everything stays on the device;
+// the host only enqueues kernels.
+//
+// Replaces ba_cuda / ba_cuda_extend / BACore of the reference (src/droid_kernels.cu:1394-1956).
+// Data layout in HBM (one caller-owned workspace, see dbaf_ba_layout):
+//   H  float64 [6P,6P] + v float64 [6P]   reduced camera system, accumulated with atomics
+//   Eij float32 [E,6,HW], Ei float32 [P,6,HW]   pose-depth blocks, pixel index fastest
+//   Q, w float32 [K,HW]                    inverse depth Hessian and depth gradient per depth frame
+//   kx, kk_exp, csr_*, srow_*  int32       graph tables
+#include "common.cuh"
+
+#include <algorithm>
+
+namespace dbaf {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kSmemSolveMaxN = 160;   // 160*161*8 B = 206 KB of shared memory
+
+inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
+
+struct Ws {
+  int* info;
+  double* H;
+  double* v;
+  float* dx;
+  int* kx;
+  int* kk_exp;
+  int* csr_ptr;
+  int* csr_idx;
+  int* srow_ptr;
+  int* srow_idx;
+  int* frame2k;
+  int* cursor;
+  float* Q;
+  float* w;
+  float* Ei;
+  float* Eij;
+  double* Lfac;
+  int Kcap;
+};
+
+void fill_layout(int N, int E, int t0, int t1, int ht, int wd, dbaf_ba_layout* L) {
+  const int64_t P = t1 - t0, HW = (int64_t)ht * wd, n = 6 * P;
+  const int64_t Kcap = std::min<int64_t>(N, P + E);
+  int64_t off = 0;
+  auto take = [&](int64_t bytes) { int64_t o = off; off = align_up(off + bytes, 256); return o; };
+  L->info = take(16 * 4);
+  L->H = take((n * n + n) * 8);
+  L->v = L->H + n * n * 8;
+  L->dx = take(std::max<int64_t>(1, n) * 4);
+  L->Lfac = take(n > kSmemSolveMaxN ? ((n + 1) * n + n) * 8 : 8);
+  L->kx = take(Kcap * 4);
+  L->kk_exp = take((P + E) * 4);
+  L->csr_ptr = take((Kcap + 1) * 4);
+  L->csr_idx = take(std::max<int64_t>(1, E) * 4);
+  L->srow_ptr = take((Kcap + 1) * 4);
+  L->srow_idx = take((P + E) * 4);
+  L->frame2k = take((int64_t)N * 4);
+  L->cursor = take((Kcap + 1) * 4);
+  L->Q = take(Kcap * HW * 4);
+  L->w = take(Kcap * HW * 4);
+  L->Ei = take(P * 6 * HW * 4);
+  L->Eij = take((int64_t)E * 6 * HW * 4);
+  L->Kcap = Kcap;
+  L->total_bytes = off;
+}
+
+Ws view(void* base, const dbaf_ba_layout& L) {
+  char* b = static_cast<char*>(base);
+  Ws w;
+  w.info = (int*)(b + L.info);
+  w.H = (double*)(b + L.H);
+  w.v = (double*)(b + L.v);
+  w.dx = (float*)(b + L.dx);
+  w.kx = (int*)(b + L.kx);
+  w.kk_exp = (int*)(b + L.kk_exp);
+  w.csr_ptr = (int*)(b + L.csr_ptr);
+  w.csr_idx = (int*)(b + L.csr_idx);
+  w.srow_ptr = (int*)(b + L.srow_ptr);
+  w.srow_idx = (int*)(b + L.srow_idx);
+  w.frame2k = (int*)(b + L.frame2k);
+  w.cursor = (int*)(b + L.cursor);
+  w.Q = (float*)(b + L.Q);
+  w.w = (float*)(b + L.w);
+  w.Ei = (float*)(b + L.Ei);
+  w.Eij = (float*)(b + L.Eij);
+  w.Lfac = (double*)(b + L.Lfac);
+  w.Kcap = (int)L.Kcap;
+  return w;
+}
+
+// ------------------------------------------------------------------ tables ----
+
+// In-place exclusive scan of data[0..n) by one 1024-thread block; returns the total.
+__device__ int block_exclusive_scan(int* data, int n) {
+  __shared__ int warp_tot[32];
+  __shared__ int carry;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (tid == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + tid;
+    const int x = i < n ? data[i] : 0;
+    int incl = x;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += y;
+    }
+    if (lane == 31) warp_tot[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+      const int t = warp_tot[lane];
+      int s = t;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, s, o);
+        if (lane >= o) s += y;
+      }
+      warp_tot[lane] = s - t;
+    }
+    __syncthreads();
+    const int excl = incl - x + warp_tot[wid] + carry;
+    if (i < n) data[i] = excl;
+    __syncthreads();
+    if (tid == 1023) carry = excl + x;
+    __syncthreads();
+  }
+  return carry;
+}
+
+// One block builds every table of the window: kx / kk_exp (sorted unique of
+// cat(arange(t0,t1), ii) and its inverse), edges grouped by source frame in ascending edge
+// order, and per depth frame the rows of E that enter the Schur complement.
+__global__ void __launch_bounds__(1024) k_tables(const int64_t* __restrict__ ii,
+                                                 const int64_t* __restrict__ jj, int E, int N,
+                                                 int t0, int t1, Ws ws) {
+  const int tid = threadIdx.x;
+  const int P = t1 - t0;
+  int* f2k = ws.frame2k;
+  if (tid < 16) ws.info[tid] = 0;
+  for (int f = tid; f < N; f += 1024) f2k[f] = (f >= t0 && f < t1) ? 1 : 0;
+  __syncthreads();
+  for (int e = tid; e < E; e += 1024) {
+    const long long i = ii[e], j = jj[e];
+    if (i < 0 || i >= N || j < 0 || j >= N) ws.info[2] = 1;
+    else f2k[i] = 1;
+  }
+  __syncthreads();
+  // flags -> exclusive ranks in place (absent frames become -1); kx lists the present frames
+  __shared__ int K_s;
+  {
+    __shared__ int warp_tot[32];
+    __shared__ int carry;
+    const int lane = tid & 31, wid = tid >> 5;
+    if (tid == 0) carry = 0;
+    __syncthreads();
+    for (int base = 0; base < N; base += 1024) {
+      const int f = base + tid;
+      const int x = f < N ? f2k[f] : 0;
+      int incl = x;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int y = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += y;
+      }
+      if (lane == 31) warp_tot[wid] = incl;
+      __syncthreads();
+      if (wid == 0) {
+        const int t = warp_tot[lane];
+        int s = t;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int y = __shfl_up_sync(0xffffffffu, s, o);
+          if (lane >= o) s += y;
+        }
+        warp_tot[lane] = s - t;
+      }
+      __syncthreads();
+      const int excl = incl - x + warp_tot[wid] + carry;
+      if (f < N) {
+        f2k[f] = x ? excl : -1;
+        if (x && excl < ws.Kcap) ws.kx[excl] = f;
+      }
+      __syncthreads();
+      if (tid == 1023) carry = excl + x;
+      __syncthreads();
+    }
+    if (tid == 0) K_s = carry;
+    __syncthreads();
+  }
+  const int K = K_s;
+  // out-degree per depth frame
+  for (int k = tid; k <= K; k += 1024) ws.csr_ptr[k] = 0;
+  __syncthreads();
+  for (int e = tid; e < E; e += 1024) {
+    const long long i = ii[e], j = jj[e];
+    if (i >= 0 && i < N && j >= 0 && j < N) atomicAdd(&ws.csr_ptr[f2k[i]], 1);
+  }
+  __syncthreads();
+  const int n_valid = block_exclusive_scan(ws.csr_ptr, K);
+  if (tid == 0) ws.csr_ptr[K] = n_valid;
+  for (int k = tid; k < K; k += 1024) ws.cursor[k] = 0;
+  __syncthreads();
+  for (int e = tid; e < E; e += 1024) {
+    const long long i = ii[e], j = jj[e];
+    if (i >= 0 && i < N && j >= 0 && j < N) {
+      const int k = f2k[i];
+      const int pos = atomicAdd(&ws.cursor[k], 1);
+      ws.csr_idx[ws.csr_ptr[k] + pos] = e;
+    }
+  }
+  __syncthreads();
+  // ascending edge order inside each segment (insertion sort; segments are short)
+  for (int k = tid; k < K; k += 1024) {
+    const int lo = ws.csr_ptr[k], hi = ws.csr_ptr[k + 1];
+    for (int a = lo + 1; a < hi; ++a) {
+      const int x = ws.csr_idx[a];
+      int b = a - 1;
+      while (b >= lo && ws.csr_idx[b] > x) { ws.csr_idx[b + 1] = ws.csr_idx[b]; --b; }
+      ws.csr_idx[b + 1] = x;
+    }
+  }
+  // inverse map of the unique
+  for (int n = tid; n < P + E; n += 1024) {
+    int k = -1;
+    if (n < P) k = f2k[t0 + n];
+    else {
+      const long long i = ii[n - P];
+      if (i >= 0 && i < N) k = f2k[i];
+    }
+    ws.kk_exp[n] = k;
+  }
+  __syncthreads();
+  // rows of E per depth frame whose pose lies inside the window: the self row (row index
+  // frame-t0) and one row per out-edge (row index P+e) with t0 <= jj[e] < t1.
+  for (int k = tid; k <= K; k += 1024) ws.srow_ptr[k] = 0;
+  __syncthreads();
+  for (int k = tid; k < K; k += 1024) {
+    const int f = ws.kx[k];
+    int c = (f >= t0 && f < t1) ? 1 : 0;
+    for (int a = ws.csr_ptr[k]; a < ws.csr_ptr[k + 1]; ++a) {
+      const long long j = jj[ws.csr_idx[a]];
+      c += (j >= t0 && j < t1) ? 1 : 0;
+    }
+    ws.srow_ptr[k] = c;
+  }
+  __syncthreads();
+  const int n_rows = block_exclusive_scan(ws.srow_ptr, K);
+  if (tid == 0) { ws.srow_ptr[K] = n_rows; ws.info[4] = n_rows; ws.info[0] = K; }
+  __syncthreads();
+  for (int k = tid; k < K; k += 1024) {
+    const int f = ws.kx[k];
+    int o = ws.srow_ptr[k];
+    if (f >= t0 && f < t1) ws.srow_idx[o++] = f - t0;
+    for (int a = ws.csr_ptr[k]; a < ws.csr_ptr[k + 1]; ++a) {
+      const int e = ws.csr_idx[a];
+      const long long j = jj[e];
+      if (j >= t0 && j < t1) ws.srow_idx[o++] = P + e;
+    }
+  }
+}
+
+// -------------------------------------------------------------- linearise ----
+
+// value index l in [0,78) <-> lower triangle (n,m), m<=n, of the 12x12 edge Hessian,
+// enumerated row by row; [78,84) = gradient wrt pose i, [84,90) = gradient wrt pose j.
+__device__ __forceinline__ void tri_unpack(int l, int& n, int& m) {
+  n = (int)((sqrtf(8.0f * l + 1.0f) - 1.0f) * 0.5f);
+  while ((n + 1) * (n + 2) / 2 <= l) ++n;
+  while (n * (n + 1) / 2 > l) --n;
+  m = l - n * (n + 1) / 2;
+}
+
+// One CTA = one depth frame k x one pixel tile.  It walks the frame's out-edges, so the
+// source disparity is read once, C/w/Ei accumulate in registers across edges (the reference
+// writes per-edge Cii/bz/Eii and re-reads them in accum_cuda), and each edge's 90 pose
+// terms are reduced with a transposed warp shuffle + one shared-memory stage.
+template <int PXT, bool MOTION_ONLY>
+__global__ void __launch_bounds__(kThreads)
+k_linearize(const float* __restrict__ poses, const float* __restrict__ disps,
+            const float* __restrict__ intr, const float* __restrict__ sens,
+            const float* __restrict__ targets, const float* __restrict__ weights,
+            const float* __restrict__ eta, int eta_rows, const int64_t* __restrict__ jj,
+            int t0, int P, int HW, int wd, float alpha, int k_lo, int k_hi, Ws ws) {
+  const int k = k_lo + blockIdx.y;
+  const int K = ws.info[0];
+  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int ix = ws.kx[k];
+  const float fx = __ldg(intr), fy = __ldg(intr + 1), cx = __ldg(intr + 2), cy = __ldg(intr + 3);
+  const int n6 = 6 * P;
+
+  __shared__ float red[2][kWarps][96];
+
+  int px[PXT];
+  bool ok[PXT];
+  float X0[PXT], X1[PXT], d0[PXT];
+  float accC[PXT], accW[PXT], accE[PXT][6];
+#pragma unroll
+  for (int s = 0; s < PXT; ++s) {
+    px[s] = (blockIdx.x * PXT + s) * kThreads + tid;
+    ok[s] = px[s] < HW;
+    const int p = ok[s] ? px[s] : 0;
+    const int i = p / wd, j = p - i * wd;
+    X0[s] = ((float)j - cx) / fx;
+    X1[s] = ((float)i - cy) / fy;
+    d0[s] = ok[s] ? __ldg(disps + (size_t)ix * HW + p) : 0.f;
+    accC[s] = 0.f; accW[s] = 0.f;
+#pragma unroll
+    for (int c = 0; c < 6; ++c) accE[s][c] = 0.f;
+  }
+
+  const int e_lo = ws.csr_ptr[k], e_hi = ws.csr_ptr[k + 1];
+  int buf = 0;
+  for (int a = e_lo; a < e_hi; ++a, buf ^= 1) {
+    const int e = ws.csr_idx[a];
+    const int jx = (int)jj[e];
+    const bool stereo = ix == jx;
+    const Se3 G = stereo ? stereo_baseline() : load_relative(poses, ix, jx);
+
+    float h[96];
+#pragma unroll
+    for (int l = 0; l < 96; ++l) h[l] = 0.f;
+
+#pragma unroll
+    for (int s = 0; s < PXT; ++s) {
+      if (!ok[s]) continue;
+      const int p = px[s];
+      const float Xi[4] = {X0[s], X1[s], 1.0f, d0[s]};
+      float Xj[4];
+      act(G, Xi, Xj);
+      const float x = Xj[0], y = Xj[1], hh = Xj[3];
+      const bool near = Xj[2] < kMinDepth;
+      const float d = near ? 0.0f : 1.0f / Xj[2];
+      const float d2 = d * d;
+      const size_t tw = ((size_t)e * 2) * HW + p;
+      float wu = near ? 0.0f : (float)(0.001 * (double)__ldg(weights + tw));
+      float wv = near ? 0.0f : (float)(0.001 * (double)__ldg(weights + tw + HW));
+      const float ru = __ldg(targets + tw) - (fx * d * x + cx);
+      const float rv = __ldg(targets + tw + HW) - (fy * d * y + cy);
+
+      float J[12];           // [0,6) wrt pose i, [6,12) wrt pose j
+      float* Jj = J + 6;
+      // ---- u row
+      Jj[0] = fx * (hh * d);
+      Jj[1] = fx * 0.f;
+      Jj[2] = fx * (-x * hh * d2);
+      Jj[3] = fx * (-x * y * d2);
+      Jj[4] = fx * (1.0f + x * x * d2);
+      Jj[5] = fx * (-y * d);
+      float Jz = fx * (G.t[0] * d - G.t[2] * (x * d2));
+      float Cp = wu * Jz * Jz;
+      float Wp = wu * ru * Jz;
+      if (stereo) wu = 0.f;
+      adjoint_T(G, Jj, J);
+#pragma unroll
+      for (int n = 0; n < 6; ++n) J[n] = -J[n];
+      {
+        int l = 0;
+#pragma unroll
+        for (int n = 0; n < 12; ++n)
+#pragma unroll
+          for (int m = 0; m <= n; ++m) { h[l] += wu * J[n] * J[m]; ++l; }
+        const float wr = wu * ru;
+#pragma unroll
+        for (int n = 0; n < 12; ++n) h[78 + n] += wr * J[n];
+      }
+      float Ej[6];
+      if (!MOTION_ONLY) {
+        const float wz = wu * Jz;
+#pragma unroll
+        for (int n = 0; n < 6; ++n) { accE[s][n] += wz * J[n]; Ej[n] = wz * Jj[n]; }
+      }
+      // ---- v row
+      Jj[0] = fy * 0.f;
+      Jj[1] = fy * (hh * d);
+      Jj[2] = fy * (-y * hh * d2);
+      Jj[3] = fy * (-1.0f - y * y * d2);
+      Jj[4] = fy * (x * y * d2);
+      Jj[5] = fy * (x * d);
+      Jz = fy * (G.t[1] * d - G.t[2] * (y * d2));
+      Cp += wv * Jz * Jz;
+      Wp += wv * rv * Jz;
+      if (stereo) wv = 0.f;
+      adjoint_T(G, Jj, J);
+#pragma unroll
+      for (int n = 0; n < 6; ++n) J[n] = -J[n];
+      {
+        int l = 0;
+#pragma unroll
+        for (int n = 0; n < 12; ++n)
+#pragma unroll
+          for (int m = 0; m <= n; ++m) { h[l] += wv * J[n] * J[m]; ++l; }
+        const float wr = wv * rv;
+#pragma unroll
+        for (int n = 0; n < 12; ++n) h[78 + n] += wr * J[n];
+      }
+      if (!MOTION_ONLY) {
+        const float wz = wv * Jz;
+        float* Eo = ws.Eij + (size_t)e * 6 * HW + p;
+#pragma unroll
+        for (int n = 0; n < 6; ++n) {
+          accE[s][n] += wz * J[n];
+          Eo[(size_t)n * HW] = Ej[n] + wz * Jj[n];
+        }
+        accC[s] += Cp;
+        accW[s] += Wp;
+      }
+    }
+
+    // block reduction of the 90 pose terms of this edge, then float64 atomics into H, v
+    warp_reduce32(h, lane);
+    warp_reduce32(h + 32, lane);
+    warp_reduce32(h + 64, lane);
+    red[buf][wid][lane] = h[0];
+    red[buf][wid][32 + lane] = h[32];
+    red[buf][wid][64 + lane] = h[64];
+    __syncthreads();
+    if (tid < 90) {
+      float sum = 0.f;
+#pragma unroll
+      for (int w = 0; w < kWarps; ++w) sum += red[buf][w][tid];
+      const int pi = ix - t0, pj = jx - t0;
+      if (tid < 78) {
+        int n, m;
+        tri_unpack(tid, n, m);
+        const int rn = n < 6 ? pi : pj, cn = m < 6 ? pi : pj;
+        if (rn >= 0 && cn >= 0 && rn < P && cn < P) {
+          const int row = 6 * rn + (n % 6), col = 6 * cn + (m % 6);
+          atomicAdd(ws.H + (size_t)row * n6 + col, (double)sum);
+          if (n != m) atomicAdd(ws.H + (size_t)col * n6 + row, (double)sum);
+        }
+      } else {
+        const int n = tid - 78;
+        const int rn = n < 6 ? pi : pj;
+        if (rn >= 0 && rn < P) atomicAdd(ws.v + 6 * rn + (n % 6), (double)sum);
+      }
+    }
+  }
+
+  if (!MOTION_ONLY) {
+    const int er = eta_rows == 1 ? 0 : min(k, eta_rows - 1);
+    const int self = ix - t0;
+#pragma unroll
+    for (int s = 0; s < PXT; ++s) {
+      if (!ok[s]) continue;
+      const int p = px[s];
+      const float sd = __ldg(sens + (size_t)ix * HW + p);
+      const float m = sd > 0.f ? 1.0f : 0.0f;
+      const float C = accC[s] + m * alpha + (1.0f - m) * __ldg(eta + (size_t)er * HW + p);
+      const float wk = accW[s] - m * alpha * (d0[s] - sd);
+      ws.Q[(size_t)k * HW + p] = 1.0f / C;
+      ws.w[(size_t)k * HW + p] = wk;
+      if (self >= 0 && self < P) {
+#pragma unroll
+        for (int n = 0; n < 6; ++n) ws.Ei[((size_t)self * 6 + n) * HW + p] = accE[s][n];
+      }
+    }
+    if (eta_rows != 1 && eta_rows != K && blockIdx.x == 0 && tid == 0) ws.info[3] = 1;
+  }
+}
+
+// ------------------------------------------------------------------ Schur ----
+
+// One CTA = depth frame k x pixel tile; each warp owns row pairs (a>=b) of the frame's slab
+// and accumulates the 6x6 block  sum_px E_a Q E_b^T  (plus E_a Q w on the diagonal pairs),
+// then subtracts it from H (both triangles) / v.
+__global__ void __launch_bounds__(kThreads)
+k_schur(const int64_t* __restrict__ jj, int t0, int P, int HW, int tile_px, int k_lo, int k_hi, Ws ws) {
+  const int k = k_lo + blockIdx.y;
+  const int K = ws.info[0];
+  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const int r_lo = ws.srow_ptr[k];
+  const int m = ws.srow_ptr[k + 1] - r_lo;
+  const int pairs = m * (m + 1) / 2;
+  const int p_lo = blockIdx.x * tile_px, p_hi = min(HW, p_lo + tile_px);
+  const int n6 = 6 * P;
+  const float* Qk = ws.Q + (size_t)k * HW;
+  const float* wk = ws.w + (size_t)k * HW;
+
+  for (int q = wid; q < pairs; q += kWarps) {
+    int a, b;
+    tri_unpack(q, a, b);
+    const int na = ws.srow_idx[r_lo + a], nb = ws.srow_idx[r_lo + b];
+    const float* Ea = na < P ? ws.Ei + (size_t)na * 6 * HW : ws.Eij + (size_t)(na - P) * 6 * HW;
+    const float* Eb = nb < P ? ws.Ei + (size_t)nb * 6 * HW : ws.Eij + (size_t)(nb - P) * 6 * HW;
+    const int pa = na < P ? na : (int)jj[na - P] - t0;
+    const int pb = nb < P ? nb : (int)jj[nb - P] - t0;
+    const bool diag = a == b;
+
+    float acc[64];
+#pragma unroll
+    for (int l = 0; l < 64; ++l) acc[l] = 0.f;
+    for (int p = p_lo + lane; p < p_hi; p += 32) {
+      const float qv = __ldg(Qk + p);
+      float ea[6], eb[6];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        ea[c] = Ea[(size_t)c * HW + p] * qv;
+        eb[c] = Eb[(size_t)c * HW + p];
+      }
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c) acc[r * 6 + c] += ea[r] * eb[c];
+      if (diag) {
+        const float wv = __ldg(wk + p);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) acc[36 + r] += ea[r] * wv;
+      }
+    }
+    warp_reduce32(acc, lane);
+    warp_reduce32(acc + 32, lane);
+    // lane l now holds value l in acc[0] and value 32+l in acc[32]
+    {
+      const int l = lane;
+      const int r = l / 6, c = l % 6;
+      const double val = -(double)acc[0];
+      atomicAdd(ws.H + (size_t)(6 * pa + r) * n6 + 6 * pb + c, val);
+      if (!diag) atomicAdd(ws.H + (size_t)(6 * pb + c) * n6 + 6 * pa + r, val);
+    }
+    if (lane < 4) {
+      const int l = 32 + lane;
+      const int r = l / 6, c = l % 6;
+      const double val = -(double)acc[32];
+      atomicAdd(ws.H + (size_t)(6 * pa + r) * n6 + 6 * pb + c, val);
+      if (!diag) atomicAdd(ws.H + (size_t)(6 * pb + c) * n6 + 6 * pa + r, val);
+    } else if (diag && lane < 10) {
+      atomicAdd(ws.v + 6 * pa + (lane - 4), -(double)acc[32]);
+    }
+  }
+}
+
+// ------------------------------------------------------------------ solve ----
+
+// In-place Cholesky of the n x n matrix L (leading dimension ld) with the right-hand side
+// carried as row n (so y = L^-1 b falls out of the factorisation), then back-substitution.
+// One CTA.  Returns false when a pivot is <= 0.
+__device__ bool cholesky_solve(double* L, int ld, int n, double* x) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  __shared__ int fail;
+  if (tid == 0) fail = 0;
+  __syncthreads();
+  for (int j = 0; j < n; ++j) {
+    const double piv = L[(size_t)j * ld + j];
+    if (piv <= 0.0) {
+      if (tid == 0) fail = 1;
+      break;   // uniform: every thread reads the same pivot
+    }
+    const double inv = 1.0 / sqrt(piv);
+    __syncthreads();
+    // scale column j (rows j..n, row n is the rhs)
+    for (int i = j + 1 + tid; i <= n; i += nt) L[(size_t)i * ld + j] *= inv;
+    if (tid == 0) L[(size_t)j * ld + j] = piv * inv;
+    __syncthreads();
+    // trailing update of rows j+1..n (lower triangle) : L[i][c] -= L[i][j]*L[c][j]
+    const int rem = n - j;           // rows j+1..n  -> rem rows, row n included
+    const int total = rem * (rem + 1) / 2;
+    for (int t = tid; t < total; t += nt) {
+      int a, b;
+      tri_unpack(t, a, b);           // a>=b in [0,rem)
+      const int i = j + 1 + a, c = j + 1 + b;
+      if (c < n) L[(size_t)i * ld + c] -= L[(size_t)i * ld + j] * L[(size_t)c * ld + j];
+    }
+    __syncthreads();
+  }
+  __syncthreads();
+  if (fail) return false;
+  // row n now holds y (forward substitution done column by column above); solve L^T x = y
+  for (int i = tid; i < n; i += nt) x[i] = L[(size_t)n * ld + i];
+  __syncthreads();
+  for (int j = n - 1; j >= 0; --j) {
+    if (tid == 0) x[j] /= L[(size_t)j * ld + j];
+    __syncthreads();
+    const double xj = x[j];
+    for (int i = tid; i < j; i += nt) x[i] -= L[(size_t)j * ld + i] * xj;
+    __syncthreads();
+  }
+  return true;
+}
+
+// L = H (+ prior), damped; Cholesky in shared memory when it fits, else in the workspace.
+__global__ void __launch_bounds__(kThreads)
+k_solve(int n, float lm, float ep, const double* __restrict__ prior, int prior_rows, int prior_cols,
+        int use_smem, Ws ws) {
+  extern __shared__ double sm[];
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int ld = n;
+  double* L = use_smem ? sm : ws.Lfac;                 // (n+1) x n, row n = rhs
+  double* x = use_smem ? sm + (size_t)(n + 1) * n : ws.Lfac + (size_t)(n + 1) * n;
+  for (int t = tid; t < n * n; t += nt) {
+    const int i = t / n, c = t - i * n;
+    if (c > i) continue;                               // lower triangle only
+    double a = ws.H[t];
+    if (prior) {
+      // ba_cuda_extend: L = Ad + Adprior, Adprior = Ad overwritten by the prior on its block
+      a += (i < prior_rows && c < prior_cols) ? prior[(size_t)i * prior_cols + c] : ws.H[t];
+    }
+    if (i == c) a += (double)ep + (double)lm * a;
+    L[(size_t)i * ld + c] = a;
+  }
+  for (int i = tid; i < n; i += nt) L[(size_t)n * ld + i] = ws.v[i];
+  __syncthreads();
+  const bool ok = cholesky_solve(L, ld, n, x);
+  __syncthreads();
+  for (int i = tid; i < n; i += nt) ws.dx[i] = ok ? (float)x[i] : 0.0f;
+  if (!ok && tid == 0) atomicAdd(&ws.info[1], 1);
+}
+
+// ---------------------------------------------------------------- retract ----
+
+__global__ void k_pose_retract(float* __restrict__ poses, const float* __restrict__ dx, int t0, int P,
+                               float* __restrict__ dx_out) {
+  for (int k = threadIdx.x; k < P; k += blockDim.x) {
+    float xi[6], T[7];
+#pragma unroll
+    for (int n = 0; n < 6; ++n) xi[n] = dx[6 * k + n];
+    if (poses) {
+#pragma unroll
+      for (int n = 0; n < 7; ++n) T[n] = poses[7 * (t0 + k) + n];
+      retract_pose(xi, T);
+#pragma unroll
+      for (int n = 0; n < 7; ++n) poses[7 * (t0 + k) + n] = T[n];
+    }
+    if (dx_out) {
+#pragma unroll
+      for (int n = 0; n < 6; ++n) dx_out[6 * k + n] = xi[n];
+    }
+  }
+}
+
+// dz = Q * (w - sum_rows E_row^T dx[pose(row)]) over the rows of depth frame k whose pose index
+// is strictly inside (0, P) -- the reference skips index 0 (src/droid_kernels.cu:1150).
+__global__ void __launch_bounds__(kThreads)
+k_backsub(const int64_t* __restrict__ jj, const float* __restrict__ dx, float* __restrict__ disps,
+          float* __restrict__ dz_out, int t0, int P, int HW, int k_lo, int k_hi, Ws ws) {
+  const int k = k_lo + blockIdx.y;
+  const int K = ws.info[0];
+  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= HW) return;
+  const int f = ws.kx[k];
+  float acc = 0.f;
+  const int self = f - t0;
+  if (self > 0 && self < P) {
+    const float* E = ws.Ei + (size_t)self * 6 * HW + p;
+    float s = 0.f;
+#pragma unroll
+    for (int n = 0; n < 6; ++n) s += E[(size_t)n * HW] * __ldg(dx + 6 * self + n);
+    acc += s;
+  }
+  for (int a = ws.csr_ptr[k]; a < ws.csr_ptr[k + 1]; ++a) {
+    const int e = ws.csr_idx[a];
+    const int pj = (int)jj[e] - t0;
+    if (pj > 0 && pj < P) {
+      const float* E = ws.Eij + (size_t)e * 6 * HW + p;
+      float s = 0.f;
+#pragma unroll
+      for (int n = 0; n < 6; ++n) s += E[(size_t)n * HW] * __ldg(dx + 6 * pj + n);
+      acc += s;
+    }
+  }
+  const float dz = ws.Q[(size_t)k * HW + p] * (ws.w[(size_t)k * HW + p] - acc);
+  if (dz_out) dz_out[(size_t)k * HW + p] = dz;
+  if (disps) disps[(size_t)f * HW + p] += dz;
+}
+
+int check_dims(int N, int E, int t0, int t1, int ht, int wd) {
+  DBAF_REQUIRE(N > 0 && E >= 0 && ht > 0 && wd > 0, "non-positive size");
+  DBAF_REQUIRE(t0 >= 0 && t1 >= t0 && t1 <= N, "need 0 <= t0 <= t1 <= n_frames");
+  return DBAF_OK;
+}
+
+}  // namespace
+}  // namespace dbaf
+
+using namespace dbaf;
+
+extern "C" int dbaf_ba_workspace_layout(int n_frames, int n_edges, int t0, int t1, int ht, int wd,
+                                        dbaf_ba_layout* out) {
+  DBAF_REQUIRE(out != nullptr, "null layout");
+  if (int rc = check_dims(n_frames, n_edges, t0, t1, ht, wd)) return rc;
+  fill_layout(n_frames, n_edges, t0, t1, ht, wd, out);
+  return DBAF_OK;
+}
+
+extern "C" int dbaf_ba_prepare(void* workspace, const int64_t* ii, const int64_t* jj, int E, int N,
+                               int t0, int t1, int ht, int wd, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
+  dbaf_ba_layout L;
+  fill_layout(N, E, t0, t1, ht, wd, &L);
+  Ws ws = view(workspace, L);
+  k_tables<<<1, 1024, 0, (cudaStream_t)stream>>>(ii, jj, E, N, t0, t1, ws);
+  DBAF_LAUNCH_CHECK("k_tables");
+  return DBAF_OK;
+}
+
+namespace {
+int pick_pxt(int Kcap, int HW) {
+  // keep at least ~2 CTAs per SM busy; more pixels per thread amortise the per-edge reduction
+  const long ctas1 = (long)Kcap * ((HW + 255) / 256);
+  if (ctas1 >= 148L * 16) return 4;
+  if (ctas1 >= 148L * 6) return 2;
+  return 1;
+}
+}  // namespace
+
+extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
+                                 const float* intrinsics, const float* disps_sens,
+                                 const float* targets, const float* weights, const float* eta,
+                                 int eta_rows, const int64_t* ii, const int64_t* jj, int E, int N,
+                                 int t0, int t1, int ht, int wd, float alpha, int motion_only,
+                                 int zero_first, int k_lo, int k_hi, void* stream) {
+  (void)ii;
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
+  DBAF_REQUIRE(motion_only || eta_rows >= 1, "eta needs at least one row");
+  dbaf_ba_layout L;
+  fill_layout(N, E, t0, t1, ht, wd, &L);
+  Ws ws = view(workspace, L);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int P = t1 - t0, HW = ht * wd;
+  const int64_t n = 6 * (int64_t)P;
+  if (zero_first) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, (n * n + n) * 8, st));
+  if (P == 0 && motion_only) return DBAF_OK;
+  if (k_lo < 0) k_lo = 0;
+  const int k_cap = (k_hi >= 0 ? std::min(k_hi, ws.Kcap) : ws.Kcap) - k_lo;
+  if (k_cap <= 0) return DBAF_OK;
+  const int pxt = pick_pxt(k_cap, HW);
+  dim3 grid((HW + 256 * pxt - 1) / (256 * pxt), k_cap);
+#define DBAF_LIN(PX, MO)                                                                       \
+  k_linearize<PX, MO><<<grid, kThreads, 0, st>>>(poses, disps, intrinsics, disps_sens, targets, \
+                                                 weights, eta, eta_rows, jj, t0, P, HW, wd,    \
+                                                 alpha, k_lo, k_hi, ws)
+  if (motion_only) {
+    if (pxt == 4) DBAF_LIN(4, true); else if (pxt == 2) DBAF_LIN(2, true); else DBAF_LIN(1, true);
+  } else {
+    if (pxt == 4) DBAF_LIN(4, false); else if (pxt == 2) DBAF_LIN(2, false); else DBAF_LIN(1, false);
+  }
+#undef DBAF_LIN
+  DBAF_LAUNCH_CHECK("k_linearize");
+  if (!motion_only && P > 0) {
+    const int tile_px = HW >= 2048 ? 1024 : 256;
+    dim3 sgrid((HW + tile_px - 1) / tile_px, k_cap);
+    k_schur<<<sgrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_schur");
+  }
+  return DBAF_OK;
+}
+
+extern "C" int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep, const double* prior,
+                             int prior_rows, int prior_cols, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  DBAF_REQUIRE(t1 >= t0, "t1 < t0");
+  // Only H, v, dx, info and Lfac are touched; their offsets depend on P alone.
+  dbaf_ba_layout L;
+  fill_layout(1, 0, 0, t1 - t0, 1, 1, &L);
+  Ws ws = view(workspace, L);
+  const int n = 6 * (t1 - t0);
+  if (n == 0) return DBAF_OK;
+  const int use_smem = n <= kSmemSolveMaxN;
+  const size_t smem = use_smem ? ((size_t)(n + 1) * n + n) * sizeof(double) : 0;
+  static bool attr_set = false;
+  if (!attr_set) {
+    DBAF_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr_set = true;
+  }
+  k_solve<<<1, kThreads, smem, (cudaStream_t)stream>>>(n, lm, ep, prior, prior_rows, prior_cols, use_smem, ws);
+  DBAF_LAUNCH_CHECK("k_solve");
+  return DBAF_OK;
+}
+
+extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,
+                               const int64_t* ii, const int64_t* jj, int E, int N, int t0, int t1,
+                               int ht, int wd, int update_poses, int update_disps, int k_lo, int k_hi,
+                               float* dx_out, float* dz_out, void* stream) {
+  (void)ii;
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
+  dbaf_ba_layout L;
+  fill_layout(N, E, t0, t1, ht, wd, &L);
+  Ws ws = view(workspace, L);
+  cudaStream_t st = (cudaStream_t)stream;
+  const int P = t1 - t0, HW = ht * wd;
+  const float* dx = dx_in ? dx_in : ws.dx;
+  if (k_lo < 0) k_lo = 0;
+  const int k_cap = (k_hi >= 0 ? std::min(k_hi, ws.Kcap) : ws.Kcap) - k_lo;
+  if (update_disps && k_cap > 0) {
+    dim3 grid((HW + kThreads - 1) / kThreads, k_cap);
+    k_backsub<<<grid, kThreads, 0, st>>>(jj, dx, disps, dz_out, t0, P, HW, k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_backsub");
+  }
+  if (P > 0 && (update_poses || dx_out)) {
+    k_pose_retract<<<1, 128, 0, st>>>(update_poses ? poses : nullptr, dx, t0, P, dx_out);
+    DBAF_LAUNCH_CHECK("k_pose_retract");
+  }
+  return DBAF_OK;
+}
+
+extern "C" int dbaf_ba(void* workspace, float* poses, float* disps, const float* intrinsics,
+                       const float* disps_sens, const float* targets, const float* weights,
+                       const float* eta, int eta_rows, const int64_t* ii, const int64_t* jj, int E,
+                       int N, int t0, int t1, int ht, int wd, int iterations, float lm, float ep,
+                       int motion_only, float* dx_out, float* dz_out, void* stream) {
+  if (int rc = dbaf_ba_prepare(workspace, ii, jj, E, N, t0, t1, ht, wd, stream)) return rc;
+  for (int it = 0; it < iterations; ++it) {
+    if (int rc = dbaf_ba_linearize(workspace, poses, disps, intrinsics, disps_sens, targets, weights,
+                                   eta, eta_rows, ii, jj, E, N, t0, t1, ht, wd, 0.05f, motion_only,
+                                   1, 0, -1, stream))
+      return rc;
+    if (int rc = dbaf_ba_solve(workspace, t0, t1, lm, ep, nullptr, 0, 0, stream)) return rc;
+    const bool last = it == iterations - 1;
+    if (int rc = dbaf_ba_retract(workspace, poses, disps, nullptr, ii, jj, E, N, t0, t1, ht, wd, 1,
+                                 motion_only ? 0 : 1, 0, -1, last ? dx_out : nullptr,
+                                 last ? dz_out : nullptr, stream))
+      return rc;
+  }
+  return DBAF_OK;
+}

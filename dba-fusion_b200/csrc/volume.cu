@@ -1,0 +1,166 @@
+// All-pairs correlation volume + 4-level pyramid (CorrBlock.__init__,
+// dbaf/modules/corr.py:24-38,63-71).
+//
+//   L0[e, p1, p2] = rn16( sum_c f1[e,c,p1] * f2[e,c,p2] / 16 )        (fp32 accumulate)
+//   L(l+1) = rn16( ((a+b)+c)+d ) / 4 ) over 2x2 blocks of the fp16 L(l)  (floor sizes)
+//
+// This file holds the entry point, the pyramid kernel for arbitrary shapes and a plain SIMT
+// GEMM that serves as the in-library cross-check of the tcgen05 kernel (volume_tc.cu).
+#include "common.cuh"
+
+#include <cstdlib>
+#include <cstring>
+
+namespace dbaf {
+
+// volume_tc.cu
+int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int wd, int levels,
+                   __half* const* out, void* workspace, size_t workspace_bytes, cudaStream_t st,
+                   bool* handled);
+size_t corr_volume_tc_workspace(int n, int C, int ht, int wd);
+
+namespace {
+
+constexpr int kTile = 64;
+
+// 64x64 output tile per CTA, 256 threads x (4x4), K staged 32 channels at a time.
+__global__ void __launch_bounds__(256)
+k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, int C, int HW,
+              __half* __restrict__ out) {
+  __shared__ float As[32][kTile + 1];
+  __shared__ float Bs[32][kTile + 1];
+  const int e = blockIdx.z;
+  const int m0 = blockIdx.y * kTile, n0 = blockIdx.x * kTile;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const __half* A = f1 + (size_t)e * C * HW;
+  const __half* B = f2 + (size_t)e * C * HW;
+  float acc[4][4] = {};
+  for (int c0 = 0; c0 < C; c0 += 32) {
+    for (int t = threadIdx.x; t < 32 * kTile; t += 256) {
+      const int c = t / kTile, x = t - c * kTile;
+      const bool cok = c0 + c < C;
+      As[c][x] = (cok && m0 + x < HW) ? __half2float(A[(size_t)(c0 + c) * HW + m0 + x]) : 0.f;
+      Bs[c][x] = (cok && n0 + x < HW) ? __half2float(B[(size_t)(c0 + c) * HW + n0 + x]) : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 8
+    for (int c = 0; c < 32; ++c) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = As[c][ty * 4 + i]; b[i] = Bs[c][tx * 4 + i]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= HW) continue;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int nn = n0 + tx * 4 + j;
+      if (nn < HW) out[((size_t)e * HW + m) * HW + nn] = __float2half_rn(acc[i][j] * 0.0625f);
+    }
+  }
+}
+
+__device__ __forceinline__ __half pool4(const __half* s, int w, int y, int x) {
+  const float a = __half2float(s[(2 * y) * w + 2 * x]), b = __half2float(s[(2 * y) * w + 2 * x + 1]);
+  const float c = __half2float(s[(2 * y + 1) * w + 2 * x]), d = __half2float(s[(2 * y + 1) * w + 2 * x + 1]);
+  return __float2half_rn((((a + b) + c) + d) * 0.25f);
+}
+
+// One CTA walks slabs (source pixels); the slab and every pooled level live in shared memory.
+__global__ void __launch_bounds__(128)
+k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int levels,
+          __half* __restrict__ L1, __half* __restrict__ L2, __half* __restrict__ L3) {
+  extern __shared__ __half sm[];
+  const int s0 = h2 * w2;
+  const int h1 = h2 >> 1, w1 = w2 >> 1, hq = h2 >> 2, wq = w2 >> 2, he = h2 >> 3, we = w2 >> 3;
+  __half* a0 = sm;
+  __half* a1 = a0 + s0;
+  __half* a2 = a1 + h1 * w1;
+  const bool vec = (s0 % 8 == 0) && ((reinterpret_cast<size_t>(L0) & 15) == 0);
+  for (long long s = blockIdx.x; s < slabs; s += gridDim.x) {
+    const __half* src = L0 + s * s0;
+    if (vec) {
+      for (int t = threadIdx.x; t < s0 / 8; t += 128)
+        reinterpret_cast<uint4*>(a0)[t] = __ldg(reinterpret_cast<const uint4*>(src) + t);
+    } else {
+      for (int t = threadIdx.x; t < s0; t += 128) a0[t] = src[t];
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < h1 * w1; t += 128) {
+      const __half v = pool4(a0, w2, t / w1, t % w1);
+      a1[t] = v;
+      L1[s * (h1 * w1) + t] = v;
+    }
+    __syncthreads();
+    if (levels > 2) {
+      for (int t = threadIdx.x; t < hq * wq; t += 128) {
+        const __half v = pool4(a1, w1, t / wq, t % wq);
+        a2[t] = v;
+        L2[s * (hq * wq) + t] = v;
+      }
+      __syncthreads();
+      if (levels > 3)
+        for (int t = threadIdx.x; t < he * we; t += 128) L3[s * (he * we) + t] = pool4(a2, wq, t / we, t % we);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace
+}  // namespace dbaf
+
+using namespace dbaf;
+
+extern "C" size_t dbaf_corr_volume_workspace_bytes(int n, int C, int ht, int wd) {
+  return corr_volume_tc_workspace(n, C, ht, wd);
+}
+
+extern "C" int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, int n, int C, int ht, int wd,
+                                        int levels, void* const* out_host, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  DBAF_REQUIRE(n >= 0 && C > 0 && ht > 0 && wd > 0, "bad sizes");
+  DBAF_REQUIRE(levels >= 1 && levels <= 4, "levels must be 1..4");
+  DBAF_REQUIRE(out_host != nullptr, "null output list");
+  if (n == 0) return DBAF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int HW = ht * wd;
+  __half* outs[4] = {nullptr, nullptr, nullptr, nullptr};
+  for (int l = 0; l < levels; ++l) outs[l] = static_cast<__half*>(out_host[l]);
+  const __half* f1 = static_cast<const __half*>(fmap1);
+  const __half* f2 = static_cast<const __half*>(fmap2);
+
+  // DBAF_VOLUME_IMPL=simt forces the cross-check kernels (tests use it to validate the
+  // tensor-core path against an independent implementation inside the same library).
+  const char* impl = std::getenv("DBAF_VOLUME_IMPL");
+  const bool force_simt = impl && std::strcmp(impl, "simt") == 0;
+  if (!force_simt) {
+    bool handled = false;
+    const int rc = corr_volume_tc(f1, f2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st, &handled);
+    if (rc != DBAF_OK) return rc;
+    if (handled) return DBAF_OK;
+  }
+  dim3 grid((HW + kTile - 1) / kTile, (HW + kTile - 1) / kTile, n);
+  k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, C, HW, outs[0]);
+  DBAF_LAUNCH_CHECK("k_volume_simt");
+  if (levels > 1) {
+    const size_t smem = ((size_t)HW + (size_t)(ht / 2) * (wd / 2) + (size_t)(ht / 4) * (wd / 4)) * 2 + 16;
+    DBAF_REQUIRE(smem <= 200 * 1024, "feature map too large for the pyramid kernel");
+    static bool attr = false;
+    if (!attr) {
+      DBAF_CUDA(cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+      attr = true;
+    }
+    const long long slabs = (long long)n * HW;
+    const int blocks = (int)std::min<long long>(slabs, 148LL * 16);
+    k_pyramid<<<blocks, 128, smem, st>>>(outs[0], slabs, ht, wd, levels, outs[1], outs[2], outs[3]);
+    DBAF_LAUNCH_CHECK("k_pyramid");
+  }
+  return DBAF_OK;
+}

@@ -1,0 +1,130 @@
+"""CorrBlock / AltCorrBlock with the reference's interface (dbaf/modules/corr.py:23-139), backed
+by the native volume+pyramid kernel and the single-launch pyramid lookup.
+
+Differences from the reference are internal only: the volume and its pyramid come from one
+native call instead of torch.matmul + 3x avg_pool2d, and the four per-level lookups are one
+launch.  Shapes, dtypes and values of everything a caller sees are the same.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn.functional as F
+
+import droid_backends
+
+
+class CorrSampler(torch.autograd.Function):
+    """dbaf/modules/corr.py:6-20"""
+
+    @staticmethod
+    def forward(ctx, volume, coords, radius):
+        ctx.save_for_backward(volume, coords)
+        ctx.radius = radius
+        corr, = droid_backends.corr_index_forward(volume, coords, radius)
+        return corr
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        volume, coords = ctx.saved_tensors
+        grad_output = grad_output.contiguous()
+        grad_volume, = droid_backends.corr_index_backward(volume, coords, grad_output, ctx.radius)
+        return grad_volume, None, None
+
+
+class CorrBlock:
+    """dbaf/modules/corr.py:23-71.  fmap1, fmap2: [batch, num, dim, ht, wd] (float16 on the
+    inference path)."""
+
+    def __init__(self, fmap1, fmap2, num_levels=4, radius=3):
+        self.num_levels = num_levels
+        self.radius = radius
+        batch, num, dim, ht, wd = fmap1.shape
+        f1 = fmap1.reshape(batch * num, dim, ht, wd).contiguous()
+        f2 = fmap2.reshape(batch * num, dim, ht, wd).contiguous()
+        if f1.dtype != torch.float16:
+            # the training path of the reference runs this in float32; the native kernel is fp16
+            f1, f2 = f1.half(), f2.half()
+        self.corr_pyramid = droid_backends.corr_volume_pyramid(f1, f2, num_levels)
+
+    def __call__(self, coords):
+        batch, num, ht, wd, _ = coords.shape
+        coords = coords.permute(0, 1, 4, 2, 3).contiguous().view(batch * num, 2, ht, wd)
+        if self.radius == 3 and not torch.is_grad_enabled():
+            out = droid_backends.corr_lookup_pyramid(self.corr_pyramid, coords.float(), self.radius)
+            return out.view(batch, num, -1, ht, wd)
+        out_pyramid = []
+        for i in range(self.num_levels):
+            corr = CorrSampler.apply(self.corr_pyramid[i], coords / 2 ** i, self.radius)
+            out_pyramid.append(corr.view(batch, num, -1, ht, wd))
+        return torch.cat(out_pyramid, dim=2)
+
+    def cat(self, other):
+        for i in range(self.num_levels):
+            self.corr_pyramid[i] = torch.cat([self.corr_pyramid[i], other.corr_pyramid[i]], 0)
+        return self
+
+    def __getitem__(self, index):
+        for i in range(self.num_levels):
+            self.corr_pyramid[i] = self.corr_pyramid[i][index]
+        return self
+
+    @staticmethod
+    def corr(fmap1, fmap2):
+        """All-pairs correlation only (level 0), dbaf/modules/corr.py:63-71."""
+        batch, num, dim, ht, wd = fmap1.shape
+        f1 = fmap1.reshape(batch * num, dim, ht, wd).contiguous().half()
+        f2 = fmap2.reshape(batch * num, dim, ht, wd).contiguous().half()
+        vol, = droid_backends.corr_volume_pyramid(f1, f2, 1)
+        return vol.view(batch, num, ht, wd, ht, wd)
+
+
+class CorrLayer(torch.autograd.Function):
+    """dbaf/modules/corr.py:74-88"""
+
+    @staticmethod
+    def forward(ctx, fmap1, fmap2, coords, r):
+        ctx.r = r
+        ctx.save_for_backward(fmap1, fmap2, coords)
+        corr, = droid_backends.altcorr_forward(fmap1, fmap2, coords, ctx.r)
+        return corr
+
+    @staticmethod
+    def backward(ctx, grad_corr):
+        fmap1, fmap2, coords = ctx.saved_tensors
+        grad_corr = grad_corr.contiguous()
+        g1, g2, gc = droid_backends.altcorr_backward(fmap1, fmap2, coords, grad_corr, ctx.r)
+        return g1, g2, gc, None
+
+
+class AltCorrBlock:
+    """Low-memory correlation: nothing is materialised, each lookup dots features on the fly.
+    Same constructor / call signature and output layout as dbaf/modules/corr.py:91-139."""
+
+    def __init__(self, fmaps, num_levels=4, radius=3):
+        self.num_levels, self.radius = num_levels, radius
+        B, N, C, H, W = fmaps.shape
+        level = fmaps.reshape(B * N, C, H, W) / 4.0          # same pre-scaling as CorrBlock.corr
+        self.pyramid = []                                     # level l: [B, N, H>>l, W>>l, C], pixel-major
+        for l in range(num_levels):
+            self.pyramid.append(level.permute(0, 2, 3, 1).contiguous().view(B, N, H >> l, W >> l, C))
+            if l + 1 < num_levels:
+                level = F.avg_pool2d(level, 2, stride=2)
+
+    def _lookup_level(self, l, coords, ii, jj):
+        # coords: [B, E, S, H, W, 2] in level-0 pixels
+        B, E, S, H, W, _ = coords.shape
+        src = self.pyramid[0][:, ii].flatten(0, 1).float().contiguous()
+        dst = self.pyramid[l][:, jj].flatten(0, 1).float().contiguous()
+        xy = (coords * (0.5 ** l)).reshape(B * E, S, H, W, 2).contiguous()
+        out = CorrLayer.apply(src, dst, xy, self.radius)      # [B*E, S, 49, H, W]
+        return out.view(B, E, S, -1, H, W).permute(0, 1, 3, 4, 5, 2)
+
+    def __call__(self, coords, ii, jj):
+        single = coords.dim() == 5                            # [B, E, H, W, 2] -> one coordinate set
+        if single:
+            coords = coords.unsqueeze(-2)
+        coords = coords.permute(0, 1, 4, 2, 3, 5)             # [B, E, S, H, W, 2]
+        corr = torch.cat([self._lookup_level(l, coords, ii, jj) for l in range(self.num_levels)], dim=2)
+        if single:
+            corr = corr.squeeze(-1)
+        return corr.contiguous()

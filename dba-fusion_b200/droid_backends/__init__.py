@@ -1,0 +1,449 @@
+"""`droid_backends` for B200: same names, argument order and return values as the module
+DBA-Fusion builds from src/droid.cpp (PYBIND11_MODULE at src/droid.cpp:297-316), backed by
+libdbaf_b200.so through its C ABI.  Put the directory that contains this package on
+PYTHONPATH ahead of the reference build and `import droid_backends` resolves here; nothing in
+dbaf/ needs to change (callers: dbaf/modules/corr.py:12,19,79,87, dbaf/depth_video.py:255-265,
+332,392-397,469-478,527,558, dbaf/dbaf.py:76,79,119,121).
+
+Tensors are torch CUDA tensors; torch only provides memory, the current stream and
+(for global BA) the process group.  All kernels are enqueued on the current stream.
+Extras beyond the reference surface: corr_volume_pyramid, corr_lookup_pyramid, ba_tables,
+ba_info.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from ._lib import BaLayout, c_void_p, check, lib
+
+__all__ = ["ba", "ba_extend", "frame_distance", "projmap", "depth_filter", "iproj",
+           "altcorr_forward", "altcorr_backward", "corr_index_forward", "corr_index_backward",
+           "BACore", "corr_volume_pyramid", "corr_lookup_pyramid", "ba_tables", "ba_info"]
+
+DBAF_F16, DBAF_F32 = 0, 1
+
+
+def _contig(**named):
+    # CHECK_CONTIGUOUS, src/droid.cpp:105-106
+    for name, t in named.items():
+        if not t.is_contiguous():
+            raise RuntimeError(f"{name} must be contiguous")
+
+
+def _cuda(dtype, **named):
+    for name, t in named.items():
+        if not t.is_cuda:
+            raise RuntimeError(f"{name} must be a CUDA tensor (droid_backends for B200 has no CPU path)")
+        if t.dtype != dtype:
+            raise RuntimeError(f"{name} must be {dtype}, got {t.dtype}")
+
+
+def _p(t):
+    return None if t is None else c_void_p(t.data_ptr())
+
+
+def _stream():
+    return c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _layout(N, E, t0, t1, ht, wd):
+    L = BaLayout()
+    check(lib.dbaf_ba_workspace_layout(N, E, t0, t1, ht, wd, ctypes.byref(L)), "dbaf_ba_workspace_layout")
+    return L
+
+
+def _ba_checks(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1):
+    _contig(targets=targets, weights=weights, poses=poses, disps=disps, intrinsics=intrinsics,
+            disps_sens=disps_sens, ii=ii, jj=jj)
+    _cuda(torch.float32, poses=poses, disps=disps, intrinsics=intrinsics, disps_sens=disps_sens,
+          targets=targets, weights=weights, eta=eta)
+    _cuda(torch.int64, ii=ii, jj=jj)
+    if disps.dim() != 3 or poses.dim() != 2 or poses.shape[1] != 7:
+        raise RuntimeError("poses must be [N,7] and disps [N,ht,wd]")
+    N, ht, wd = disps.shape
+    E = ii.numel()
+    if jj.numel() != E or targets.numel() != E * 2 * ht * wd or weights.numel() != targets.numel():
+        raise RuntimeError("targets/weights must be [E,2,ht,wd] with E = len(ii) = len(jj)")
+    if poses.shape[0] < t1 or disps_sens.shape != disps.shape or not (0 <= t0 <= t1 <= N):
+        raise RuntimeError("need 0 <= t0 <= t1 <= N and matching poses/disps/disps_sens")
+    return N, ht, wd, E
+
+
+def _eta_rows(eta, ii, t0, t1, HW):
+    eta = eta.contiguous()
+    rows = eta.numel() // HW
+    if rows * HW != eta.numel() or rows < 1:
+        raise RuntimeError("eta must be [K,ht,wd]")
+    if rows == 1:
+        # a single row broadcasts over all K depth frames; K then has to be counted
+        K = int(torch.unique(torch.cat([torch.arange(t0, t1, device=ii.device), ii])).numel())
+    else:
+        K = rows
+    return eta, rows, K
+
+
+class _Window:
+    """Workspace + dimensions shared by ba / ba_extend / BACore."""
+
+    def __init__(self, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
+                 need_eta=True):
+        self.N, self.ht, self.wd, self.E = _ba_checks(poses, disps, intrinsics, disps_sens, targets,
+                                                      weights, eta, ii, jj, t0, t1)
+        self.t0, self.t1, self.P, self.HW = int(t0), int(t1), int(t1 - t0), self.ht * self.wd
+        self.args = (poses, disps, intrinsics, disps_sens, targets, weights, ii, jj)
+        if need_eta:
+            self.eta, self.eta_rows, self.K = _eta_rows(eta, ii, t0, t1, self.HW)
+        else:
+            self.eta, self.eta_rows, self.K = eta, max(1, eta.numel() // self.HW), 0
+        self.L = _layout(self.N, self.E, self.t0, self.t1, self.ht, self.wd)
+        self.ws = torch.empty(self.L.total_bytes, dtype=torch.uint8, device=poses.device)
+        self.n = 6 * self.P
+
+    # views into the workspace ------------------------------------------------
+    def _view(self, off, count, dtype):
+        nbytes = count * torch.empty((), dtype=dtype).element_size()
+        return self.ws[off:off + nbytes].view(dtype)
+
+    def H(self):
+        return self._view(self.L.H, self.n * self.n, torch.float64).view(self.n, self.n)
+
+    def v(self):
+        return self._view(self.L.v, self.n, torch.float64)
+
+    def Hv(self):
+        """H and v as one contiguous float64 span (what global BA all-reduces)."""
+        return self._view(self.L.H, self.n * self.n + self.n, torch.float64)
+
+    def dx(self):
+        return self._view(self.L.dx, self.n, torch.float32).view(self.P, 6)
+
+    def info(self):
+        return self._view(self.L.info, 16, torch.int32)
+
+    # stages ------------------------------------------------------------------
+    def prepare(self):
+        poses, disps, intr, sens, tg, wt, ii, jj = self.args
+        check(lib.dbaf_ba_prepare(_p(self.ws), _p(ii), _p(jj), self.E, self.N, self.t0, self.t1,
+                                  self.ht, self.wd, _stream()), "dbaf_ba_prepare")
+
+    def linearize(self, alpha, motion_only=False, zero_first=True, k_lo=0, k_hi=-1):
+        poses, disps, intr, sens, tg, wt, ii, jj = self.args
+        check(lib.dbaf_ba_linearize(_p(self.ws), _p(poses), _p(disps), _p(intr), _p(sens), _p(tg), _p(wt),
+                                    _p(self.eta), self.eta_rows, _p(ii), _p(jj), self.E, self.N, self.t0,
+                                    self.t1, self.ht, self.wd, float(alpha), int(motion_only),
+                                    int(zero_first), int(k_lo), int(k_hi), _stream()), "dbaf_ba_linearize")
+
+    def solve(self, lm, ep, prior=None):
+        pr, pc = (prior.shape if prior is not None else (0, 0))
+        check(lib.dbaf_ba_solve(_p(self.ws), self.t0, self.t1, float(lm), float(ep), _p(prior),
+                                int(pr), int(pc), _stream()), "dbaf_ba_solve")
+
+    def retract(self, dx_in=None, update_poses=True, update_disps=True, k_lo=0, k_hi=-1,
+                want_dx=True, want_dz=True):
+        poses, disps, intr, sens, tg, wt, ii, jj = self.args
+        dx_out = torch.empty(self.P, 6, dtype=torch.float32, device=poses.device) if want_dx else None
+        dz_out = (torch.empty(self.K, self.HW, dtype=torch.float32, device=poses.device)
+                  if (want_dz and update_disps) else None)
+        check(lib.dbaf_ba_retract(_p(self.ws), _p(poses), _p(disps), _p(dx_in), _p(ii), _p(jj), self.E,
+                                  self.N, self.t0, self.t1, self.ht, self.wd, int(update_poses),
+                                  int(update_disps), int(k_lo), int(k_hi), _p(dx_out), _p(dz_out),
+                                  _stream()), "dbaf_ba_retract")
+        return dx_out, dz_out
+
+
+_last_window = None
+
+
+def ba_info():
+    """int32[16] status words of the most recent ba / ba_extend / BACore window (forces a
+    device synchronisation): [0]=K, [1]=#failed factorisations, [2]=bad index, [3]=eta row
+    mismatch, [4]=#Schur rows."""
+    if _last_window is None:
+        return None
+    return _last_window.info().cpu()
+
+
+def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj,
+       t0, t1, iterations, lm, ep, motion_only):
+    """droid_backends.ba (src/droid.cpp:109-138 -> ba_cuda, src/droid_kernels.cu:1394-1512).
+    Updates poses[t0:t1] and disps[kx] in place; returns [dx, dz] of the last iteration
+    (dz is None for motion_only, both None when iterations == 0)."""
+    global _last_window
+    w = _Window(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
+                need_eta=not motion_only)
+    _last_window = w
+    if iterations <= 0:
+        return [None, None]
+    dx = torch.empty(w.P, 6, dtype=torch.float32, device=poses.device)
+    dz = None if motion_only else torch.empty(w.K, w.HW, dtype=torch.float32, device=poses.device)
+    poses_, disps_, intr, sens, tg, wt, ii_, jj_ = w.args
+    check(lib.dbaf_ba(_p(w.ws), _p(poses_), _p(disps_), _p(intr), _p(sens), _p(tg), _p(wt), _p(w.eta),
+                      w.eta_rows, _p(ii_), _p(jj_), w.E, w.N, w.t0, w.t1, w.ht, w.wd, int(iterations),
+                      float(lm), float(ep), int(bool(motion_only)), _p(dx), _p(dz), _stream()), "dbaf_ba")
+    return [dx, dz]
+
+
+def _export(w, H, v):
+    """Copy the undamped reduced system to the caller's float64 CPU tensors
+    (src/droid_kernels.cu:1632-1640, 1889-1897: only H.size(0) x H.size(1) entries are written)."""
+    if H.dtype != torch.float64 or v.dtype != torch.float64 or H.is_cuda or v.is_cuda:
+        raise RuntimeError("H and v must be float64 CPU tensors")
+    r, c = H.shape
+    if r > w.n or c > w.n:
+        raise RuntimeError(f"H is larger than the {w.n}x{w.n} reduced camera system")
+    hv = w.Hv().cpu()                      # one D2H copy, synchronises the stream
+    H.copy_(hv[:w.n * w.n].view(w.n, w.n)[:r, :c])
+    v[:r].copy_(hv[w.n * w.n:][:r])
+
+
+def ba_extend(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, H, v, A_prior,
+              t0, t1, iterations, lm, ep, motion_only, skip_solve):
+    """droid_backends.ba_extend (src/droid.cpp:140-178 -> ba_cuda_extend,
+    src/droid_kernels.cu:1514-1678)."""
+    global _last_window
+    _contig(H=H, v=v, A_prior=A_prior)
+    w = _Window(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1,
+                need_eta=not motion_only)
+    _last_window = w
+    dx = dz = None
+    if iterations <= 0:
+        return [dx, dz]
+    w.prepare()
+    prior = None
+    for _ in range(int(iterations)):
+        w.linearize(0.05, motion_only=motion_only)
+        if motion_only:
+            w.solve(lm, ep)
+            dx, _ = w.retract(update_disps=False)
+            continue
+        _export(w, H, v)
+        if skip_solve:
+            return [dx, dz]
+        if prior is None:
+            if A_prior.dtype != torch.float64 or A_prior.dim() != 2:
+                raise RuntimeError("A_prior must be a 2-D float64 tensor")
+            prior = A_prior.to(poses.device).contiguous()
+        w.solve(lm, ep, prior)
+        dx, dz = w.retract()
+    return [dx, dz]
+
+
+class BACore:
+    """Stateful BA object (src/bacore.h:4-70, src/droid_kernels.cu:1786-1956): `hessian` exports
+    the undamped reduced camera system for the GTSAM factor graph, `retract` applies the
+    externally solved pose update plus the depth back-substitution."""
+
+    def __init__(self):
+        self._w = None
+
+    def init(self, poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj,
+             t0, t1, iterations, lm, ep, motion_only):
+        # `iterations` and `motion_only` are accepted and ignored, as in the reference (:1802-1814)
+        global _last_window
+        self._w = _Window(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1)
+        _last_window = self._w
+        self.lm, self.ep = float(lm), float(ep)
+        self.dx = None
+        self.dz = None
+        self._w.prepare()
+
+    def hessian(self, H, v):
+        w = self._w
+        w.linearize(0.001)                 # alpha = 0.001, src/droid_kernels.cu:1872
+        _export(w, H, v)
+
+    def optimize(self, H, v):
+        w = self._w
+        if H.shape != (w.n, w.n) or v.numel() != w.n:
+            raise RuntimeError("optimize expects the full reduced system")
+        hv = torch.cat([H.reshape(-1).to(torch.float64), v.reshape(-1).to(torch.float64)])
+        w.Hv().copy_(hv.to(w.ws.device))
+        w.solve(self.lm, self.ep)
+        self.dx = w.dx().clone()
+
+    def retract(self, dx):
+        w = self._w
+        if dx.is_cuda or dx.dtype != torch.float64:
+            raise RuntimeError("dx must be a float64 CPU tensor")
+        dxd = dx.reshape(-1)[:w.n].to(torch.float32).to(w.ws.device).contiguous()
+        self.dx, self.dz = w.retract(dx_in=dxd)
+        return [self.dx, self.dz]
+
+
+def ba_tables(ii, jj, t0, t1, n_frames, ht=1, wd=1):
+    """Graph bookkeeping tables built on the device (kx, kk_exp, csr_ptr/csr_idx, srow_ptr/srow_idx)
+    as int64 CPU tensors -- the tables ba_cuda derives at src/droid_kernels.cu:1416-1424,
+    993-1031 and 1316-1328."""
+    _cuda(torch.int64, ii=ii, jj=jj)
+    E = ii.numel()
+    L = _layout(n_frames, E, t0, t1, ht, wd)
+    ws = torch.empty(L.total_bytes, dtype=torch.uint8, device=ii.device)
+    check(lib.dbaf_ba_prepare(_p(ws), _p(ii.contiguous()), _p(jj.contiguous()), E, n_frames, t0, t1, ht, wd,
+                              _stream()), "dbaf_ba_prepare")
+    P = t1 - t0
+
+    def iv(off, n):
+        return ws[off:off + 4 * n].view(torch.int32).cpu().to(torch.int64)
+
+    info = iv(L.info, 16)
+    K = int(info[0])
+    ptr = iv(L.csr_ptr, K + 1)
+    sp = iv(L.srow_ptr, K + 1)
+    return dict(info=info, kx=iv(L.kx, K), kk_exp=iv(L.kk_exp, P + E), csr_ptr=ptr,
+                csr_idx=iv(L.csr_idx, int(ptr[-1])), srow_ptr=sp, srow_idx=iv(L.srow_idx, int(sp[-1])))
+
+
+# ----------------------------------------------------------------------- geometry --
+def frame_distance(poses, disps, intrinsics, ii, jj, beta):
+    """src/droid.cpp:181-197."""
+    _contig(poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
+    _cuda(torch.float32, poses=poses, disps=disps, intrinsics=intrinsics)
+    _cuda(torch.int64, ii=ii, jj=jj)
+    M = ii.numel()
+    dist = torch.empty(M, dtype=torch.float32, device=poses.device)
+    check(lib.dbaf_frame_distance(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), M, disps.shape[1],
+                                  disps.shape[2], float(beta), _p(dist), _stream()), "dbaf_frame_distance")
+    return dist
+
+
+def projmap(poses, disps, intrinsics, ii, jj):
+    """src/droid.cpp:200-215.  Returns [coords [E,ht,wd,3], valid [E,ht,wd,1]]."""
+    _contig(poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
+    _cuda(torch.float32, poses=poses, disps=disps, intrinsics=intrinsics)
+    _cuda(torch.int64, ii=ii, jj=jj)
+    E, ht, wd = ii.numel(), disps.shape[1], disps.shape[2]
+    coords = torch.empty(E, ht, wd, 3, dtype=torch.float32, device=poses.device)
+    valid = torch.empty(E, ht, wd, 1, dtype=torch.float32, device=poses.device)
+    check(lib.dbaf_projmap(_p(poses), _p(disps), _p(intrinsics), _p(ii), _p(jj), E, ht, wd, _p(coords),
+                           _p(valid), _stream()), "dbaf_projmap")
+    return [coords, valid]
+
+
+def iproj(poses, disps, intrinsics):
+    """src/droid.cpp:218-227.  Returns points [N,ht,wd,3] for N = disps.shape[0]."""
+    _contig(poses=poses, disps=disps, intrinsics=intrinsics)
+    _cuda(torch.float32, poses=poses, disps=disps, intrinsics=intrinsics)
+    N, ht, wd = disps.shape
+    pts = torch.empty(N, ht, wd, 3, dtype=torch.float32, device=disps.device)
+    check(lib.dbaf_iproj(_p(poses), _p(disps), _p(intrinsics), N, ht, wd, _p(pts), _stream()), "dbaf_iproj")
+    return pts
+
+
+def depth_filter(poses, disps, intrinsics, ix, thresh):
+    """src/droid.cpp:281-295.  Returns counter [M,ht,wd]."""
+    _contig(poses=poses, disps=disps, intrinsics=intrinsics, ix=ix, thresh=thresh)
+    _cuda(torch.float32, poses=poses, disps=disps, intrinsics=intrinsics, thresh=thresh)
+    _cuda(torch.int64, ix=ix)
+    N, ht, wd = disps.shape
+    M = ix.numel()
+    counter = torch.empty(M, ht, wd, dtype=torch.float32, device=disps.device)
+    check(lib.dbaf_depth_filter(_p(poses), _p(disps), _p(intrinsics), _p(ix), _p(thresh), M, N, ht, wd,
+                                _p(counter), _stream()), "dbaf_depth_filter")
+    return counter
+
+
+# -------------------------------------------------------------------- correlation --
+def _corr_dtype(t, name):
+    if t.dtype == torch.float16:
+        return DBAF_F16
+    if t.dtype == torch.float32:
+        return DBAF_F32
+    raise RuntimeError(f"{name}: only float16 and float32 are supported, got {t.dtype}")
+
+
+def corr_index_forward(volume, coords, radius):
+    """src/droid.cpp:231-239.  volume [n,h1,w1,h2,w2], coords [n,2,h1,w1] -> [corr [n,2r+1,2r+1,h1,w1]]."""
+    _contig(volume=volume, coords=coords)
+    _cuda(torch.float32, coords=coords)
+    if not volume.is_cuda:
+        raise RuntimeError("volume must be a CUDA tensor")
+    dt = _corr_dtype(volume, "volume")
+    n, h1, w1, h2, w2 = volume.shape
+    rd = 2 * radius + 1
+    corr = torch.empty(n, rd, rd, h1, w1, dtype=volume.dtype, device=volume.device)
+    check(lib.dbaf_corr_index_forward(_p(volume), dt, _p(coords), n, h1, w1, h2, w2, int(radius), _p(corr),
+                                      _stream()), "dbaf_corr_index_forward")
+    return [corr]
+
+
+def corr_index_backward(volume, coords, corr_grad, radius):
+    """src/droid.cpp:241-252.  Returns [volume_grad]."""
+    _contig(volume=volume, coords=coords, corr_grad=corr_grad)
+    _cuda(torch.float32, coords=coords)
+    dt = _corr_dtype(volume, "volume")
+    if corr_grad.dtype != volume.dtype:
+        raise RuntimeError("corr_grad must have the dtype of volume")
+    n, h1, w1, h2, w2 = volume.shape
+    grad = torch.empty_like(volume)
+    check(lib.dbaf_corr_index_backward(_p(coords), _p(corr_grad), dt, n, h1, w1, h2, w2, int(radius),
+                                       _p(grad), _stream()), "dbaf_corr_index_backward")
+    return [grad]
+
+
+def altcorr_forward(fmap1, fmap2, coords, radius):
+    """src/droid.cpp:254-264.  fmap1 [B,H1,W1,C], fmap2 [B,H2,W2,C], coords [B,S,H1,W1,2]."""
+    _contig(fmap1=fmap1, fmap2=fmap2, coords=coords)
+    if fmap1.dtype != torch.float32:
+        # the reference dispatches on dtype but DBA-Fusion only ever passes float32 (corr.py:120)
+        raise RuntimeError("altcorr_forward: float32 feature maps only")
+    _cuda(torch.float32, fmap1=fmap1, fmap2=fmap2, coords=coords)
+    B, S, H1, W1, _ = coords.shape
+    _, H2, W2, C = fmap2.shape
+    rd = 2 * radius + 1
+    corr = torch.empty(B, S, rd * rd, H1, W1, dtype=torch.float32, device=fmap1.device)
+    check(lib.dbaf_altcorr_forward(_p(fmap1), _p(fmap2), _p(coords), B, S, H1, W1, H2, W2, C, int(radius),
+                                   _p(corr), _stream()), "dbaf_altcorr_forward")
+    return [corr]
+
+
+def altcorr_backward(fmap1, fmap2, coords, corr_grad, radius):
+    """src/droid.cpp:266-279.  Returns [fmap1_grad, fmap2_grad, coords_grad (zeros)]."""
+    _contig(fmap1=fmap1, fmap2=fmap2, coords=coords, corr_grad=corr_grad)
+    _cuda(torch.float32, fmap1=fmap1, fmap2=fmap2, coords=coords, corr_grad=corr_grad)
+    B, S, H1, W1, _ = coords.shape
+    _, H2, W2, C = fmap2.shape
+    g1 = torch.empty_like(fmap1)
+    g2 = torch.empty_like(fmap2)
+    gc = torch.empty_like(coords)
+    check(lib.dbaf_altcorr_backward(_p(fmap1), _p(fmap2), _p(coords), _p(corr_grad), B, S, H1, W1, H2, W2, C,
+                                    int(radius), _p(g1), _p(g2), _p(gc), _stream()), "dbaf_altcorr_backward")
+    return [g1, g2, gc]
+
+
+def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
+    """Native CorrBlock.__init__ (dbaf/modules/corr.py:24-38,63-71): fmap1, fmap2 [n,C,ht,wd]
+    float16 -> list of `num_levels` tensors [n,ht,wd,ht>>l,wd>>l] float16."""
+    _contig(fmap1=fmap1, fmap2=fmap2)
+    _cuda(torch.float16, fmap1=fmap1, fmap2=fmap2)
+    n, C, ht, wd = fmap1.shape
+    if fmap2.shape != fmap1.shape:
+        raise RuntimeError("fmap1 and fmap2 must have the same shape")
+    outs = [torch.empty(n, ht, wd, ht >> l, wd >> l, dtype=torch.float16, device=fmap1.device)
+            for l in range(num_levels)]
+    nbytes = lib.dbaf_corr_volume_workspace_bytes(n, C, ht, wd)
+    ws = torch.empty(max(1, nbytes), dtype=torch.uint8, device=fmap1.device)
+    arr = (c_void_p * num_levels)(*[o.data_ptr() for o in outs])
+    check(lib.dbaf_corr_volume_pyramid(_p(fmap1), _p(fmap2), n, C, ht, wd, num_levels, arr, _p(ws), nbytes,
+                                       _stream()), "dbaf_corr_volume_pyramid")
+    return outs
+
+
+def corr_lookup_pyramid(pyramid, coords, radius=3):
+    """All levels of CorrBlock.__call__ (dbaf/modules/corr.py:40-50) in one launch.
+    pyramid[l] [n,h1,w1,h2>>l,w2>>l]; coords [n,2,h1,w1] (level-0 pixels) ->
+    [n, levels*(2r+1)^2, h1, w1], i.e. torch.cat(out_pyramid, dim=2) without the batch dim."""
+    _contig(coords=coords, **{f"pyramid[{i}]": t for i, t in enumerate(pyramid)})
+    _cuda(torch.float32, coords=coords)
+    dt = _corr_dtype(pyramid[0], "pyramid")
+    n, h1, w1, h2, w2 = pyramid[0].shape
+    for l, t in enumerate(pyramid):
+        if tuple(t.shape) != (n, h1, w1, h2 >> l, w2 >> l) or t.dtype != pyramid[0].dtype:
+            raise RuntimeError(f"pyramid level {l} has the wrong shape or dtype")
+    rd = 2 * radius + 1
+    out = torch.empty(n, len(pyramid) * rd * rd, h1, w1, dtype=pyramid[0].dtype, device=coords.device)
+    arr = (c_void_p * len(pyramid))(*[t.data_ptr() for t in pyramid])
+    check(lib.dbaf_corr_lookup_pyramid(arr, len(pyramid), dt, _p(coords), n, h1, w1, h2, w2, int(radius),
+                                       _p(out), _stream()), "dbaf_corr_lookup_pyramid")
+    return out

@@ -1,0 +1,185 @@
+/*
+ * dbaf_b200.h -- C ABI of libdbaf_b200.so: the sm_100a implementation of DBA-Fusion's
+ * `droid_backends` operator family (dense bundle adjustment + correlation).
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless its name ends in `_host`;
+ *   - tensors are dense row-major with the shape given in the comment;
+ *   - `stream` is a cudaStream_t passed as void*; every call only enqueues work on it
+ *     (no device synchronisation, no allocation) unless stated otherwise;
+ *   - return value: 0 = ok, DBAF_EINVAL = bad argument, DBAF_ECUDA = CUDA runtime error;
+ *     dbaf_last_error() returns a thread-local message for the last non-zero return;
+ *   - poses are [N,7] float32 (tx,ty,tz,qx,qy,qz,qw), world->camera; intrinsics [4] float32
+ *     (fx,fy,cx,cy) at the feature-map resolution; ii/jj are int64 edge endpoints.
+ *
+ * Each entry point names the reference interface it replaces (paths relative to the
+ * DBA-Fusion checkout).  The Python module `droid_backends` in dba-fusion_b200/ binds these
+ * one to one; INTEGRATION.md shows the binding.
+ */
+#ifndef DBAF_B200_H
+#define DBAF_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DBAF_OK 0
+#define DBAF_EINVAL 1
+#define DBAF_ECUDA 2
+
+#define DBAF_F16 0
+#define DBAF_F32 1
+
+int dbaf_version(void);
+const char* dbaf_last_error(void);
+
+/* ------------------------------------------------------------------ geometry ---- */
+
+/* droid_backends.projmap, src/droid.cpp:200-215, src/droid_kernels.cu:471-560,1706-1731.
+ * coords [E,ht,wd,3] (x,y; channel 2 = 0), valid [E,ht,wd,1]. */
+int dbaf_projmap(const float* poses, const float* disps, const float* intrinsics,
+                 const int64_t* ii, const int64_t* jj, int n_edges, int ht, int wd,
+                 float* coords, float* valid, void* stream);
+
+/* droid_backends.frame_distance, src/droid.cpp:181-197, src/droid_kernels.cu:562-702.  dist [M]. */
+int dbaf_frame_distance(const float* poses, const float* disps, const float* intrinsics,
+                        const int64_t* ii, const int64_t* jj, int n_pairs, int ht, int wd,
+                        float beta, float* dist, void* stream);
+
+/* droid_backends.iproj, src/droid.cpp:218-227, src/droid_kernels.cu:824-895.  points [N,ht,wd,3]. */
+int dbaf_iproj(const float* poses, const float* disps, const float* intrinsics,
+               int n_frames, int ht, int wd, float* points, void* stream);
+
+/* droid_backends.depth_filter, src/droid.cpp:281-295, src/droid_kernels.cu:706-820.
+ * counter [M,ht,wd] is overwritten (the reference allocates it zeroed). */
+int dbaf_depth_filter(const float* poses, const float* disps, const float* intrinsics,
+                      const int64_t* ix, const float* thresh, int n_idx, int n_frames,
+                      int ht, int wd, float* counter, void* stream);
+
+/* --------------------------------------------------------------- correlation ---- */
+
+/* droid_backends.corr_index_forward, src/droid.cpp:231-239, src/correlation_kernels.cu:19-70,126-155.
+ * volume [n,h1,w1,h2,w2] (dtype DBAF_F16 or DBAF_F32), coords [n,2,h1,w1] float32 (x then y),
+ * corr [n,2r+1,2r+1,h1,w1] same dtype, fully overwritten.  fp16 results reproduce the
+ * reference's rounding sequence bit for bit. */
+int dbaf_corr_index_forward(const void* volume, int dtype, const float* coords,
+                            int n, int h1, int w1, int h2, int w2, int radius,
+                            void* corr, void* stream);
+
+/* All pyramid levels in one launch: what CorrBlock.__call__ does with `levels` separate
+ * calls (dbaf/modules/corr.py:40-50).  volumes[l] is [n,h1,w1,h2>>l,w2>>l]; coords are the
+ * level-0 coordinates (scaled by 2^-l inside); out [n,levels*(2r+1)^2,h1,w1] is the
+ * concatenated tensor `torch.cat(out_pyramid, dim=2)`.  levels <= 8. */
+int dbaf_corr_lookup_pyramid(const void* const* volumes_host, int levels, int dtype,
+                             const float* coords, int n, int h1, int w1, int h2, int w2,
+                             int radius, void* out, void* stream);
+
+/* droid_backends.corr_index_backward, src/droid.cpp:241-252, src/correlation_kernels.cu:73-124,157-185.
+ * volume_grad [n,h1,w1,h2,w2] is fully overwritten. */
+int dbaf_corr_index_backward(const float* coords, const void* corr_grad, int dtype,
+                             int n, int h1, int w1, int h2, int w2, int radius,
+                             void* volume_grad, void* stream);
+
+/* droid_backends.altcorr_forward, src/droid.cpp:254-264, src/altcorr_kernel.cu:27-149,290-319.
+ * fmap1 [B,H1,W1,C], fmap2 [B,H2,W2,C] float32, coords [B,S,H1,W1,2], corr [B,S,(2r+1)^2,H1,W1]. */
+int dbaf_altcorr_forward(const float* fmap1, const float* fmap2, const float* coords,
+                         int B, int S, int H1, int W1, int H2, int W2, int C, int radius,
+                         float* corr, void* stream);
+
+/* droid_backends.altcorr_backward, src/droid.cpp:266-279, src/altcorr_kernel.cu:152-286,321-356.
+ * fmap1_grad/fmap2_grad are fully overwritten; coords_grad [B,S,H1,W1,2] is zero-filled. */
+int dbaf_altcorr_backward(const float* fmap1, const float* fmap2, const float* coords,
+                          const float* corr_grad, int B, int S, int H1, int W1, int H2, int W2,
+                          int C, int radius, float* fmap1_grad, float* fmap2_grad,
+                          float* coords_grad, void* stream);
+
+/* CorrBlock.corr + pyramid, dbaf/modules/corr.py:24-38,63-71 (torch.matmul + 3x avg_pool2d).
+ * fmap1, fmap2 [n,C,ht,wd] fp16 (channel-major, as stored by DepthVideo); out_host[l] is
+ * [n,ht,wd,ht>>l,wd>>l] fp16.  The 1/4 scaling of both operands is folded in.
+ * workspace: dbaf_corr_volume_workspace_bytes(n,C,ht,wd) bytes of device scratch. */
+size_t dbaf_corr_volume_workspace_bytes(int n, int C, int ht, int wd);
+int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, int n, int C, int ht, int wd,
+                             int levels, void* const* out_host, void* workspace,
+                             size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------- bundle adjustment ---- */
+
+/* Workspace layout (byte offsets into one caller-allocated device buffer).  The caller owns
+ * the buffer; H/v live in it as float64 so a host can read them back (BACore.hessian) or a
+ * collective can reduce them in place (edge-sharded global BA). */
+typedef struct dbaf_ba_layout {
+  int64_t total_bytes;
+  int64_t info;      /* int32[16]: [0]=K (#depth frames), [1]=#failed factorisations, [2]=bad index flag,
+                                   [3]=eta row mismatch flag, [4]=#rows of E inside the Schur complement */
+  int64_t H;         /* float64[(6P)^2] followed directly by v float64[6P] (one contiguous span) */
+  int64_t v;
+  int64_t dx;        /* float32[P*6] */
+  int64_t Lfac;      /* float64 factorisation scratch, used only when 6P > 160 */
+  int64_t kx;        /* int32[Kcap]   depth-frame list (sorted unique of cat(arange(t0,t1), ii)) */
+  int64_t kk_exp;    /* int32[P+E]    inverse map of the unique, src/droid_kernels.cu:1420-1424 */
+  int64_t csr_ptr;   /* int32[Kcap+1] edges grouped by source frame ... */
+  int64_t csr_idx;   /* int32[E]      ... in ascending edge order */
+  int64_t srow_ptr;  /* int32[Kcap+1] per depth frame: rows of E whose pose is inside [t0,t1) ... */
+  int64_t srow_idx;  /* int32[P+E]    ... row n<P = self row of pose t0+n, row P+e = edge e
+                                      (the graph/index lists of schur_block, src/droid_kernels.cu:1316-1328) */
+  int64_t frame2k;   /* int32[N]      frame -> position in kx, -1 if absent */
+  int64_t cursor;    /* int32[Kcap+1] scratch */
+  int64_t Q;         /* float32[Kcap,HW] */
+  int64_t w;         /* float32[Kcap,HW] */
+  int64_t Ei;        /* float32[P,6,HW] */
+  int64_t Eij;       /* float32[E,6,HW] */
+  int64_t Kcap;      /* capacity of the depth-frame tables = min(N, P+E) */
+} dbaf_ba_layout;
+
+int dbaf_ba_workspace_layout(int n_frames, int n_edges, int t0, int t1, int ht, int wd,
+                             dbaf_ba_layout* out_host);
+
+/* Graph bookkeeping of ba_cuda, src/droid_kernels.cu:1416-1424 plus the segment lists that
+ * accum_cuda rebuilds on the host every call (:993-1031).  Once per window. */
+int dbaf_ba_prepare(void* workspace, const int64_t* ii, const int64_t* jj, int n_edges,
+                    int n_frames, int t0, int t1, int ht, int wd, void* stream);
+
+/* One linearisation: projective_transform_kernel + SparseBlock assembly + accum_cuda + schur_block,
+ * src/droid_kernels.cu:220-468,1162-1222,993-1043,1297-1391.  Zeroes H/v first when `zero_first`,
+ * then adds this call's edges: A - S into H, b_A - b_S into v (undamped, float64), and stores
+ * E, Q, w for the back-substitution.  Only depth frames k in [k_lo,k_hi) (positions in kx) and
+ * their out-edges are processed, which is how edge-sharded global BA splits the work
+ * (k_hi < 0 means all).  alpha: sensor-depth prior weight (0.05 in `ba`, 0.001 in BACore).
+ * eta [eta_rows,ht,wd]; eta_rows must equal K or be 1 (broadcast). */
+int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
+                      const float* intrinsics, const float* disps_sens, const float* targets,
+                      const float* weights, const float* eta, int eta_rows,
+                      const int64_t* ii, const int64_t* jj, int n_edges, int n_frames,
+                      int t0, int t1, int ht, int wd, float alpha, int motion_only,
+                      int zero_first, int k_lo, int k_hi, void* stream);
+
+/* SparseBlock::solve / solveDense, src/droid_kernels.cu:1248-1288,180-198: L = H (+ prior);
+ * diag += ep + lm*diag; float64 Cholesky; dx -> workspace (float32), zeros if a pivot <= 0.
+ * prior (float64 [prior_rows,prior_cols], may be NULL) follows ba_cuda_extend :1624-1644. */
+int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep,
+                  const double* prior, int prior_rows, int prior_cols, void* stream);
+
+/* EvT6x1_kernel + dz + pose_retr_kernel + disp_retr_kernel, src/droid_kernels.cu:1140-1160,
+ * 1486-1506,943-991.  dx_in: float32 [P,6] (NULL = the workspace's dx).  poses/disps are updated
+ * in place.  dz_out [K,HW] (may be NULL), dx_out [P,6] (may be NULL).  update_disps=0 gives the
+ * motion-only update.  Depth frames [k_lo,k_hi) only, as in dbaf_ba_linearize. */
+int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,
+                    const int64_t* ii, const int64_t* jj, int n_edges, int n_frames,
+                    int t0, int t1, int ht, int wd, int update_poses, int update_disps,
+                    int k_lo, int k_hi, float* dx_out, float* dz_out, void* stream);
+
+/* droid_backends.ba, src/droid.cpp:109-138, src/droid_kernels.cu:1394-1512: prepare, then
+ * `iterations` x {linearize, solve, retract}.  dx_out [P,6], dz_out [K,HW] may be NULL. */
+int dbaf_ba(void* workspace, float* poses, float* disps, const float* intrinsics,
+            const float* disps_sens, const float* targets, const float* weights,
+            const float* eta, int eta_rows, const int64_t* ii, const int64_t* jj,
+            int n_edges, int n_frames, int t0, int t1, int ht, int wd, int iterations,
+            float lm, float ep, int motion_only, float* dx_out, float* dz_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DBAF_B200_H */

@@ -567,7 +567,7 @@ def depth_filter(poses, disps, intr, ix, thresh, dtype=np.float32):
                 hit = np.zeros(HW, bool)
                 for dv_, du_ in ((0, 0), (0, 1), (1, 0), (1, 1)):
                     dn = dj_img[np.minimum(v0 + dv_, ht - 1), np.minimum(u0 + du_, wd - 1)]
-                    hit |= np.abs(dtype(1.0) / dj - dtype(1.0) / dn) < t
+                    hit |= np.abs(1.0 / dj.astype(np.float64) - 1.0 / dn.astype(np.float64)) < float(t)
             count[b] += (ok & hit).astype(dtype)
     return count.reshape(len(ix), ht, wd)
 

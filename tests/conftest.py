@@ -1,0 +1,62 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (os.path.join(ROOT, "dba-fusion_b200"), os.path.join(ROOT, "oracle"), ROOT):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+def pytest_collection_modifyitems(config, items):
+    # keep the no-allocation entry point's test (if present) last, everything else in file order
+    items.sort(key=lambda it: (os.path.basename(str(it.fspath)).startswith("test_zz_"),))
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    import dbaf_oracle
+    return dbaf_oracle
+
+
+@pytest.fixture(scope="session")
+def synth():
+    from dbaf_b200 import synth as s
+    return s
+
+
+@pytest.fixture(scope="session")
+def dev():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
+
+
+@pytest.fixture(scope="session")
+def db():
+    import droid_backends
+    return droid_backends
+
+
+@pytest.fixture(scope="session")
+def ref():
+    """The reference CUDA extension rebuilt for sm_100a (oracle/_ref/droid_backends_ref.so)."""
+    import build_ref
+    mod = build_ref.load()
+    if mod is None:
+        pytest.skip("oracle/_ref/droid_backends_ref.so not built (python oracle/build_ref.py)")
+    return mod
+
+
+def relerr(a, b):
+    """normwise relative error max|a-b| / max|b|."""
+    a = np.asarray(a, np.float64)
+    b = np.asarray(b, np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
