@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""Benchmark of the dense-BA / correlation hot path (BASELINE.json: "dense-BA ms/iter + corr edges/s").
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c2|c3|c5]
+
+N = 1 (default): the TUM-VI-shaped frontend window (BASELINE.json configs[1]: 64x64 disparity maps,
+12 keyframes, 48 edges).  One step = one `droid_backends.ba(..., iterations=2)` call; `value` is
+milliseconds per Gauss-Newton iteration with every input already resident in HBM, `e2e` is the same
+through the public API with HOST (pinned) inputs, host->device copies and the device->host read of
+the result inside the timed region.  The correlation half of the metric (volume+pyramid build and the
+4-level lookup over the same 48 edges) is timed in the same run and reported under "corr".
+
+N > 1 (torchrun): edge-sharded global BA over a banded keyframe graph (configs[4]); every rank
+linearises the depth frames it owns, the reduced camera system is all-reduced with NCCL, the solve
+is replicated.  `value` is ms per iteration (strong scaling), max over ranks.
+
+--impl reference runs the unmodified reference extension (oracle/_ref/droid_backends_ref.so, built by
+oracle/build_ref.py from the reference's own sources) on the same workload; if that library is absent
+it times the oracle's CPU port instead.  Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (os.path.join(ROOT, "dba-fusion_b200"), os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+
+
+# ----------------------------------------------------------------------------- helpers
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm=float(d["hbm_gbs"]), tf_burst=float(d["bf16_tflops"]),
+                    tf_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), src="measured")
+    return dict(hbm=6650.0, tf_burst=1590.0, tf_sustained=1400.0, src="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def __enter__(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except Exception:
+            self.proc = None
+        return self
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def __exit__(self, *a):
+        if self.proc:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def summary(self):
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows if len(r) >= 6 for n, v in zip(names, r[2:6]) if v.lower().startswith("active")})
+        return dict(sm_mhz=statistics.median(sm) if sm else None, sm_max_mhz=max(mx) if mx else None,
+                    reasons=reasons, samples=len(sm))
+
+
+class L2Flusher:
+    def __init__(self, dev, mb=512):
+        self.buf = torch.empty(mb * 1024 * 1024 // 4, dtype=torch.float32, device=dev)
+
+    def __call__(self):
+        self.buf.add_(1.0)          # read + write of a buffer 4x the 126 MB L2
+
+
+def timed_steps(fn, steps, warmup, flush, reset=None):
+    """Device time of `steps` calls of fn (CUDA events on the current stream), L2 flushed and
+    state reset between steps outside the timed intervals.  Returns per-step milliseconds."""
+    for _ in range(warmup):
+        if reset:
+            reset()
+        fn()
+    torch.cuda.synchronize()
+    out = []
+    for _ in range(steps):
+        if reset:
+            reset()
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        b.synchronize()
+        out.append(a.elapsed_time(b))
+    return out
+
+
+def window_tensors(win, dev):
+    return {k: (torch.from_numpy(v.copy()).to(dev) if isinstance(v, np.ndarray) else v) for k, v in win.items()}
+
+
+def ba_call_args(t):
+    return (t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], t["eta"],
+            t["ii"], t["jj"])
+
+
+# --------------------------------------------------------------------- single-GPU arm
+def bench_local(args, dev, rank, world):
+    import droid_backends as db
+    from dbaf_b200 import synth
+    cfg = args.workload
+    ht, wd, P, E, _ = synth.CONFIGS[cfg]
+    win = synth.make_window(cfg, seed=0)
+    t = window_tensors(win, dev)
+    p0, d0 = t["poses"].clone(), t["disps"].clone()
+    t0, t1, iters = win["t0"], win["t1"], 2
+    flush = L2Flusher(dev)
+    peaks = measured_peaks()
+    HW, K = ht * wd, win["eta"].shape[0]
+
+    def reset():
+        t["poses"].copy_(p0)
+        t["disps"].copy_(d0)
+
+    def step():
+        db.ba(*ba_call_args(t), t0, t1, iters, 1e-4, 0.1, False)
+
+    with ClockSampler(dev.index or 0) as clk:
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+        ms = timed_steps(step, args.steps, args.warmup, flush, reset)
+        torch.cuda.synchronize()
+        if world > 1:
+            torch.distributed.barrier()
+    step_ms = sum(ms) / len(ms)
+
+    # ---- per-stage device times (same inputs, L2 flushed): which kernel dominates
+    w = db._Window(*ba_call_args(t), t0, t1)
+    w.prepare()
+    stage = {}
+    for name, fn in (("linearize", lambda: w.linearize(0.05, motion_only=2, zero_first=False)),
+                     ("linearize+schur", lambda: w.linearize(0.05)),
+                     ("solve", lambda: w.solve(1e-4, 0.1)),
+                     ("retract", lambda: w.retract(want_dx=False, want_dz=False))):
+        stage[name] = statistics.mean(timed_steps(fn, max(5, args.steps), 3, flush, reset))
+    lin_ms = stage["linearize"]
+    lin_bytes = E * HW * 20 + K * HW * 12          # algorithmic bytes of the linearise kernel
+    roof = dict(bound="hbm", kernel="k_linearize", achieved=lin_bytes / (lin_ms * 1e-3) / 1e9, peak=peaks["hbm"],
+                unit="GB/s", peak_source=peaks["src"] + " (burst, kernel timed alone)", traffic=None,
+                algorithmic_bytes=lin_bytes, ms=lin_ms)
+    roof["frac"] = roof["achieved"] / roof["peak"]
+
+    # ---- end to end through the public API with host buffers
+    host = {k: torch.from_numpy(win[k]).pin_memory() for k in
+            ("poses", "disps", "disps_sens", "targets", "weights", "eta", "ii", "jj", "intrinsics")}
+    out_dx = torch.empty(t1 - t0, 6).pin_memory()
+    out_p = torch.empty(t1 - t0, 7).pin_memory()
+    h2d = sum(host[k].numel() * host[k].element_size() for k in host)
+    d2h = out_dx.numel() * 4 + out_p.numel() * 4
+
+    def e2e_step():
+        g = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
+        dx, dz = db.ba(g["poses"], g["disps"], g["intrinsics"], g["disps_sens"], g["targets"], g["weights"],
+                       g["eta"], g["ii"], g["jj"], t0, t1, iters, 1e-4, 0.1, False)
+        out_dx.copy_(dx, non_blocking=True)
+        out_p.copy_(g["poses"][t0:t1], non_blocking=True)
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        e2e_step()
+    e2e_ms = []
+    for _ in range(args.steps):
+        flush()
+        torch.cuda.synchronize()
+        a = time.perf_counter()
+        e2e_step()
+        e2e_ms.append((time.perf_counter() - a) * 1e3)
+    e2e_val = statistics.mean(e2e_ms) / iters
+
+    # ---- correlation half of the metric: volume + pyramid build, 4-level lookup (same 48 edges)
+    corr = bench_corr(db, synth, cfg, win, dev, flush, peaks, args)
+
+    line = dict(metric="dense-BA ms/iter", value=step_ms / iters, unit="ms/iter", n_gpus=world, steps=args.steps,
+                warmup=args.warmup, ms_per_step=step_ms, higher_is_better=False, scaling="weak",
+                vs_baseline=None, dtype="f32", data="synthetic",
+                config=dict(workload=f"{cfg}: {ht}x{wd} disparity maps, {win['poses'].shape[0]} keyframes, "
+                                     f"{E} edges, {iters} GN iterations per step (droid_backends.ba)",
+                            l2="512 MB read+write between steps (inputs are smaller than L2)",
+                            replicas=world),
+                roofline=roof, stages_ms=stage,
+                e2e=dict(value=e2e_val, unit="ms/iter", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
+                         ms_per_step=statistics.mean(e2e_ms)),
+                gpu_launches=args.steps * (1 + iters * 5), corr=corr)
+    return line, clk
+
+
+def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
+    ht, wd, P, E, _ = synth.CONFIGS[cfg]
+    HW = ht * wd
+    feats = torch.from_numpy(synth.make_features(cfg, seed=0, n_frames=win["poses"].shape[0])).to(dev)
+    ii, jj = torch.from_numpy(win["ii"]).to(dev), torch.from_numpy(win["jj"]).to(dev)
+    f1, f2 = feats[ii].contiguous(), feats[jj].contiguous()
+    coords = torch.from_numpy(synth.lookup_coords(win, 0.05, 0)).to(dev)
+    n = f1.shape[0]
+    steps = max(3, min(args.steps, 10))
+    pyr = db.corr_volume_pyramid(f1, f2, 4)
+    vol_ms = statistics.mean(timed_steps(lambda: db.corr_volume_pyramid(f1, f2, 4), steps, 3, flush))
+    look_ms = statistics.mean(timed_steps(lambda: db.corr_lookup_pyramid(pyr, coords, 3), steps, 3, flush))
+    lvl = sum((ht >> l) * (wd >> l) for l in range(4))
+    vol_bytes = n * (2 * HW * 128 * 2 + 2 * HW * lvl)             # read both fmaps, write 4 levels
+    vol_flop = n * 2.0 * HW * HW * 128
+    look_bytes = n * HW * 912                                     # 64 taps + 49 outputs per level + coords
+    return dict(
+        volume_pyramid=dict(edges_per_s=n / (vol_ms * 1e-3), ms=vol_ms,
+                            roofline=dict(bound="hbm", achieved=vol_bytes / (vol_ms * 1e-3) / 1e9, peak=peaks["hbm"],
+                                          unit="GB/s", frac=vol_bytes / (vol_ms * 1e-3) / 1e9 / peaks["hbm"]),
+                            tensor=dict(achieved=vol_flop / (vol_ms * 1e-3) / 1e12, peak=peaks["tf_burst"], unit="TFLOP/s",
+                                        frac=vol_flop / (vol_ms * 1e-3) / 1e12 / peaks["tf_burst"])),
+        lookup=dict(edges_per_s=n / (look_ms * 1e-3), ms=look_ms,
+                    roofline=dict(bound="hbm", achieved=look_bytes / (look_ms * 1e-3) / 1e9, peak=peaks["hbm"],
+                                  unit="GB/s", frac=look_bytes / (look_ms * 1e-3) / 1e9 / peaks["hbm"])),
+        edges=n)
+
+
+def cpu_baseline(cfg, budget_s=20.0):
+    """Oracle port (numpy, float32) of `ba` on the same workload, on the host cores of this box."""
+    import dbaf_oracle as oracle
+    from dbaf_b200 import synth
+    try:
+        from threadpoolctl import threadpool_limits
+    except Exception:
+        threadpool_limits = None
+    win = synth.make_window(cfg, seed=0)
+    times = []
+    t_start = time.perf_counter()
+
+    def one():
+        p, d = win["poses"].copy(), win["disps"].copy()
+        a = time.perf_counter()
+        oracle.ba(p, d, win["intrinsics"], win["disps_sens"], win["targets"], win["weights"], win["eta"],
+                  win["ii"], win["jj"], win["t0"], win["t1"], 2, 1e-4, 0.1, False, dtype=np.float32)
+        times.append((time.perf_counter() - a) * 1e3)
+
+    ctx = threadpool_limits(limits=1) if threadpool_limits else None
+    try:
+        if ctx:
+            ctx.__enter__()
+        one()
+        while time.perf_counter() - t_start < budget_s and len(times) < 6:
+            one()
+    finally:
+        if ctx:
+            ctx.__exit__(None, None, None)
+    best = statistics.median(times)
+    return dict(value=best / 2, unit="ms/iter", cores=1, kind="port",
+                sample=f"{len(times)} x oracle.ba (numpy float32, 2 iterations) on the full {cfg} window")
+
+
+# --------------------------------------------------------------------- reference arm
+def bench_reference(args, dev):
+    import build_ref
+    from dbaf_b200 import synth
+    cfg = args.workload
+    ht, wd, P, E, _ = synth.CONFIGS[cfg]
+    win = synth.make_window(cfg, seed=0)
+    ref = build_ref.load() if torch.cuda.is_available() else None
+    iters = 2
+    if ref is None:
+        cb = cpu_baseline(cfg, budget_s=60.0)
+        val, step_ms, kind = cb["value"], cb["value"] * iters, cb
+    else:
+        t = window_tensors(win, dev)
+        p0, d0 = t["poses"].clone(), t["disps"].clone()
+        flush = L2Flusher(dev)
+
+        def reset():
+            t["poses"].copy_(p0)
+            t["disps"].copy_(d0)
+
+        def step():
+            ref.ba(*ba_call_args(t), win["t0"], win["t1"], iters, 1e-4, 0.1, False)
+
+        # wall clock: the reference synchronises with the host ~20 times per iteration
+        for _ in range(args.warmup):
+            reset()
+            step()
+        torch.cuda.synchronize()
+        ms = []
+        for _ in range(args.steps):
+            reset()
+            flush()
+            torch.cuda.synchronize()
+            a = time.perf_counter()
+            step()
+            torch.cuda.synchronize()
+            ms.append((time.perf_counter() - a) * 1e3)
+        step_ms = statistics.mean(ms)
+        val = step_ms / iters
+        kind = dict(value=val, unit="ms/iter", cores=1, kind="reference",
+                    sample=f"{args.steps} x reference droid_backends.ba (oracle/_ref, CUDA kernels + host Eigen "
+                           f"float64 solve on one core) on the full {cfg} window")
+    return dict(impl="reference", metric="dense-BA ms/iter", value=val, unit="ms/iter", n_gpus=1, steps=args.steps,
+                warmup=args.warmup, ms_per_step=step_ms, higher_is_better=False, scaling="weak", vs_baseline=None,
+                dtype="f32", data="synthetic",
+                config=dict(workload=f"{cfg}: {ht}x{wd} disparity maps, {win['poses'].shape[0]} keyframes, {E} edges, "
+                                     f"{iters} GN iterations per step"),
+                cpu_baseline=kind,
+                e2e=dict(value=val, unit="ms/iter", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
+
+
+# ----------------------------------------------------------------------------- main
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(3, args.warmup)
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        args.workload = args.workload or "c2"
+        dev = torch.device("cuda:0") if torch.cuda.is_available() else torch.device("cpu")
+        print(json.dumps(bench_reference(args, dev)))
+        return
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (there is no CPU fallback); use --impl reference for the CPU port")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        torch.distributed.init_process_group("nccl", device_id=dev)
+
+    if world > 1 or (args.workload or "").startswith("c5"):
+        from dbaf_b200 import global_ba
+        line, clk = global_ba.bench(args, dev, rank, world, ClockSampler, L2Flusher, measured_peaks())
+    else:
+        args.workload = args.workload or "c2"
+        line, clk = bench_local(args, dev, rank, world)
+
+    if world > 1:
+        v = torch.tensor([line["ms_per_step"]], device=dev, dtype=torch.float64)
+        torch.distributed.all_reduce(v, op=torch.distributed.ReduceOp.MAX)
+        scale = float(v.item()) / line["ms_per_step"]
+        line["ms_per_step"] = float(v.item())
+        line["value"] *= scale
+    if rank == 0:
+        line["clocks"] = clk.summary()
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = cpu_baseline(args.workload if args.workload in ("c1", "c2", "c2_real", "c3", "tiny") else "c2")
+        print(json.dumps(line))
+    if world > 1:
+        torch.distributed.barrier()
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

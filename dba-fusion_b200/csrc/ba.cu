@@ -722,7 +722,8 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
   (void)ii;
   DBAF_REQUIRE(workspace != nullptr, "null workspace");
   if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
-  DBAF_REQUIRE(motion_only || eta_rows >= 1, "eta needs at least one row");
+  DBAF_REQUIRE(motion_only == 1 || eta_rows >= 1, "eta needs at least one row");
+  DBAF_REQUIRE(motion_only >= 0 && motion_only <= 2, "motion_only must be 0, 1 or 2");
   dbaf_ba_layout L;
   fill_layout(N, E, t0, t1, ht, wd, &L);
   Ws ws = view(workspace, L);
@@ -730,7 +731,7 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
   const int P = t1 - t0, HW = ht * wd;
   const int64_t n = 6 * (int64_t)P;
   if (zero_first) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, (n * n + n) * 8, st));
-  if (P == 0 && motion_only) return DBAF_OK;
+  if (P == 0 && motion_only == 1) return DBAF_OK;
   if (k_lo < 0) k_lo = 0;
   const int k_cap = (k_hi >= 0 ? std::min(k_hi, ws.Kcap) : ws.Kcap) - k_lo;
   if (k_cap <= 0) return DBAF_OK;
@@ -740,14 +741,14 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
   k_linearize<PX, MO><<<grid, kThreads, 0, st>>>(poses, disps, intrinsics, disps_sens, targets, \
                                                  weights, eta, eta_rows, jj, t0, P, HW, wd,    \
                                                  alpha, k_lo, k_hi, ws)
-  if (motion_only) {
+  if (motion_only == 1) {
     if (pxt == 4) DBAF_LIN(4, true); else if (pxt == 2) DBAF_LIN(2, true); else DBAF_LIN(1, true);
   } else {
     if (pxt == 4) DBAF_LIN(4, false); else if (pxt == 2) DBAF_LIN(2, false); else DBAF_LIN(1, false);
   }
 #undef DBAF_LIN
   DBAF_LAUNCH_CHECK("k_linearize");
-  if (!motion_only && P > 0) {
+  if (motion_only == 0 && P > 0) {
     const int tile_px = HW >= 2048 ? 1024 : 256;
     dim3 sgrid((HW + tile_px - 1) / tile_px, k_cap);
     k_schur<<<sgrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, k_lo, k_hi, ws);

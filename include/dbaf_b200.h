@@ -148,7 +148,9 @@ int dbaf_ba_prepare(void* workspace, const int64_t* ii, const int64_t* jj, int n
  * E, Q, w for the back-substitution.  Only depth frames k in [k_lo,k_hi) (positions in kx) and
  * their out-edges are processed, which is how edge-sharded global BA splits the work
  * (k_hi < 0 means all).  alpha: sensor-depth prior weight (0.05 in `ba`, 0.001 in BACore).
- * eta [eta_rows,ht,wd]; eta_rows must equal K or be 1 (broadcast). */
+ * eta [eta_rows,ht,wd]; eta_rows must equal K or be 1 (broadcast).
+ * motion_only: 0 = full, 1 = pose blocks only (no E/Q/w, no Schur), 2 = full linearisation but
+ * the Schur kernel is not launched (profiling aid: times the Jacobian kernel alone). */
 int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
                       const float* intrinsics, const float* disps_sens, const float* targets,
                       const float* weights, const float* eta, int eta_rows,

@@ -1,0 +1,127 @@
+"""Differential tests against the UNMODIFIED reference CUDA extension (oracle/_ref, built from
+/root/reference/src by oracle/build_ref.py) on the same GPU and the same inputs.  Skipped when the
+extension was never built.  This is the strongest parity statement the repo makes: the reference
+has no tests or golden vectors of its own."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import ba_args, relerr, to_torch
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def _np(t):
+    return t.detach().cpu().numpy()
+
+
+@pytest.mark.parametrize("cfg,kw", [
+    ("tiny", dict(seed=1, sensor_frac=0.3, near_frac=0.05, stereo_edges=2)),
+    ("c2", dict(seed=0)),
+    ("c2_real", dict(seed=1, sensor_frac=0.3)),
+    ("c3", dict(seed=2, near_frac=0.02)),
+])
+def test_bacore_hessian_and_retract(dev, db, ref, synth, cfg, kw):
+    w = synth.make_window(cfg, **kw)
+    n = 6 * (w["t1"] - w["t0"])
+    outs = []
+    for mod in (db, ref):
+        t = to_torch(w, dev)
+        core = mod.BACore()
+        core.init(*ba_args(t), w["t0"], w["t1"], 2, 1e-4, 0.1, False)
+        H = torch.zeros(n, n, dtype=torch.float64)
+        v = torch.zeros(n, dtype=torch.float64)
+        core.hessian(H, v)
+        dx = torch.from_numpy(np.random.default_rng(5).normal(0, 1e-3, n))
+        dxr, dzr = core.retract(dx)
+        outs.append((H.numpy().copy(), v.numpy().copy(), _np(dxr), _np(dzr), _np(t["poses"]), _np(t["disps"])))
+        del core
+    (H, v, dx, dz, p, d), (Hr, vr, dxr, dzr, pr, dr) = outs
+    assert relerr(H, Hr) < TOL and relerr(v, vr) < TOL
+    assert relerr(dx, dxr) < 1e-6 and relerr(dz, dzr) < TOL
+    assert relerr(p, pr) < 1e-6 and relerr(d, dr) < TOL
+
+
+@pytest.mark.parametrize("cfg,kw", [("tiny", dict(seed=2)), ("c2", dict(seed=0)), ("c3", dict(seed=1))])
+@pytest.mark.parametrize("motion_only", [False, True])
+def test_ba(dev, db, ref, oracle, synth, cfg, kw, motion_only):
+    w = synth.make_window(cfg, **kw)
+    res = []
+    for mod in (db, ref):
+        t = to_torch(w, dev)
+        dx, dz = mod.ba(*ba_args(t), w["t0"], w["t1"], 2, 1e-4, 0.1, motion_only)
+        res.append((_np(dx), None if dz is None else _np(dz), _np(t["poses"]), _np(t["disps"])))
+    (dx, dz, p, d), (dxr, dzr, pr, dr) = res
+    # float64 answer to measure how far the reference itself is from the exact solution
+    p64, d64 = w["poses"].astype(np.float64), w["disps"].astype(np.float64)
+    dx64, dz64 = oracle.ba(p64, d64, w["intrinsics"], w["disps_sens"], w["targets"], w["weights"], w["eta"],
+                           w["ii"], w["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, motion_only, dtype=np.float64)
+    slack = lambda r, x: max(TOL, 3 * relerr(r, x))      # see test_gpu_parity.test_ba_vs_oracle
+    assert relerr(dx, dxr) < slack(dxr, dx64), (relerr(dx, dxr), relerr(dxr, dx64), relerr(dx, dx64))
+    assert relerr(p, pr) < TOL
+    if motion_only:
+        assert dz is None and dzr is None
+    else:
+        assert relerr(dz, dzr) < slack(dzr, dz64), (relerr(dz, dzr), relerr(dzr, dz64))
+        assert relerr(d, dr) < slack(dr, d64)
+
+
+def test_geometry(dev, db, ref, synth):
+    w = synth.make_window("c2_real", seed=3, near_frac=0.05)
+    t = to_torch(w, dev)
+    a, b = db.projmap(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"]), \
+        ref.projmap(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"])
+    assert (a[1] != b[1]).float().mean().item() < 1e-5
+    assert relerr(_np(a[0]), _np(b[0])) < 1e-5
+    for beta in (0.3, 0.0, 1.0):
+        d1 = db.frame_distance(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"], beta)
+        d2 = ref.frame_distance(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"], beta)
+        assert torch.equal(d1 > 999, d2 > 999)
+        assert relerr(_np(d1), _np(d2)) < 1e-4
+    assert relerr(_np(db.iproj(t["poses"], t["disps"], t["intrinsics"])),
+                  _np(ref.iproj(t["poses"], t["disps"], t["intrinsics"]))) < 1e-6
+    tg = to_torch(dict(p=w["poses_gt"], d=w["disps_gt"]), dev)
+    ix = torch.arange(w["poses"].shape[0], device=dev)
+    th = torch.full((len(ix),), 0.05, device=dev)
+    c1 = db.depth_filter(tg["p"], tg["d"], t["intrinsics"], ix, th)
+    c2 = ref.depth_filter(tg["p"], tg["d"], t["intrinsics"], ix, th)
+    assert (c1 != c2).float().mean().item() < 1e-4
+
+
+@pytest.mark.parametrize("cfg,n", [("tiny", 4), ("c2", 3), ("c2_real", 3), ("c3", 3)])
+def test_corr_lookup_bit_exact(dev, db, ref, synth, cfg, n):
+    """fp16 lookups must reproduce the reference bit for bit on every pyramid level."""
+    w = synth.make_window(cfg, seed=0)
+    f = torch.from_numpy(synth.make_features(cfg, seed=0, n_frames=w["poses"].shape[0])).to(dev)
+    coords = torch.from_numpy(synth.lookup_coords(w, 0.05, 0)[:n]).to(dev)
+    f1, f2 = f[w["ii"][:n]], f[w["jj"][:n]]
+    nn, C, ht, wd = f1.shape
+    corr = torch.matmul((f1.reshape(nn, C, -1) / 4.0).transpose(1, 2), f2.reshape(nn, C, -1) / 4.0)
+    corr = corr.reshape(nn * ht * wd, 1, ht, wd)
+    for l in range(4):
+        vol = corr.view(nn, ht, wd, ht >> l, wd >> l).contiguous()
+        c = (coords / 2 ** l).contiguous()
+        got, = db.corr_index_forward(vol, c, 3)
+        want, = ref.corr_index_forward(vol, c, 3)
+        assert torch.equal(got.view(torch.int16), want.view(torch.int16)), (cfg, l)
+        g32, = db.corr_index_forward(vol.float(), c, 3)
+        w32, = ref.corr_index_forward(vol.float(), c, 3)
+        assert relerr(_np(g32), _np(w32)) < 1e-6
+        corr = torch.nn.functional.avg_pool2d(corr, 2, stride=2)
+
+
+def test_altcorr(dev, db, ref, synth):
+    w = synth.make_window("c4", seed=0)
+    f = torch.from_numpy(synth.make_features("c4", seed=0, n_frames=w["poses"].shape[0])).to(dev)
+    n = 4
+    coords = torch.from_numpy(synth.lookup_coords(w, 0.05, 0)[:n]).to(dev).permute(0, 2, 3, 1)[:, None].contiguous()
+    f1 = (f[w["ii"][:n]].float() / 4.0).permute(0, 2, 3, 1).contiguous()
+    f2 = (f[w["jj"][:n]].float() / 4.0).permute(0, 2, 3, 1).contiguous()
+    got, = db.altcorr_forward(f1, f2, coords, 3)
+    want, = ref.altcorr_forward(f1, f2, coords, 3)
+    assert relerr(_np(got), _np(want)) < 1e-5
+    g = torch.randn_like(want)
+    a = db.altcorr_backward(f1, f2, coords, g, 3)
+    b = ref.altcorr_backward(f1, f2, coords, g, 3)
+    assert relerr(_np(a[0]), _np(b[0])) < 1e-5 and relerr(_np(a[1]), _np(b[1])) < 1e-4
