@@ -11,6 +11,12 @@ namespace {
 constexpr int kThreads = 128;
 constexpr int kChunk = 32;   // CHANNEL_STRIDE of the reference: partial dots over 32 channels
 
+// see corr.cu: saturating float->int like the reference, clamped so window arithmetic cannot overflow
+__device__ __forceinline__ int window_base(float floored, int r) {
+  const int v = (int)floored;
+  return max(-(1 << 24), min(1 << 24, v)) - r;
+}
+
 template <int R>
 __global__ void __launch_bounds__(kThreads)
 k_altcorr_fwd(const float* __restrict__ f1, const float* __restrict__ f2,
@@ -26,7 +32,7 @@ k_altcorr_fwd(const float* __restrict__ f1, const float* __restrict__ f2,
   const float y = __ldg(coords + ((size_t)bs * HW1 + p) * 2 + 1);
   const float fx0 = floorf(x), fy0 = floorf(y);
   const float dx = x - fx0, dy = y - fy0;
-  const int bx = (int)fx0 - R, by = (int)fy0 - R;
+  const int bx = window_base(fx0, R), by = window_base(fy0, R);
   const float wnw = dy * dx, wne = dy * (1.0f - dx), wsw = (1.0f - dy) * dx, wse = (1.0f - dy) * (1.0f - dx);
 
   float acc[RD][RD];   // [iy][ix]
@@ -93,7 +99,7 @@ k_altcorr_bwd(const float* __restrict__ f1, const float* __restrict__ f2,
       const float y = __ldg(coords + (bs * HW1 + p) * 2 + 1);
       const float fx0 = floorf(x), fy0 = floorf(y);
       const float dx = x - fx0, dy = y - fy0;
-      const int bx = (int)fx0 - r, by = (int)fy0 - r;
+      const int bx = window_base(fx0, r), by = window_base(fy0, r);
       const float* g0 = cg + bs * rd * rd * HW1 + p;
       for (int iy = 0; iy <= rd; ++iy)
         for (int ix = 0; ix <= rd; ++ix) {
@@ -128,7 +134,7 @@ k_altcorr_fwd_any(const float* __restrict__ f1, const float* __restrict__ f2,
   const float y = __ldg(coords + ((size_t)bs * HW1 + p) * 2 + 1);
   const float fx0 = floorf(x), fy0 = floorf(y);
   const float dx = x - fx0, dy = y - fy0;
-  const int bx = (int)fx0 - r, by = (int)fy0 - r;
+  const int bx = window_base(fx0, r), by = window_base(fy0, r);
   float* o = corr + (size_t)bs * rd * rd * HW1 + p;
   for (int c = 0; c < rd * rd; ++c) o[(size_t)c * HW1] = 0.f;
   const float* f1p = f1 + ((size_t)b * HW1 + p) * C;

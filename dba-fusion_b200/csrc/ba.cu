@@ -19,7 +19,7 @@ namespace {
 
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
-constexpr int kSmemSolveMaxN = 160;   // 160*161*8 B = 206 KB of shared memory
+constexpr int kSmemSolveMaxN = 160;   // (161*160 + 160)*8 B = 207 KB of shared memory
 
 inline int64_t align_up(int64_t x, int64_t a) { return (x + a - 1) / a * a; }
 
@@ -769,11 +769,8 @@ extern "C" int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep
   if (n == 0) return DBAF_OK;
   const int use_smem = n <= kSmemSolveMaxN;
   const size_t smem = use_smem ? ((size_t)(n + 1) * n + n) * sizeof(double) : 0;
-  static bool attr_set = false;
-  if (!attr_set) {
-    DBAF_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    attr_set = true;
-  }
+  // static shared memory of the kernel counts against the 227 KB opt-in limit
+  DBAF_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
   k_solve<<<1, kThreads, smem, (cudaStream_t)stream>>>(n, lm, ep, prior, prior_rows, prior_cols, use_smem, ws);
   DBAF_LAUNCH_CHECK("k_solve");
   return DBAF_OK;

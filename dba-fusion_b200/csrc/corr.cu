@@ -27,6 +27,14 @@ struct LevelPtrs {
 __device__ __forceinline__ float h2f(unsigned short b) { return __half2float(__ushort_as_half(b)); }
 __device__ __forceinline__ float round_h(float x) { return __half2float(__float2half_rn(x)); }
 
+// floor(x) as an int the way the reference converts it (saturating, NaN -> 0), then clamped to
+// +-2^24 so that the window arithmetic below can never overflow.  Any base beyond the clamp is
+// out of bounds for every tap either way, so results are unchanged.
+__device__ __forceinline__ int window_base(float floored, int r) {
+  const int v = (int)floored;
+  return max(-(1 << 24), min(1 << 24, v)) - r;
+}
+
 __device__ __forceinline__ unsigned long long funnel64(unsigned long long lo, unsigned long long hi, int sh) {
   return sh ? (lo >> sh) | (hi << (64 - sh)) : lo;
 }
@@ -82,7 +90,7 @@ k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, in
   const float y0 = __ldg(coords + ((size_t)e * 2 + 1) * HW1 + p) * scale;
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int bx = (int)fx0 - R, by = (int)fy0 - R;   // saturating conversions, like the reference
+  const int bx = window_base(fx0, R), by = window_base(fy0, R);
 
   float acc[RD][RD];
 #pragma unroll
@@ -173,7 +181,7 @@ k_corr_lookup_any(const T* __restrict__ vol, const float* __restrict__ coords, i
   const float y0 = __ldg(coords + ((size_t)e * 2 + 1) * HW1 + p);
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int bx = (int)fx0 - r, by = (int)fy0 - r;
+  const int bx = window_base(fx0, r), by = window_base(fy0, r);
   const bool half = sizeof(T) == 2;
   float w11 = dx * dy, w10 = dx * (1.0f - dy), w01 = (1.0f - dx) * dy, w00 = (1.0f - dx) * (1.0f - dy);
   if (half) { w11 = round_h(w11); w10 = round_h(w10); w01 = round_h(w01); w00 = round_h(w00); }
@@ -211,7 +219,7 @@ k_corr_lookup_bwd(const float* __restrict__ coords, const T* __restrict__ cg, in
   const float y0 = __ldg(coords + ((size_t)e * 2 + 1) * HW1 + p);
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int bx = (int)fx0 - r, by = (int)fy0 - r;
+  const int bx = window_base(fx0, r), by = window_base(fy0, r);
   const bool half = sizeof(T) == 2;
   float w11 = dx * dy, w10 = dx * (1.0f - dy), w01 = (1.0f - dx) * dy, w00 = (1.0f - dx) * (1.0f - dy);
   if (half) { w11 = round_h(w11); w10 = round_h(w10); w01 = round_h(w01); w00 = round_h(w00); }

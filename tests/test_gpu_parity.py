@@ -95,7 +95,8 @@ def test_bacore_hessian_vs_oracle(dev, db, oracle, synth, cfg, kw):
     oc.hessian(Ho, vo)
     assert relerr(H.numpy(), Ho) < TOL, relerr(H.numpy(), Ho)
     assert relerr(v.numpy(), vo) < TOL, relerr(v.numpy(), vo)
-    assert np.abs(H.numpy() - H.numpy().T).max() <= 1e-9 * np.abs(Ho).max()
+    # S_kk blocks are accumulated as (E q) E^T in float32, like EEt6x6_kernel: symmetric to rounding only
+    assert np.abs(H.numpy() - H.numpy().T).max() <= 1e-6 * np.abs(Ho).max()
     # E, Q, w kept for the back-substitution
     W = core._w
     K = len(oc.tab["kx"])
@@ -304,25 +305,30 @@ def test_lookup_fp32_generic_radius_and_backward(dev, db, oracle):
 @pytest.mark.parametrize("cfg,n", [("tiny", 3), ("c2", 2), ("c2_real", 2), ("c3", 2)])
 def test_volume_pyramid_vs_torch_reference(dev, db, synth, cfg, n):
     """Against the reference's own code path: torch.matmul (cuBLAS fp16, fp32 accumulate) followed
-    by 3x avg_pool2d (dbaf/modules/corr.py:30-38,63-71).  One fp16 ulp on level 0 (different
-    summation order inside the tensor cores), then the pooling of possibly-flipped values."""
+    by 3x avg_pool2d (dbaf/modules/corr.py:30-38,63-71).
+
+    Stated tolerance (measured with scripts/volume_ulp_study.py on the B200: cuBLAS itself is up to
+    ~5 fp16 ulp away from the exactly rounded product where the 128-term sum cancels, because the
+    fp32 accumulation error scales with sum|a||b|, not with the result):
+        |ours - cuBLAS| <= (l+1) * 2^-10 * |cuBLAS| + 8e-6
+    i.e. one fp16 rounding per pyramid level plus the fp32 accumulation-order noise, and our error
+    against the float64 product is never worse than cuBLAS's by more than that."""
     f1, f2, _ = _corr_case(synth, cfg, n)
     a, b = torch.from_numpy(f1).to(dev), torch.from_numpy(f2).to(dev)
     pyr = db.corr_volume_pyramid(a, b, 4)
     nn, C, ht, wd = a.shape
     corr = torch.matmul((a.reshape(nn, C, -1) / 4.0).transpose(1, 2), b.reshape(nn, C, -1) / 4.0)
     corr = corr.reshape(nn * ht * wd, 1, ht, wd)
-    exact = torch.matmul((a.float().reshape(nn, C, -1) / 4.0).transpose(1, 2), b.float().reshape(nn, C, -1) / 4.0)
+    exact = torch.matmul((a.double().reshape(nn, C, -1) / 4.0).transpose(1, 2), b.double().reshape(nn, C, -1) / 4.0)
     exact = exact.reshape(nn * ht * wd, 1, ht, wd)
     for l in range(4):
         want = corr.view(nn, ht, wd, ht >> l, wd >> l).float()
         got = pyr[l].float()
         assert got.shape == want.shape
-        ulp = torch.maximum(want.abs(), torch.tensor(2.0 ** -14, device=dev)) * 2.0 ** -10
-        assert torch.all((got - want).abs() <= 1.01 * ulp * (l + 1)), (cfg, l, (got - want).abs().max().item())
-        # and never further from the fp32 truth than the reference is (+ half an ulp)
+        tol = (l + 1) * 2.0 ** -10 * want.abs() + 8e-6
+        assert torch.all((got - want).abs() <= tol), (cfg, l, (got - want).abs().max().item())
         ex = exact.view(nn, ht, wd, ht >> l, wd >> l)
-        assert (got - ex).abs().max() <= (want - ex).abs().max() + (ulp.max() * (l + 1))
+        assert (got.double() - ex).abs().max() <= (want.double() - ex).abs().max() + tol.max()
         corr = torch.nn.functional.avg_pool2d(corr, 2, stride=2)
         exact = torch.nn.functional.avg_pool2d(exact, 2, stride=2)
 

@@ -47,6 +47,13 @@ def test_bacore_hessian_and_retract(dev, db, ref, synth, cfg, kw):
 @pytest.mark.parametrize("motion_only", [False, True])
 def test_ba(dev, db, ref, oracle, synth, cfg, kw, motion_only):
     w = synth.make_window(cfg, **kw)
+    if motion_only:
+        # The reference aborts the process (Eigen assertion in SparseMatrix::diagonal(), reached from
+        # SparseBlock::solve, src/droid_kernels.cu:1253) when a window pose has no edge at all in
+        # motion-only mode; ours returns dx = 0 for such a pose (covered in test_gpu_parity).
+        touched = set(w["ii"].tolist()) | set(w["jj"].tolist())
+        if not all(f in touched for f in range(w["t0"], w["t1"])):
+            pytest.skip("window has an isolated pose: the reference aborts on it in motion-only mode")
     res = []
     for mod in (db, ref):
         t = to_torch(w, dev)
