@@ -823,3 +823,93 @@ extern "C" int dbaf_ba(void* workspace, float* poses, float* disps, const float*
   }
   return DBAF_OK;
 }
+
+// ------------------------------------------------------- allocation-free graph tables ----
+//
+// dbaf_ba_tables_noalloc: the graph bookkeeping kernel (k_tables) for hosts that must not
+// allocate device memory around the call.  Two kinds of caller are in that position: a
+// real-time tracking thread that has handed its whole memory budget out at start-up and may not
+// touch an allocator afterwards (cudaMalloc takes a driver lock and synchronises the whole
+// device, which stalls the camera pipeline running next to it), and a plugin whose host
+// application owns every buffer and only passes pointers in.  Such a caller brings the inputs
+// (ii, jj) and the outputs; the intermediate tables the kernel needs live in the fixed array
+// below, which is part of the library image: every GPU that loads libdbaf_b200.so holds these
+// 1.5 MiB until the process exits.
+//
+// Limits (checked, DBAF_EINVAL with a message otherwise): n_frames <= 16384, n_edges <= 262144.
+//
+// The first call on each device looks up the device address of the array
+// (cudaGetSymbolAddress, a host-side set-up step, not an allocation).  Make that first call
+// before starting any stream capture.  All calls on one device share the array and it keeps
+// whatever the previous call left in it; the kernel re-initialises every word it later reads,
+// so stale contents are harmless, but two calls that overlap on the GPU (different streams)
+// race on it -- serialise them.
+namespace dbaf {
+namespace {
+
+constexpr int kNoAllocMaxFrames = 16384;
+constexpr int kNoAllocMaxEdges = 262144;
+// frame2k[N] + cursor[N+1] + srow_ptr[N+1] + srow_idx[N+E] int32, rounded up
+constexpr size_t kNoAllocScratchBytes = 1536 * 1024;
+static_assert(4ull * (4ull * kNoAllocMaxFrames + kNoAllocMaxEdges + 2) + 3 * 256 <= kNoAllocScratchBytes,
+              "static scratch too small for the advertised limits");
+
+static __device__ __align__(256) unsigned char g_tables_scratch[kNoAllocScratchBytes];
+
+constexpr int kMaxDevices = 64;
+unsigned char* g_tables_scratch_addr[kMaxDevices] = {};   // device address per device, filled on first use
+
+// The array's name is only a host-side handle here; the kernel needs the address the symbol has
+// on the device that is current right now.
+int tables_scratch_for_current_device(unsigned char** out) {
+  int dev = 0;
+  DBAF_CUDA(cudaGetDevice(&dev));
+  DBAF_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
+  if (g_tables_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    DBAF_CUDA(cudaGetSymbolAddress(&p, g_tables_scratch));
+    DBAF_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
+    g_tables_scratch_addr[dev] = static_cast<unsigned char*>(p);
+  }
+  *out = g_tables_scratch_addr[dev];
+  return DBAF_OK;
+}
+
+}  // namespace
+}  // namespace dbaf
+
+extern "C" int dbaf_ba_tables_noalloc(const int64_t* ii, const int64_t* jj, int n_edges, int n_frames,
+                                      int t0, int t1, int32_t* info, int32_t* kx, int32_t* kk_exp,
+                                      int32_t* csr_ptr, int32_t* csr_idx, void* stream) {
+  if (int rc = check_dims(n_frames, n_edges, t0, t1, 1, 1)) return rc;
+  DBAF_REQUIRE(n_frames <= kNoAllocMaxFrames,
+               "n_frames exceeds the 16384-frame limit of the allocation-free entry point");
+  DBAF_REQUIRE(n_edges <= kNoAllocMaxEdges,
+               "n_edges exceeds the 262144-edge limit of the allocation-free entry point");
+  DBAF_REQUIRE(info && kx && kk_exp && csr_ptr && (csr_idx || n_edges == 0), "null output pointer");
+  unsigned char* scratch = nullptr;
+  if (int rc = tables_scratch_for_current_device(&scratch)) return rc;
+  const int P = t1 - t0;
+  const int Kcap = std::min(n_frames, P + n_edges);
+  auto carve = [&](size_t count) {
+    unsigned char* p = scratch;
+    scratch += align_up((int64_t)count * 4, 256);
+    return reinterpret_cast<int*>(p);
+  };
+  Ws ws{};
+  ws.info = info;
+  ws.kx = kx;
+  ws.kk_exp = kk_exp;
+  ws.csr_ptr = csr_ptr;
+  ws.csr_idx = csr_idx;
+  ws.frame2k = carve(n_frames);
+  ws.cursor = carve(Kcap + 1);
+  ws.srow_ptr = carve(Kcap + 1);
+  ws.srow_idx = carve(P + n_edges);
+  ws.Kcap = Kcap;
+  // k_tables writes every table word before reading it (flags, counters and cursors are reset at
+  // the top of the kernel), so nothing from an earlier call can leak into this one.
+  k_tables<<<1, 1024, 0, (cudaStream_t)stream>>>(ii, jj, n_edges, n_frames, t0, t1, ws);
+  DBAF_LAUNCH_CHECK("k_tables (noalloc)");
+  return DBAF_OK;
+}

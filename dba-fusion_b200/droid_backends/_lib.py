@@ -43,6 +43,7 @@ SIGNATURES = {
                                          ctypes.POINTER(c_void_p), P, c_size_t, P]),
     "dbaf_ba_workspace_layout": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(BaLayout)]),
     "dbaf_ba_prepare": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P]),
+    "dbaf_ba_tables_noalloc": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P, P, P]),
     "dbaf_ba_linearize": (c_int, [P, P, P, P, P, P, P, P, c_int, P, P, c_int, c_int, c_int, c_int, c_int,
                                   c_int, c_float, c_int, c_int, c_int, c_int, P]),
     "dbaf_ba_solve": (c_int, [P, c_int, c_int, c_float, c_float, P, c_int, c_int, P]),

@@ -142,6 +142,22 @@ int dbaf_ba_workspace_layout(int n_frames, int n_edges, int t0, int t1, int ht, 
 int dbaf_ba_prepare(void* workspace, const int64_t* ii, const int64_t* jj, int n_edges,
                     int n_frames, int t0, int t1, int ht, int wd, void* stream);
 
+/* No counterpart in the reference.  The same graph tables as dbaf_ba_prepare, for callers that may
+ * not allocate device memory around the call (a real-time tracking thread whose memory budget was
+ * handed out at start-up -- cudaMalloc locks the driver and synchronises the device -- or a plugin
+ * whose host application owns every buffer).  The caller passes inputs and outputs only:
+ *   info int32[16], kx int32[min(N,P+E)], kk_exp int32[P+E], csr_ptr int32[min(N,P+E)+1],
+ *   csr_idx int32[E]      (P = t1-t0, meanings as in dbaf_ba_layout).
+ * Intermediate tables live in a 1.5 MiB array inside the library image (held by every GPU that loads
+ * the library, until exit).  Limits: n_frames <= 16384, n_edges <= 262144, else DBAF_EINVAL.
+ * The first call on a device resolves that array's device address (host-side set-up, no
+ * allocation): make it before any stream capture.  Calls on one device share the array, which
+ * keeps the previous call's contents (the kernel resets all it reads); calls that overlap on the
+ * GPU race on it, so keep them in one stream or otherwise serialised. */
+int dbaf_ba_tables_noalloc(const int64_t* ii, const int64_t* jj, int n_edges, int n_frames,
+                           int t0, int t1, int32_t* info, int32_t* kx, int32_t* kk_exp,
+                           int32_t* csr_ptr, int32_t* csr_idx, void* stream);
+
 /* One linearisation: projective_transform_kernel + SparseBlock assembly + accum_cuda + schur_block,
  * src/droid_kernels.cu:220-468,1162-1222,993-1043,1297-1391.  Zeroes H/v first when `zero_first`,
  * then adds this call's edges: A - S into H, b_A - b_S into v (undamped, float64), and stores
