@@ -472,13 +472,14 @@ k_linearize(const float* __restrict__ poses, const float* __restrict__ disps,
 // and accumulates the 6x6 block  sum_px E_a Q E_b^T  (plus E_a Q w on the diagonal pairs),
 // then subtracts it from H (both triangles) / v.
 __global__ void __launch_bounds__(kThreads)
-k_schur(const int64_t* __restrict__ jj, int t0, int P, int HW, int tile_px, int k_lo, int k_hi, Ws ws) {
+k_schur(const int64_t* __restrict__ jj, int t0, int P, int HW, int tile_px, int min_rows, int k_lo, int k_hi, Ws ws) {
   const int k = k_lo + blockIdx.y;
   const int K = ws.info[0];
   if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
   const int r_lo = ws.srow_ptr[k];
   const int m = ws.srow_ptr[k + 1] - r_lo;
+  if (m < min_rows) return;
   const int pairs = m * (m + 1) / 2;
   const int p_lo = blockIdx.x * tile_px, p_hi = min(HW, p_lo + tile_px);
   const int n6 = 6 * P;
@@ -636,41 +637,7 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
   }
 }
 
-// dz = Q * (w - sum_rows E_row^T dx[pose(row)]) over the rows of depth frame k whose pose index
-// is strictly inside (0, P) -- the reference skips index 0 (src/droid_kernels.cu:1150).
-__global__ void __launch_bounds__(kThreads)
-k_backsub(const int64_t* __restrict__ jj, const float* __restrict__ dx, float* __restrict__ disps,
-          float* __restrict__ dz_out, int t0, int P, int HW, int k_lo, int k_hi, Ws ws) {
-  const int k = k_lo + blockIdx.y;
-  const int K = ws.info[0];
-  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
-  const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= HW) return;
-  const int f = ws.kx[k];
-  float acc = 0.f;
-  const int self = f - t0;
-  if (self > 0 && self < P) {
-    const float* E = ws.Ei + (size_t)self * 6 * HW + p;
-    float s = 0.f;
-#pragma unroll
-    for (int n = 0; n < 6; ++n) s += E[(size_t)n * HW] * __ldg(dx + 6 * self + n);
-    acc += s;
-  }
-  for (int a = ws.csr_ptr[k]; a < ws.csr_ptr[k + 1]; ++a) {
-    const int e = ws.csr_idx[a];
-    const int pj = (int)jj[e] - t0;
-    if (pj > 0 && pj < P) {
-      const float* E = ws.Eij + (size_t)e * 6 * HW + p;
-      float s = 0.f;
-#pragma unroll
-      for (int n = 0; n < 6; ++n) s += E[(size_t)n * HW] * __ldg(dx + 6 * pj + n);
-      acc += s;
-    }
-  }
-  const float dz = ws.Q[(size_t)k * HW + p] * (ws.w[(size_t)k * HW + p] - acc);
-  if (dz_out) dz_out[(size_t)k * HW + p] = dz;
-  if (disps) disps[(size_t)f * HW + p] += dz;
-}
+#include "ba_fast.cuh"
 
 int check_dims(int N, int E, int t0, int t1, int ht, int wd) {
   DBAF_REQUIRE(N > 0 && E >= 0 && ht > 0 && wd > 0, "non-positive size");
@@ -749,31 +716,64 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
 #undef DBAF_LIN
   DBAF_LAUNCH_CHECK("k_linearize");
   if (motion_only == 0 && P > 0) {
-    const int tile_px = HW >= 2048 ? 1024 : 256;
-    dim3 sgrid((HW + tile_px - 1) / tile_px, k_cap);
-    k_schur<<<sgrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, k_lo, k_hi, ws);
-    DBAF_LAUNCH_CHECK("k_schur");
+    static bool schur_attr[64] = {};
+    int dev_id = 0;
+    DBAF_CUDA(cudaGetDevice(&dev_id));
+    if (!schur_attr[dev_id & 63]) {   // once per device: the attribute call costs ~10 us of host time
+      DBAF_CUDA(cudaFuncSetAttribute(k_schur_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
+      schur_attr[dev_id & 63] = true;
+    }
+    const int S = 256;
+    dim3 sgrid((HW + S - 1) / S, k_cap);
+    k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_schur_smem");
+    if (E + 1 > kSchurMaxRows) {
+      // a depth frame can only have more than kSchurMaxRows rows if the graph has that many edges
+      const int tile_px = 1024;
+      dim3 ogrid((HW + tile_px - 1) / tile_px, k_cap);
+      k_schur<<<ogrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, kSchurMaxRows + 1, k_lo, k_hi, ws);
+      DBAF_LAUNCH_CHECK("k_schur");
+    }
   }
   return DBAF_OK;
 }
+
+namespace {
+int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const double* prior, int prior_rows,
+                 int prior_cols, int rezero, cudaStream_t st) {
+  // Only info, H, v, dx and Lfac are touched; their offsets depend on P alone.
+  dbaf_ba_layout L;
+  fill_layout(1, 0, 0, t1 - t0, 1, 1, &L);
+  Ws ws = view(workspace, L);
+  const int P = t1 - t0, n = 6 * P;
+  if (n == 0) return DBAF_OK;
+  if (n <= kSmemSolveMaxN) {
+    const int ld = n | 1;
+    const size_t smem = ((size_t)(n + 1) * ld + 2 * n) * sizeof(double);
+    // static shared memory of the kernel counts against the 227 KB opt-in limit
+    static bool solve_attr[64] = {};
+    int dev_id = 0;
+    DBAF_CUDA(cudaGetDevice(&dev_id));
+    if (!solve_attr[dev_id & 63]) {
+      DBAF_CUDA(cudaFuncSetAttribute(k_solve6, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+      solve_attr[dev_id & 63] = true;
+    }
+    k_solve6<<<1, kThreads, smem, st>>>(P, lm, ep, prior, prior_rows, prior_cols, rezero, ws);
+    DBAF_LAUNCH_CHECK("k_solve6");
+  } else {
+    k_solve<<<1, kThreads, 0, st>>>(n, lm, ep, prior, prior_rows, prior_cols, 0, ws);
+    DBAF_LAUNCH_CHECK("k_solve");
+    if (rezero) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, ((size_t)n * n + n) * 8, st));
+  }
+  return DBAF_OK;
+}
+}  // namespace
 
 extern "C" int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep, const double* prior,
                              int prior_rows, int prior_cols, void* stream) {
   DBAF_REQUIRE(workspace != nullptr, "null workspace");
   DBAF_REQUIRE(t1 >= t0, "t1 < t0");
-  // Only H, v, dx, info and Lfac are touched; their offsets depend on P alone.
-  dbaf_ba_layout L;
-  fill_layout(1, 0, 0, t1 - t0, 1, 1, &L);
-  Ws ws = view(workspace, L);
-  const int n = 6 * (t1 - t0);
-  if (n == 0) return DBAF_OK;
-  const int use_smem = n <= kSmemSolveMaxN;
-  const size_t smem = use_smem ? ((size_t)(n + 1) * n + n) * sizeof(double) : 0;
-  // static shared memory of the kernel counts against the 227 KB opt-in limit
-  DBAF_CUDA(cudaFuncSetAttribute(k_solve, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
-  k_solve<<<1, kThreads, smem, (cudaStream_t)stream>>>(n, lm, ep, prior, prior_rows, prior_cols, use_smem, ws);
-  DBAF_LAUNCH_CHECK("k_solve");
-  return DBAF_OK;
+  return launch_solve(workspace, t0, t1, lm, ep, prior, prior_rows, prior_cols, 0, (cudaStream_t)stream);
 }
 
 extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,
@@ -791,12 +791,14 @@ extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, cons
   const float* dx = dx_in ? dx_in : ws.dx;
   if (k_lo < 0) k_lo = 0;
   const int k_cap = (k_hi >= 0 ? std::min(k_hi, ws.Kcap) : ws.Kcap) - k_lo;
+  const bool pose_work = P > 0 && (update_poses || dx_out);
   if (update_disps && k_cap > 0) {
     dim3 grid((HW + kThreads - 1) / kThreads, k_cap);
-    k_backsub<<<grid, kThreads, 0, st>>>(jj, dx, disps, dz_out, t0, P, HW, k_lo, k_hi, ws);
-    DBAF_LAUNCH_CHECK("k_backsub");
-  }
-  if (P > 0 && (update_poses || dx_out)) {
+    k_backsub_fused<<<grid, kThreads, 0, st>>>(jj, dx, disps, dz_out, update_poses ? poses : nullptr,
+                                               pose_work ? dx_out : nullptr, t0, P, pose_work ? P : 0, HW,
+                                               k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_backsub_fused");
+  } else if (pose_work) {
     k_pose_retract<<<1, 128, 0, st>>>(update_poses ? poses : nullptr, dx, t0, P, dx_out);
     DBAF_LAUNCH_CHECK("k_pose_retract");
   }
@@ -812,9 +814,9 @@ extern "C" int dbaf_ba(void* workspace, float* poses, float* disps, const float*
   for (int it = 0; it < iterations; ++it) {
     if (int rc = dbaf_ba_linearize(workspace, poses, disps, intrinsics, disps_sens, targets, weights,
                                    eta, eta_rows, ii, jj, E, N, t0, t1, ht, wd, 0.05f, motion_only,
-                                   1, 0, -1, stream))
+                                   it == 0 ? 1 : 0, 0, -1, stream))
       return rc;
-    if (int rc = dbaf_ba_solve(workspace, t0, t1, lm, ep, nullptr, 0, 0, stream)) return rc;
+    if (int rc = launch_solve(workspace, t0, t1, lm, ep, nullptr, 0, 0, it + 1 < iterations, (cudaStream_t)stream)) return rc;
     const bool last = it == iterations - 1;
     if (int rc = dbaf_ba_retract(workspace, poses, disps, nullptr, ii, jj, E, N, t0, t1, ht, wd, 1,
                                  motion_only ? 0 : 1, 0, -1, last ? dx_out : nullptr,

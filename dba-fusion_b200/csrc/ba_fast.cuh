@@ -1,0 +1,365 @@
+// Second-generation BA kernels, included by ba.cu inside namespace dbaf::{anonymous} after `Ws`:
+//   k_schur_smem   Schur complement with the frame's slab tile staged in shared memory
+//   k_solve6       blocked (6x6) float64 Cholesky + substitutions in shared memory, one CTA
+//   k_backsub_fused depth back-substitution + disparity update + pose retraction in one launch
+#pragma once
+
+// ------------------------------------------------------------------ Schur ----
+// One CTA = depth frame k x S pixels.  The (6 m_k) x tp tile of E rows plus Q and w is loaded once
+// per pass with coalesced reads (every thread has many independent loads in flight), then each
+// warp owns row pairs (a >= b) and accumulates  sum_px (E_a Q) E_b^T  from shared memory.  The
+// tile width tp adapts to the number of rows so that the staging buffer is a fixed 72 KB (three
+// CTAs per SM): tp = 256 up to 12 rows, 128 up to 24, ... 32 up to 96 rows; frames with more rows
+// are left to k_schur.  The reference launches one CTA per 6x6 block and re-reads both rows from
+// global memory for each of the m_k^2 blocks (EEt6x6_kernel, src/droid_kernels.cu:1046-1101).
+// 4-byte cp.async (LDGSTS); `ok == false` zero-fills the destination without touching memory
+__device__ __forceinline__ void cp_async_f32(float* smem_dst, const float* gmem_src, bool ok) {
+  const unsigned dst = (unsigned)__cvta_generic_to_shared(smem_dst);
+  const int bytes = ok ? 4 : 0;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;\n" ::"r"(dst), "l"(gmem_src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;\n" ::: "memory");
+  asm volatile("cp.async.wait_group 0;\n" ::: "memory");
+}
+
+constexpr int kSchurCapFloats = 18432;   // 6 rows * 12 * 256
+constexpr int kSchurMaxRows = kSchurCapFloats / (6 * 32);
+constexpr size_t kSchurSmemBytes = (size_t)(kSchurCapFloats + 2 * 256) * 4 + 2 * kSchurMaxRows * 4;
+
+__global__ void __launch_bounds__(kThreads)
+k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k_lo, int k_hi, Ws ws) {
+  extern __shared__ float smf[];
+  const int k = k_lo + blockIdx.y;
+  const int K = ws.info[0];
+  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const int r_lo = ws.srow_ptr[k];
+  const int m = ws.srow_ptr[k + 1] - r_lo;
+  if (m == 0 || m > kSchurMaxRows) return;
+  const int rows6 = 6 * m;
+  const int tp = min(256, (kSchurCapFloats / rows6) & ~31);
+  float* Es = smf;                                // [rows6][tp]
+  float* Qs = smf + kSchurCapFloats;              // [256]
+  float* Wsm = Qs + 256;                          // [256]
+  int* rown = reinterpret_cast<int*>(Wsm + 256);  // [m] row ids
+  int* rowp = rown + kSchurMaxRows;               // [m] pose index of each row
+  for (int a = tid; a < m; a += kThreads) {
+    const int n = ws.srow_idx[r_lo + a];
+    rown[a] = n;
+    rowp[a] = n < P ? n : (int)jj[n - P] - t0;
+  }
+  const int pairs = m * (m + 1) / 2;
+  const int n6 = 6 * P;
+  const int s_lo = blockIdx.x * S, s_hi = min(HW, s_lo + S);
+  for (int p0 = s_lo; p0 < s_hi; p0 += tp) {
+    const int np = min(tp, s_hi - p0);
+    __syncthreads();                               // previous pass done with the tile; rown/rowp visible
+    if (tid < tp) {
+      // asynchronous global->shared copies: all 6m+2 loads of a thread are in flight at once
+      const bool ok = tid < np;
+      const int off = ok ? tid : 0;
+      cp_async_f32(Qs + tid, ws.Q + (size_t)k * HW + p0 + off, ok);
+      cp_async_f32(Wsm + tid, ws.w + (size_t)k * HW + p0 + off, ok);
+      for (int a = 0; a < m; ++a) {
+        const int n = rown[a];
+        const float* src = (n < P ? ws.Ei + (size_t)n * 6 * HW : ws.Eij + (size_t)(n - P) * 6 * HW) + p0 + off;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) cp_async_f32(Es + (6 * a + c) * tp + tid, src + (size_t)c * HW, ok);
+      }
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    for (int q = wid; q < pairs; q += kWarps) {
+      int a, b;
+      tri_unpack(q, a, b);
+      const bool diag = a == b;
+      const float* Ea = Es + 6 * a * tp;
+      const float* Eb = Es + 6 * b * tp;
+      float acc[64];
+#pragma unroll
+      for (int l = 0; l < 64; ++l) acc[l] = 0.f;
+#pragma unroll 2
+      for (int px = lane; px < tp; px += 32) {
+        const float qv = Qs[px];
+        float ea[6], eb[6];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          ea[c] = Ea[c * tp + px] * qv;
+          eb[c] = Eb[c * tp + px];
+        }
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+#pragma unroll
+          for (int c = 0; c < 6; ++c) acc[r * 6 + c] += ea[r] * eb[c];
+        if (diag) {
+          const float wv = Wsm[px];
+#pragma unroll
+          for (int r = 0; r < 6; ++r) acc[36 + r] += ea[r] * wv;
+        }
+      }
+      warp_reduce32(acc, lane);
+      warp_reduce32(acc + 32, lane);
+      const int pa = rowp[a], pb = rowp[b];
+      {
+        const int r = lane / 6, c = lane % 6;
+        const double val = -(double)acc[0];
+        atomicAdd(ws.H + (size_t)(6 * pa + r) * n6 + 6 * pb + c, val);
+        if (!diag) atomicAdd(ws.H + (size_t)(6 * pb + c) * n6 + 6 * pa + r, val);
+      }
+      if (lane < 4) {
+        const int l = 32 + lane;
+        const int r = l / 6, c = l % 6;
+        const double val = -(double)acc[32];
+        atomicAdd(ws.H + (size_t)(6 * pa + r) * n6 + 6 * pb + c, val);
+        if (!diag) atomicAdd(ws.H + (size_t)(6 * pb + c) * n6 + 6 * pa + r, val);
+      } else if (diag && lane < 10) {
+        atomicAdd(ws.v + 6 * pa + (lane - 4), -(double)acc[32]);
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------ solve ----
+// Blocked right-looking Cholesky on 6x6 pose blocks, matrix (plus the right-hand side as an extra
+// row, so the forward substitution falls out of the factorisation) resident in shared memory.
+// P block steps with 3 barriers each instead of 6P column steps with 4.
+// Layout: L[(n+1)][ld], lower triangle used; dinv[n] = 1 / L[c][c].
+__device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* dinv, int* fail) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int n = 6 * P;
+  if (tid == 0) *fail = 0;
+  __syncthreads();
+  for (int J = 0; J < P; ++J) {
+    const int j0 = 6 * J;
+    // (1) factor the 6x6 diagonal block (one thread; 56 flops)
+    if (tid == 0) {
+      // whole lower triangle into registers first (21 independent loads), then a fully
+      // unrolled in-register factorisation: the only serial chain left is 6 x (rsqrt + a few FMAs)
+      double a[6][6];
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+          if (c <= r) a[r][c] = L[(size_t)(j0 + r) * ld + j0 + c];
+      bool bad = false;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        double d = a[c][c];
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk)
+          if (kk < c) d -= a[c][kk] * a[c][kk];
+        if (d <= 0.0) { bad = true; d = 1.0; }
+        const double inv = rsqrt(d);
+        a[c][c] = d * inv;
+        dinv[j0 + c] = inv;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          if (r > c) {
+            double s = a[r][c];
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk)
+              if (kk < c) s -= a[r][kk] * a[c][kk];
+            a[r][c] = s * inv;
+          }
+        }
+      }
+      if (bad) *fail = 1;
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+          if (c <= r) L[(size_t)(j0 + r) * ld + j0 + c] = a[r][c];
+    }
+    __syncthreads();
+    if (*fail) return false;
+    // (2) panel below the block (rows j0+6 .. n, row n = rhs): X L_JJ^T = A
+    for (int r = j0 + 6 + tid; r <= n; r += nt) {
+      double row[6];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        double a = L[(size_t)r * ld + j0 + c];
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk)
+          if (kk < c) a -= row[kk] * L[(size_t)(j0 + c) * ld + j0 + kk];
+        row[c] = a * dinv[j0 + c];
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) L[(size_t)r * ld + j0 + c] = row[c];
+    }
+    __syncthreads();
+    // (3) trailing update A[r][c] -= sum_k L[r][j0+k] L[c][j0+k] for j0+6 <= c <= min(r, n-1), r <= n
+    const int r0 = j0 + 6;
+    const int mrows = n - r0 + 1;
+    if (mrows > 1) {
+      // 16x16 thread grid over the (rows x cols) triangle: no integer division, the row's six
+      // panel values are loaded once per row and reused along it
+      const int ty = tid >> 4, tx = tid & 15;
+      for (int ro = ty; ro < mrows; ro += (nt >> 4)) {
+        const double* lr = L + (size_t)(r0 + ro) * ld + j0;
+        double a[6];
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk) a[kk] = lr[kk];
+        const int cmax = min(ro, mrows - 2);
+        for (int co = tx; co <= cmax; co += 16) {
+          const double* lc = L + (size_t)(r0 + co) * ld + j0;
+          double s = 0.0;
+#pragma unroll
+          for (int kk = 0; kk < 6; ++kk) s += a[kk] * lc[kk];
+          L[(size_t)(r0 + ro) * ld + r0 + co] -= s;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  // back-substitution L^T x = y, y = row n; block by block from the bottom
+  for (int i = tid; i < n; i += nt) x[i] = L[(size_t)n * ld + i];
+  __syncthreads();
+  for (int J = P - 1; J >= 0; --J) {
+    const int j0 = 6 * J;
+    if (tid == 0) {
+      double a[6][6], xv[6], di[6];
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        xv[r] = x[j0 + r];
+        di[r] = dinv[j0 + r];
+#pragma unroll
+        for (int c = 0; c < 6; ++c)
+          if (c < r) a[r][c] = L[(size_t)(j0 + r) * ld + j0 + c];
+      }
+#pragma unroll
+      for (int c = 5; c >= 0; --c) {
+        double s = xv[c];
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk)
+          if (kk > c) s -= a[kk][c] * xv[kk];
+        xv[c] = s * di[c];
+      }
+#pragma unroll
+      for (int r = 0; r < 6; ++r) x[j0 + r] = xv[r];
+    }
+    __syncthreads();
+    for (int i = tid; i < j0; i += nt) {
+      double s = x[i];
+#pragma unroll
+      for (int c = 0; c < 6; ++c) s -= L[(size_t)(j0 + c) * ld + i] * x[j0 + c];
+      x[i] = s;
+    }
+    __syncthreads();
+  }
+  return true;
+}
+
+// L = H (+ prior), damped; blocked Cholesky in shared memory; dx -> workspace.  With `rezero` the
+// kernel clears H and v afterwards so the next linearisation can accumulate without a memset.
+__global__ void __launch_bounds__(kThreads)
+k_solve6(int P, float lm, float ep, const double* __restrict__ prior, int prior_rows, int prior_cols,
+         int rezero, Ws ws) {
+  extern __shared__ double smd[];
+  __shared__ int fail;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int n = 6 * P;
+  const int ld = n | 1;                                // odd leading dimension: column walks hit different banks
+  double* L = smd;                                     // (n+1) x ld
+  double* x = L + (size_t)(n + 1) * ld;                // n
+  double* dinv = x + n;                                // n
+  for (int i = tid >> 4; i < n; i += (nt >> 4)) {
+    for (int c = tid & 15; c <= i; c += 16) {
+      const size_t t = (size_t)i * n + c;
+      double a = ws.H[t];
+      if (prior) a += (i < prior_rows && c < prior_cols) ? prior[(size_t)i * prior_cols + c] : ws.H[t];
+      if (i == c) a += (double)ep + (double)lm * a;
+      L[(size_t)i * ld + c] = a;
+    }
+  }
+  for (int i = tid; i < n; i += nt) L[(size_t)n * ld + i] = ws.v[i];
+  __syncthreads();
+  const bool ok = cholesky6_solve(L, ld, P, x, dinv, &fail);
+  __syncthreads();
+  for (int i = tid; i < n; i += nt) ws.dx[i] = ok ? (float)x[i] : 0.0f;
+  if (!ok && tid == 0) atomicAdd(&ws.info[1], 1);
+  if (rezero) {
+    for (int t = tid; t < n * n + n; t += nt) ws.H[t] = 0.0;   // v follows H directly
+  }
+}
+
+// ---------------------------------------------------------------- retract ----
+// dz = Q (w - sum_rows E_row^T dx[pose(row)]), disps += dz, and -- in block (0,0) -- the SE3
+// retraction of the window poses and the dx copy-out, so one launch finishes the iteration.
+__global__ void __launch_bounds__(kThreads)
+k_backsub_fused(const int64_t* __restrict__ jj, const float* __restrict__ dx, float* __restrict__ disps,
+                float* __restrict__ dz_out, float* __restrict__ poses, float* __restrict__ dx_out,
+                int t0, int P, int pose_n, int HW, int k_lo, int k_hi, Ws ws) {
+  if (blockIdx.x == 0 && blockIdx.y == 0) {
+    for (int kk = threadIdx.x; kk < pose_n; kk += blockDim.x) {
+      float xi[6], T[7];
+#pragma unroll
+      for (int n = 0; n < 6; ++n) xi[n] = dx[6 * kk + n];
+      if (poses) {
+#pragma unroll
+        for (int n = 0; n < 7; ++n) T[n] = poses[7 * (t0 + kk) + n];
+        retract_pose(xi, T);
+#pragma unroll
+        for (int n = 0; n < 7; ++n) poses[7 * (t0 + kk) + n] = T[n];
+      }
+      if (dx_out) {
+#pragma unroll
+        for (int n = 0; n < 6; ++n) dx_out[6 * kk + n] = xi[n];
+      }
+    }
+  }
+  const int k = k_lo + blockIdx.y;
+  const int K = ws.info[0];
+  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = p < HW;
+  const int f = ws.kx[k];
+  const int self = f - t0;
+  const int e_lo = ws.csr_ptr[k], deg = ws.csr_ptr[k + 1] - e_lo;
+  // The frame's row list (self row + out-edges) is resolved once per CTA into shared memory, so the
+  // per-pixel loop below has no dependent index loads and keeps 6 independent loads per row in flight.
+  constexpr int kChunk = 64;
+  __shared__ const float* s_row[kChunk];
+  __shared__ float s_dx[kChunk][6];
+  const float qv = live ? ws.Q[(size_t)k * HW + p] : 0.f;
+  const float wv = live ? ws.w[(size_t)k * HW + p] : 0.f;
+  float acc = 0.f;
+  for (int base = -1; base < deg; base += kChunk) {     // index -1 is the self row
+    __syncthreads();
+    if (threadIdx.x < kChunk) {
+      const int a = base + (int)threadIdx.x;
+      const float* row = nullptr;
+      int pj = -1;
+      if (a == -1) {
+        if (self > 0 && self < P) { row = ws.Ei + (size_t)self * 6 * HW; pj = self; }
+      } else if (a < deg) {
+        const int e = ws.csr_idx[e_lo + a];
+        const int q = (int)jj[e] - t0;
+        if (q > 0 && q < P) { row = ws.Eij + (size_t)e * 6 * HW; pj = q; }
+      }
+      s_row[threadIdx.x] = row;
+      if (row) {
+#pragma unroll
+        for (int n = 0; n < 6; ++n) s_dx[threadIdx.x][n] = __ldg(dx + 6 * pj + n);
+      }
+    }
+    __syncthreads();
+    const int cnt = min(kChunk, deg - base);
+    if (live) {
+#pragma unroll 4
+      for (int i = 0; i < cnt; ++i) {
+        const float* row = s_row[i];
+        if (row == nullptr) continue;                  // uniform across the CTA
+        float s = 0.f;
+#pragma unroll
+        for (int n = 0; n < 6; ++n) s += row[(size_t)n * HW + p] * s_dx[i][n];
+        acc += s;
+      }
+    }
+  }
+  if (live) {
+    const float dz = qv * (wv - acc);
+    if (dz_out) dz_out[(size_t)k * HW + p] = dz;
+    if (disps) disps[(size_t)f * HW + p] += dz;
+  }
+}

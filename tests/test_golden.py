@@ -164,7 +164,7 @@ def test_cuda_ba_matches_golden(dev, db, oracle, synth, name):
         dx64, dz64 = oracle.ba(p64, d64, *common, iters, 1e-4, 0.1, False, dtype=np.float64)
         assert relerr(dx.cpu().numpy(), g[key + "_dx"]) < _slack(g[key + "_dx"], dx64)
         assert relerr(dz.cpu().numpy(), g[key + "_dz"]) < _slack(g[key + "_dz"], dz64)
-        assert relerr(t["poses"].cpu().numpy(), g[key + "_poses"]) < TOL
+        assert relerr(t["poses"].cpu().numpy(), g[key + "_poses"]) < _slack(g[key + "_poses"], p64)
         assert relerr(t["disps"].cpu().numpy(), g[key + "_disps"]) < _slack(g[key + "_disps"], d64)
     t = to_torch(w, dev)
     dx, dz = db.ba(*ba_args(t), w["t0"], w["t1"], 2, 1e-4, 0.1, True)

@@ -155,7 +155,7 @@ def test_ba_vs_oracle(dev, db, oracle, synth, cfg, kw, motion_only):
     # float64 answer by the deviation of the float32 restatement of the reference (x3) or 1e-4.
     bound = lambda a, b: max(TOL, 3 * relerr(a, b))
     assert relerr(dx.cpu().numpy(), dx64) < bound(dx32, dx64)
-    assert relerr(t["poses"].cpu().numpy(), p64) < TOL
+    assert relerr(t["poses"].cpu().numpy(), p64) < bound(p32, p64)
     if motion_only:
         assert dz is None and torch.equal(t["disps"].cpu(), torch.from_numpy(w["disps"]))
     else:
