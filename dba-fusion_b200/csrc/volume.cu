@@ -16,7 +16,7 @@ namespace dbaf {
 // volume_tc.cu
 int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int wd, int levels,
                    __half* const* out, void* workspace, size_t workspace_bytes, cudaStream_t st,
-                   bool* handled);
+                   int* levels_done);
 size_t corr_volume_tc_workspace(int n, int C, int ht, int wd);
 
 namespace {
@@ -140,15 +140,17 @@ extern "C" int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, in
   // tensor-core path against an independent implementation inside the same library).
   const char* impl = std::getenv("DBAF_VOLUME_IMPL");
   const bool force_simt = impl && std::strcmp(impl, "simt") == 0;
+  int done = 0;
   if (!force_simt) {
-    bool handled = false;
-    const int rc = corr_volume_tc(f1, f2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st, &handled);
+    const int rc = corr_volume_tc(f1, f2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st, &done);
     if (rc != DBAF_OK) return rc;
-    if (handled) return DBAF_OK;
+    if (done >= levels) return DBAF_OK;
   }
-  dim3 grid((HW + kTile - 1) / kTile, (HW + kTile - 1) / kTile, n);
-  k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, C, HW, outs[0]);
-  DBAF_LAUNCH_CHECK("k_volume_simt");
+  if (done == 0) {
+    dim3 grid((HW + kTile - 1) / kTile, (HW + kTile - 1) / kTile, n);
+    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, C, HW, outs[0]);
+    DBAF_LAUNCH_CHECK("k_volume_simt");
+  }
   if (levels > 1) {
     const size_t smem = ((size_t)HW + (size_t)(ht / 2) * (wd / 2) + (size_t)(ht / 4) * (wd / 4)) * 2 + 16;
     DBAF_REQUIRE(smem <= 200 * 1024, "feature map too large for the pyramid kernel");

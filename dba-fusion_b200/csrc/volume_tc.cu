@@ -1,10 +1,438 @@
-// placeholder until the tcgen05 kernel lands
+// All-pairs correlation volume on the 5th-generation tensor cores (tcgen05), sm_100a.
+//
+//   L0[e, p1, p2] = rn16( (1/16) * sum_c f1[e, c, p1] * f2[e, c, p2] )          fp16 in, fp32 accumulate
+//
+// One CTA = one edge x 128 source pixels (UMMA M = 128).  The A tile (128 px x 128 ch, 32 KB) is
+// loaded once by TMA; the CTA then walks the target image in chunks of 256 pixels (UMMA N = 256):
+// TMA brings the B chunk (64 KB) into a single shared-memory buffer, one thread issues 8
+// tcgen05.mma (K = 16 each) into one of two 256-column TMEM accumulator stages, and four epilogue
+// warps drain the other stage (tcgen05.ld, scale, round to fp16, store).  The epilogue is the long
+// pole (the kernel is bound by the HBM write of the volume: 128 FLOP per output byte is below the
+// machine's ~220 FLOP/B ridge), so a single B buffer is enough: it is free again as soon as the MMAs
+// of the chunk have committed, long before the epilogue of that chunk is finished.
+//
+// With 64-pixel-wide frames a 256-pixel chunk is exactly 4 target rows, and the 2x2 / 4x4 / 8x8
+// average-pool pyramid of dbaf/modules/corr.py:35-38 is produced in the same epilogue from registers
+// (level 3 needs 8 rows = two chunks; the level-2 row of the even chunk is carried in registers).
+// The pooled levels are computed from the fp16-rounded level below, in the reference's order
+// ((a+b)+c)+d, *0.25, one rounding), so they are bit-identical to avg_pool2d of our level 0.
+//
+// Operands are K-major (pixel-major, 128 channels contiguous = two 128-byte swizzle rows per pixel);
+// a pre-pass transposes the channel-major feature maps of DepthVideo into that layout once per call.
 #include "common.cuh"
+
+#include <cuda.h>
+
 namespace dbaf {
-size_t corr_volume_tc_workspace(int, int, int, int) { return 256; }
-int corr_volume_tc(const __half*, const __half*, int, int, int, int, int, __half* const*, void*, size_t,
-                   cudaStream_t, bool* handled) {
-  *handled = false;
+namespace {
+
+constexpr int kBM = 128;          // source pixels per CTA (UMMA M)
+constexpr int kBN = 256;          // target pixels per chunk (UMMA N)
+constexpr int kC = 128;           // channels (K)
+constexpr int kKBlock = 64;       // channels per 128-byte swizzle row
+constexpr int kSmemA = kBM * kC * 2;                 // 32 KB
+constexpr int kSmemB = kBN * kC * 2;                 // 64 KB
+constexpr int kSmemBytes = kSmemA + kSmemB + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int kThreadsTc = 256;   // warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7: epilogue
+
+// ------------------------------------------------------------------ PTX wrappers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  while (!done) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 consecutive TMEM columns of this thread's lane -> 32 registers
+__device__ __forceinline__ void tc_ld32(uint32_t taddr, float* v) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// K-major, 128-byte swizzle: 8-row groups 1024 B apart (SBO), version 1 (Blackwell), layout type 2.
+__device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);          // start address, bits [0,14)
+  d |= (uint64_t)1 << 16;                               // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;                     // stride byte offset, bits [32,46)
+  d |= (uint64_t)1 << 46;                               // descriptor version
+  d |= (uint64_t)2 << 61;                               // SWIZZLE_128B
+  return d;
+}
+// kind::f16: D = F32, A = B = F16, both K-major, N = 256, M = 128
+constexpr uint32_t kInstrDesc = (1u << 4) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+
+__device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
+  return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
+}
+__device__ __forceinline__ __half pool_h(__half a, __half b, __half c, __half d) {
+  return __float2half_rn((((__half2float(a) + __half2float(b)) + __half2float(c)) + __half2float(d)) * 0.25f);
+}
+
+struct Pyr {
+  __half* l[4];
+};
+
+// ------------------------------------------------------------------ transpose pre-pass ----
+// [n, C, HW] (channel-major) -> [n, HW, C] (pixel-major): 32 px x 64 ch tiles through shared memory
+__global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW) {
+  __shared__ __half tile[64][33];
+  const int e = blockIdx.z, p0 = blockIdx.x * 32, c0 = blockIdx.y * 64;
+  const __half* s = src + (size_t)e * C * HW;
+  __half* d = dst + (size_t)e * HW * C;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int c = ty; c < 64; c += 8) {
+    const int p = p0 + tx;
+    tile[c][tx] = (p < HW && c0 + c < C) ? s[(size_t)(c0 + c) * HW + p] : __float2half(0.f);
+  }
+  __syncthreads();
+  // each thread writes a pair of channels (4 B) so that a warp writes 128 contiguous bytes of one pixel
+  for (int p = ty; p < 32; p += 8) {
+    if (p0 + p < HW && c0 + 2 * tx + 1 < C) {
+      const uint32_t v = pack_h2(tile[2 * tx][p], tile[2 * tx + 1][p]);
+      *reinterpret_cast<uint32_t*>(d + (size_t)(p0 + p) * C + c0 + 2 * tx) = v;
+    }
+  }
+}
+
+// ------------------------------------------------------------------ main kernel ----
+template <bool FUSE>
+__global__ void __launch_bounds__(kThreadsTc, 1)
+k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+            int HW, int m_tiles, Pyr out) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kSmemA;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA + kSmemB);
+  // bars[0]: A landed, bars[1]: B landed, bars[2]: B buffer free, bars[3..4]: accumulator full,
+  // bars[5..6]: accumulator drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int e = blockIdx.x / m_tiles;
+  const int m0 = (blockIdx.x - e * m_tiles) * kBM;
+  const int n_chunks = (HW + kBN - 1) / kBN;
+
+  if (threadIdx.x == 0) {
+    mbar_init(smem_u32(&bars[0]), 1);
+    mbar_init(smem_u32(&bars[1]), 1);
+    mbar_init(smem_u32(&bars[2]), 1);
+    mbar_init(smem_u32(&bars[3]), 1);
+    mbar_init(smem_u32(&bars[4]), 1);
+    mbar_init(smem_u32(&bars[5]), 4);   // one arrival per epilogue warp
+    mbar_init(smem_u32(&bars[6]), 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(512)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+    // ---------------------------------------------------------------- TMA producer
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+    const uint32_t barA = smem_u32(&bars[0]), barB = smem_u32(&bars[1]), barFree = smem_u32(&bars[2]);
+    mbar_expect_tx(barA, kSmemA);
+    tma_load_2d(smem_u32(sA), &mapA, barA, 0, e * HW + m0);
+    tma_load_2d(smem_u32(sA) + kBM * 128, &mapA, barA, kKBlock, e * HW + m0);
+    for (int c = 0; c < n_chunks; ++c) {
+      mbar_wait(barFree, (c + 1) & 1);
+      mbar_expect_tx(barB, kSmemB);
+      tma_load_2d(smem_u32(sB), &mapB, barB, 0, e * HW + c * kBN);
+      tma_load_2d(smem_u32(sB) + kBN * 128, &mapB, barB, kKBlock, e * HW + c * kBN);
+    }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+    // ---------------------------------------------------------------- MMA issuer
+    const uint32_t barA = smem_u32(&bars[0]), barB = smem_u32(&bars[1]), barFree = smem_u32(&bars[2]);
+    mbar_wait(barA, 0);
+    for (int c = 0; c < n_chunks; ++c) {
+      const int s = c & 1, u = c >> 1;
+      mbar_wait(smem_u32(&bars[5 + s]), (u + 1) & 1);      // epilogue has drained this accumulator stage
+      mbar_wait(barB, c & 1);
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + (uint32_t)(s * kBN);
+#pragma unroll
+      for (int kb = 0; kb < 2; ++kb) {
+#pragma unroll
+        for (int k4 = 0; k4 < 4; ++k4) {
+          const uint64_t ad = umma_desc_k128(smem_u32(sA) + kb * (kBM * 128) + k4 * 32);
+          const uint64_t bd = umma_desc_k128(smem_u32(sB) + kb * (kBN * 128) + k4 * 32);
+          tc_mma_f16(d_tmem, ad, bd, kInstrDesc, (kb | k4) ? 1u : 0u);
+        }
+      }
+      tc_commit(barFree);                 // B buffer may be overwritten once these MMAs are done
+      tc_commit(smem_u32(&bars[3 + s]));  // accumulator stage s is complete
+    }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ---------------------------------------------------------------- epilogue
+    const int q = warp - 4;                           // TMEM lane quarter == warp % 4
+    const int m = m0 + q * 32 + lane;                 // this thread's source pixel
+    const bool mok = m < HW;
+    const size_t row = (size_t)e * HW + (mok ? m : 0);
+    __half* o0 = out.l[0] + row * (size_t)HW;
+    uint32_t carry2[8];                               // level-2 row of the even chunk (FUSE)
+#pragma unroll
+    for (int i = 0; i < 8; ++i) carry2[i] = 0;
+    for (int c = 0; c < n_chunks; ++c) {
+      const int s = c & 1, u = c >> 1;
+      mbar_wait(smem_u32(&bars[3 + s]), u & 1);
+      tc_fence_after();
+      const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * kBN);
+      if constexpr (FUSE) {
+        // chunk = target rows 4c .. 4c+3 of a 64-wide frame
+        uint32_t l1row[2][16];                        // level-1 rows 2c, 2c+1 (32 halves each)
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+#pragma unroll
+          for (int xb = 0; xb < 2; ++xb) {
+            float v0[32], v1[32];
+            tc_ld32(t0 + (uint32_t)((2 * j) * 64 + xb * 32), v0);
+            tc_ld32(t0 + (uint32_t)((2 * j + 1) * 64 + xb * 32), v1);
+            __half h0[32], h1[32];
+#pragma unroll
+            for (int i = 0; i < 32; ++i) {
+              h0[i] = __float2half_rn(v0[i] * 0.0625f);
+              h1[i] = __float2half_rn(v1[i] * 0.0625f);
+            }
+            if (mok) {
+              uint4* d0 = reinterpret_cast<uint4*>(o0 + (size_t)(4 * c + 2 * j) * 64 + xb * 32);
+              uint4* d1 = reinterpret_cast<uint4*>(o0 + (size_t)(4 * c + 2 * j + 1) * 64 + xb * 32);
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                d0[g] = make_uint4(pack_h2(h0[8 * g], h0[8 * g + 1]), pack_h2(h0[8 * g + 2], h0[8 * g + 3]),
+                                   pack_h2(h0[8 * g + 4], h0[8 * g + 5]), pack_h2(h0[8 * g + 6], h0[8 * g + 7]));
+                d1[g] = make_uint4(pack_h2(h1[8 * g], h1[8 * g + 1]), pack_h2(h1[8 * g + 2], h1[8 * g + 3]),
+                                   pack_h2(h1[8 * g + 4], h1[8 * g + 5]), pack_h2(h1[8 * g + 6], h1[8 * g + 7]));
+              }
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const __half a = pool_h(h0[4 * i], h0[4 * i + 1], h1[4 * i], h1[4 * i + 1]);
+              const __half b = pool_h(h0[4 * i + 2], h0[4 * i + 3], h1[4 * i + 2], h1[4 * i + 3]);
+              l1row[j][xb * 8 + i] = pack_h2(a, b);
+            }
+          }
+          if (mok && out.l[1]) {
+            uint4* d = reinterpret_cast<uint4*>(out.l[1] + row * (size_t)(HW / 4) + (size_t)(2 * c + j) * 32);
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+              d[g] = make_uint4(l1row[j][4 * g], l1row[j][4 * g + 1], l1row[j][4 * g + 2], l1row[j][4 * g + 3]);
+          }
+        }
+        // this accumulator stage has been read completely
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars[5 + s]));
+        // level 2: row c (16 values) from level-1 rows 2c, 2c+1
+        uint32_t l2[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t a0 = l1row[0][2 * i], a1 = l1row[0][2 * i + 1];
+          const uint32_t b0 = l1row[1][2 * i], b1 = l1row[1][2 * i + 1];
+          const __half x = pool_h(__ushort_as_half(a0 & 0xffff), __ushort_as_half(a0 >> 16),
+                                  __ushort_as_half(b0 & 0xffff), __ushort_as_half(b0 >> 16));
+          const __half y = pool_h(__ushort_as_half(a1 & 0xffff), __ushort_as_half(a1 >> 16),
+                                  __ushort_as_half(b1 & 0xffff), __ushort_as_half(b1 >> 16));
+          l2[i] = pack_h2(x, y);
+        }
+        if (mok && out.l[2]) {
+          uint4* d = reinterpret_cast<uint4*>(out.l[2] + row * (size_t)(HW / 16) + (size_t)c * 16);
+          d[0] = make_uint4(l2[0], l2[1], l2[2], l2[3]);
+          d[1] = make_uint4(l2[4], l2[5], l2[6], l2[7]);
+        }
+        if ((c & 1) == 0) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) carry2[i] = l2[i];
+        } else if (mok && out.l[3]) {
+          uint32_t l3[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint32_t a0 = carry2[2 * i], a1 = carry2[2 * i + 1];
+            const uint32_t b0 = l2[2 * i], b1 = l2[2 * i + 1];
+            const __half x = pool_h(__ushort_as_half(a0 & 0xffff), __ushort_as_half(a0 >> 16),
+                                    __ushort_as_half(b0 & 0xffff), __ushort_as_half(b0 >> 16));
+            const __half y = pool_h(__ushort_as_half(a1 & 0xffff), __ushort_as_half(a1 >> 16),
+                                    __ushort_as_half(b1 & 0xffff), __ushort_as_half(b1 >> 16));
+            l3[i] = pack_h2(x, y);
+          }
+          *reinterpret_cast<uint4*>(out.l[3] + row * (size_t)(HW / 64) + (size_t)(c >> 1) * 8) =
+              make_uint4(l3[0], l3[1], l3[2], l3[3]);
+        }
+      } else {
+        // generic shapes: level 0 only, 256 consecutive target pixels per chunk
+        const int n0 = c * kBN;
+#pragma unroll 1
+        for (int b = 0; b < kBN / 32; ++b) {
+          float v[32];
+          tc_ld32(t0 + (uint32_t)(b * 32), v);
+          const int nb = n0 + b * 32;
+          if (mok && nb < HW) {
+            __half* d = o0 + nb;
+            const bool vec = (nb + 32 <= HW) && ((reinterpret_cast<uintptr_t>(d) & 15) == 0);
+            if (vec) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g) {
+                uint32_t w[4];
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                  w[t] = pack_h2(__float2half_rn(v[8 * g + 2 * t] * 0.0625f), __float2half_rn(v[8 * g + 2 * t + 1] * 0.0625f));
+                reinterpret_cast<uint4*>(d)[g] = make_uint4(w[0], w[1], w[2], w[3]);
+              }
+            } else {
+#pragma unroll
+              for (int i = 0; i < 32; ++i)
+                if (nb + i < HW) d[i] = __float2half_rn(v[i] * 0.0625f);
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars[5 + s]));
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host side ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  // resolved through the runtime so the library has no link-time dependency on libcuda
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// [rows, 128] fp16 pixel-major matrix, box = 64 channels (128 B, swizzled) x box_rows pixels
+int make_map(CUtensorMap* map, const __half* base, size_t rows, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  DBAF_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t dims[2] = {(cuuint64_t)kC, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)kC * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kKBlock, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DBAF_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed");
   return DBAF_OK;
 }
+
+}  // namespace
+
+size_t corr_volume_tc_workspace(int n, int C, int ht, int wd) {
+  // two pixel-major copies of the feature maps
+  return (size_t)2 * n * ht * wd * C * sizeof(__half) + 512;
+}
+
+int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int wd, int levels,
+                   __half* const* out, void* workspace, size_t workspace_bytes, cudaStream_t st, int* levels_done) {
+  *levels_done = 0;
+  const int HW = ht * wd;
+  if (C != kC) return DBAF_OK;                              // the SIMT kernel takes other channel counts
+  if (workspace == nullptr || workspace_bytes < corr_volume_tc_workspace(n, C, ht, wd)) return DBAF_OK;
+  if ((size_t)n * HW >= (size_t)1 << 31) return DBAF_OK;
+  __half* a_t = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
+  __half* b_t = a_t + (size_t)n * HW * C;
+  dim3 tg((HW + 31) / 32, C / 64, n);
+  k_to_pixel_major<<<tg, 256, 0, st>>>(f1, a_t, C, HW);
+  k_to_pixel_major<<<tg, 256, 0, st>>>(f2, b_t, C, HW);
+  DBAF_LAUNCH_CHECK("k_to_pixel_major");
+  CUtensorMap mapA, mapB;
+  if (int rc = make_map(&mapA, a_t, (size_t)n * HW, kBM)) return rc;
+  if (int rc = make_map(&mapB, b_t, (size_t)n * HW, kBN)) return rc;
+  const bool fuse = wd == 64 && ht % 8 == 0;
+  const int m_tiles = (HW + kBM - 1) / kBM;
+  Pyr pyr;
+  for (int l = 0; l < 4; ++l) pyr.l[l] = (fuse && l < levels) ? out[l] : nullptr;
+  pyr.l[0] = out[0];
+  static bool attr[2] = {false, false};
+  if (!attr[fuse]) {
+    if (fuse) DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
+    attr[fuse] = true;
+  }
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, HW, m_tiles, pyr);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, HW, m_tiles, pyr);
+  DBAF_LAUNCH_CHECK("k_volume_tc");
+  // fused: all requested levels are written; otherwise only level 0 and the caller pools
+  *levels_done = fuse ? levels : 1;
+  return DBAF_OK;
+}
+
 }  // namespace dbaf
