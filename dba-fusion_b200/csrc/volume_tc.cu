@@ -32,7 +32,9 @@ constexpr int kC = 128;           // channels (K)
 constexpr int kKBlock = 64;       // channels per 128-byte swizzle row
 constexpr int kSmemA = kBM * kC * 2;                 // 32 KB
 constexpr int kSmemB = kBN * kC * 2;                 // 64 KB
-constexpr int kSmemBytes = kSmemA + kSmemB + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int kStageWarp = 5 * 4096;                 // per epilogue warp: 4 level-0 boxes + 1 level-1 box, 32 px x 128 B each
+constexpr int kSmemStage = 4 * kStageWarp;           // 80 KB
+constexpr int kSmemBytes = kSmemA + kSmemB + kSmemStage + 1024 /*alignment slack*/ + 256 /*barriers*/;
 constexpr int kThreadsTc = 256;   // warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7: epilogue
 
 // ------------------------------------------------------------------ PTX wrappers ----
@@ -64,6 +66,20 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
+}
+// shared -> global tile store (async proxy); the source box is 32 rows x 128 B, 128-byte swizzled
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(map), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// 16-byte chunk `chunk` (0..7) of row `r` inside a 128-byte-swizzled 32 x 128 B box
+__device__ __forceinline__ uint4* swz(uint8_t* box, int r, int chunk) {
+  return reinterpret_cast<uint4*>(box + r * 128 + ((chunk ^ (r & 7)) << 4));
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -146,12 +162,14 @@ __global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict
 template <bool FUSE>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
+            const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
             int HW, int m_tiles, Pyr out) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = smem + kSmemA;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA + kSmemB);
+  uint8_t* sStage = smem + kSmemA + kSmemB;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA + kSmemB + kSmemStage);
   // bars[0]: A landed, bars[1]: B landed, bars[2]: B buffer free, bars[3..4]: accumulator full,
   // bars[5..6]: accumulator drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
@@ -240,6 +258,9 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * kBN);
       if constexpr (FUSE) {
         // chunk = target rows 4c .. 4c+3 of a 64-wide frame
+        uint8_t* stage = sStage + q * kStageWarp;
+        if (lane == 0) bulk_wait_read0();        // the previous chunk's tiles have left shared memory
+        __syncwarp();
         uint32_t l1row[2][16];                        // level-1 rows 2c, 2c+1 (32 halves each)
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
@@ -254,15 +275,17 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
               h0[i] = __float2half_rn(v0[i] * 0.0625f);
               h1[i] = __float2half_rn(v1[i] * 0.0625f);
             }
-            if (mok) {
-              uint4* d0 = reinterpret_cast<uint4*>(o0 + (size_t)(4 * c + 2 * j) * 64 + xb * 32);
-              uint4* d1 = reinterpret_cast<uint4*>(o0 + (size_t)(4 * c + 2 * j + 1) * 64 + xb * 32);
+            {
+              uint8_t* b0 = stage + (2 * j) * 4096;
+              uint8_t* b1 = stage + (2 * j + 1) * 4096;
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
-                d0[g] = make_uint4(pack_h2(h0[8 * g], h0[8 * g + 1]), pack_h2(h0[8 * g + 2], h0[8 * g + 3]),
-                                   pack_h2(h0[8 * g + 4], h0[8 * g + 5]), pack_h2(h0[8 * g + 6], h0[8 * g + 7]));
-                d1[g] = make_uint4(pack_h2(h1[8 * g], h1[8 * g + 1]), pack_h2(h1[8 * g + 2], h1[8 * g + 3]),
-                                   pack_h2(h1[8 * g + 4], h1[8 * g + 5]), pack_h2(h1[8 * g + 6], h1[8 * g + 7]));
+                *swz(b0, lane, xb * 4 + g) =
+                    make_uint4(pack_h2(h0[8 * g], h0[8 * g + 1]), pack_h2(h0[8 * g + 2], h0[8 * g + 3]),
+                               pack_h2(h0[8 * g + 4], h0[8 * g + 5]), pack_h2(h0[8 * g + 6], h0[8 * g + 7]));
+                *swz(b1, lane, xb * 4 + g) =
+                    make_uint4(pack_h2(h1[8 * g], h1[8 * g + 1]), pack_h2(h1[8 * g + 2], h1[8 * g + 3]),
+                               pack_h2(h1[8 * g + 4], h1[8 * g + 5]), pack_h2(h1[8 * g + 6], h1[8 * g + 7]));
               }
             }
 #pragma unroll
@@ -272,12 +295,22 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
               l1row[j][xb * 8 + i] = pack_h2(a, b);
             }
           }
-          if (mok && out.l[1]) {
-            uint4* d = reinterpret_cast<uint4*>(out.l[1] + row * (size_t)(HW / 4) + (size_t)(2 * c + j) * 32);
+          if (out.l[1]) {
 #pragma unroll
             for (int g = 0; g < 4; ++g)
-              d[g] = make_uint4(l1row[j][4 * g], l1row[j][4 * g + 1], l1row[j][4 * g + 2], l1row[j][4 * g + 3]);
+              *swz(stage + 4 * 4096, lane, j * 4 + g) =
+                  make_uint4(l1row[j][4 * g], l1row[j][4 * g + 1], l1row[j][4 * g + 2], l1row[j][4 * g + 3]);
           }
+        }
+        // hand the staged tiles to the TMA store engine: 4 level-0 boxes (one per target row) + level 1
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          const int r0 = e * HW + m0 + q * 32;
+#pragma unroll
+          for (int rr = 0; rr < 4; ++rr) tma_store_2d(&mapO0, smem_u32(stage + rr * 4096), c * kBN + rr * 64, r0);
+          if (out.l[1]) tma_store_2d(&mapO1, smem_u32(stage + 4 * 4096), c * 64, r0);
+          bulk_commit();
         }
         // this accumulator stage has been read completely
         tc_fence_before();
@@ -352,6 +385,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     }
   }
 
+  if (FUSE && warp >= 4 && lane == 0) bulk_wait0();
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -376,6 +410,21 @@ EncodeTiledFn encode_fn() {
       fn = reinterpret_cast<EncodeTiledFn>(p);
   }
   return fn;
+}
+
+// generic 2-D fp16 row-major matrix [rows, cols], box = 64 columns (128 B, swizzled) x box_rows rows
+int make_map2(CUtensorMap* map, const __half* base, size_t rows, size_t cols, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  DBAF_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled is not available from the driver");
+  const cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  DBAF_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled (output) failed");
+  return DBAF_OK;
 }
 
 // [rows, 128] fp16 pixel-major matrix, box = 64 channels (128 B, swizzled) x box_rows pixels
@@ -418,6 +467,13 @@ int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int
   if (int rc = make_map(&mapB, b_t, (size_t)n * HW, kBN)) return rc;
   const bool fuse = wd == 64 && ht % 8 == 0;
   const int m_tiles = (HW + kBM - 1) / kBM;
+  CUtensorMap mapO0 = mapA, mapO1 = mapA;     // only the fused kernel stores through tensor maps
+  if (fuse) {
+    if (int rc = make_map2(&mapO0, out[0], (size_t)n * HW, (size_t)HW, 32)) return rc;
+    mapO1 = mapO0;
+    if (levels > 1)
+      if (int rc = make_map2(&mapO1, out[1], (size_t)n * HW, (size_t)HW / 4, 32)) return rc;
+  }
   Pyr pyr;
   for (int l = 0; l < 4; ++l) pyr.l[l] = (fuse && l < levels) ? out[l] : nullptr;
   pyr.l[0] = out[0];
@@ -427,8 +483,8 @@ int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, HW, m_tiles, pyr);
-  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, HW, m_tiles, pyr);
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr);
   DBAF_LAUNCH_CHECK("k_volume_tc");
   // fused: all requested levels are written; otherwise only level 0 and the caller pools
   *levels_done = fuse ? levels : 1;
