@@ -638,6 +638,7 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
 }
 
 #include "ba_fast.cuh"
+#include "ba_banded.cuh"
 
 int check_dims(int N, int E, int t0, int t1, int ht, int wd) {
   DBAF_REQUIRE(N > 0 && E >= 0 && ht > 0 && wd > 0, "non-positive size");
@@ -740,7 +741,7 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
 
 namespace {
 int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const double* prior, int prior_rows,
-                 int prior_cols, int rezero, cudaStream_t st) {
+                 int prior_cols, int rezero, cudaStream_t st, int band_blocks = 0) {
   // Only info, H, v, dx and Lfac are touched; their offsets depend on P alone.
   dbaf_ba_layout L;
   fill_layout(1, 0, 0, t1 - t0, 1, 1, &L);
@@ -760,6 +761,20 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
     }
     k_solve6<<<1, kThreads, smem, st>>>(P, lm, ep, prior, prior_rows, prior_cols, rezero, ws);
     DBAF_LAUNCH_CHECK("k_solve6");
+  } else if (band_blocks > 0 && band_blocks <= kBandMaxB && prior == nullptr) {
+    const int B = std::min(band_blocks, P - 1);
+    const int NB = B + 2;
+    const size_t smem = ((size_t)NB * NB * 36 + NB * 6 + 36 + 6 + 8) * sizeof(double);
+    static bool band_attr[64] = {};
+    int dev_id = 0;
+    DBAF_CUDA(cudaGetDevice(&dev_id));
+    if (!band_attr[dev_id & 63]) {
+      DBAF_CUDA(cudaFuncSetAttribute(k_solve_banded, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+      band_attr[dev_id & 63] = true;
+    }
+    k_solve_banded<<<1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, ws);
+    DBAF_LAUNCH_CHECK("k_solve_banded");
+    if (rezero) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, ((size_t)n * n + n) * 8, st));
   } else {
     k_solve<<<1, kThreads, 0, st>>>(n, lm, ep, prior, prior_rows, prior_cols, 0, ws);
     DBAF_LAUNCH_CHECK("k_solve");
@@ -774,6 +789,14 @@ extern "C" int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep
   DBAF_REQUIRE(workspace != nullptr, "null workspace");
   DBAF_REQUIRE(t1 >= t0, "t1 < t0");
   return launch_solve(workspace, t0, t1, lm, ep, prior, prior_rows, prior_cols, 0, (cudaStream_t)stream);
+}
+
+extern "C" int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, int band_blocks,
+                                    void* stream) {
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  DBAF_REQUIRE(t1 >= t0, "t1 < t0");
+  DBAF_REQUIRE(band_blocks >= 0, "negative band");
+  return launch_solve(workspace, t0, t1, lm, ep, nullptr, 0, 0, 0, (cudaStream_t)stream, band_blocks);
 }
 
 extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,

@@ -20,7 +20,12 @@ CONFIGS = {
     "c4": (64, 64, 12, 36, (23.87, 23.87, 31.87, 32.11)),
     "c5": (64, 64, 1000, 20000, (23.87, 23.87, 31.87, 32.11)),
     "tiny": (16, 24, 5, 10, (12.0, 12.5, 11.5, 7.5)),
+    "g40": (24, 32, 40, 160, (14.0, 14.5, 15.5, 11.5)),     # small banded global graph (6P = 240 > 160)
 }
+
+
+# fixed per-config seed slots: the golden fixtures depend on them, so new configs append
+_SEED_SLOT = {"c1": 0, "c2": 1, "c2_real": 2, "c3": 3, "c4": 4, "c5": 5, "tiny": 6, "g40": 7}
 
 
 def _qmul(a, b):
@@ -128,7 +133,7 @@ def make_window(config="c2", seed=0, t0=1, sensor_frac=0.0, near_frac=0.0, stere
     intrinsics [4], targets, weights [E,2,ht,wd], eta [K,ht,wd], ii, jj [E], t0, t1, plus the
     ground truth poses_gt / disps_gt."""
     ht, wd, P, E, intr = CONFIGS[config]
-    rng = np.random.default_rng(1234 + seed + 1000 * sorted(CONFIGS).index(config))
+    rng = np.random.default_rng(1234 + seed + 1000 * _SEED_SLOT[config])
     n = P + n_extra_frames
     poses_gt = trajectory(rng, n)
     disps_gt = _smooth(rng, (n, ht, wd), 0.3, 2.0)

@@ -135,7 +135,11 @@ class _Window:
                                     self.t1, self.ht, self.wd, float(alpha), int(motion_only),
                                     int(zero_first), int(k_lo), int(k_hi), _stream()), "dbaf_ba_linearize")
 
-    def solve(self, lm, ep, prior=None):
+    def solve(self, lm, ep, prior=None, band=0):
+        if band and prior is None:
+            check(lib.dbaf_ba_solve_banded(_p(self.ws), self.t0, self.t1, float(lm), float(ep), int(band),
+                                           _stream()), "dbaf_ba_solve_banded")
+            return
         pr, pc = (prior.shape if prior is not None else (0, 0))
         check(lib.dbaf_ba_solve(_p(self.ws), self.t0, self.t1, float(lm), float(ep), _p(prior),
                                 int(pr), int(pc), _stream()), "dbaf_ba_solve")

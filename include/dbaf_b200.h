@@ -180,6 +180,13 @@ int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
 int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep,
                   const double* prior, int prior_rows, int prior_cols, void* stream);
 
+/* Same solve for large windows whose reduced system is block-banded: every non-zero 6x6 block (I,J) of H
+ * satisfies |I-J| <= band_blocks (a temporal graph with edges reaching `reach` frames gives 2*reach).
+ * Windows up to 6P = 160 ignore the hint and use the dense shared-memory solver; beyond that a band of
+ * 1..25 blocks selects the sliding-window factorisation, anything else the slow dense fallback.
+ * Replaces Eigen::SimplicialLLT on the host (src/droid_kernels.cu:1248-1269). */
+int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, int band_blocks, void* stream);
+
 /* EvT6x1_kernel + dz + pose_retr_kernel + disp_retr_kernel, src/droid_kernels.cu:1140-1160,
  * 1486-1506,943-991.  dx_in: float32 [P,6] (NULL = the workspace's dx).  poses/disps are updated
  * in place.  dz_out [K,HW] (may be NULL), dx_out [P,6] (may be NULL).  update_disps=0 gives the

@@ -1,0 +1,183 @@
+"""Edge-sharded global BA: host logic on CPU (gloo, world_size 2, numpy oracle as the per-rank engine)
+and the CUDA engine + banded solver on the GPU."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from helpers import relerr, to_torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+class OracleEngine:
+    """Per-rank engine for the CPU test: the numpy restatement restricted to a depth-frame range."""
+
+    def __init__(self, oracle, w):
+        self.o, self.w = oracle, w
+        self.poses, self.disps = w["poses"].astype(np.float64), w["disps"].astype(np.float64)
+        self.ii, self.jj, self.t0, self.t1 = w["ii"], w["jj"], w["t0"], w["t1"]
+        self.tab = oracle.build_tables(self.ii, self.jj, self.t0, self.t1)
+        n = 6 * (self.t1 - self.t0)
+        self.Hv = torch.zeros(n * n + n, dtype=torch.float64)
+
+    def linearize(self, alpha, k_lo, k_hi):
+        o, w = self.o, self.w
+        frames = self.tab["kx"][k_lo:k_hi]
+        mine = np.isin(self.ii, frames)
+        Hs, vs, Eii, Eij, Cii, bz = o.jacobian_edges(self.poses, self.disps, w["intrinsics"], w["targets"],
+                                                     w["weights"], self.ii, self.jj, np.float64)
+        A, b = o.assemble_pose_system(Hs[:, mine], vs[:, mine], self.ii[mine], self.jj[mine], self.t0, self.t1)
+        self.C, self.wk, self.Q, self.E = o.depth_system(Cii, bz, Eii, Eij, self.disps, w["disps_sens"], w["eta"],
+                                                         self.ii, self.tab, self.t0, self.t1, alpha, np.float64)
+        P = self.t1 - self.t0
+        S = np.zeros((P, 6, P, 6))
+        sv = np.zeros((P, 6))
+        for a, bb, n, m, k in o.schur_triples(self.tab, self.t0, self.t1):
+            if k_lo <= k < k_hi:
+                S[a, :, bb, :] += (self.E[n] * self.Q[k]) @ self.E[m].T
+        qw = self.Q * self.wk
+        for n in range(self.E.shape[0]):
+            k, p = self.tab["kk_exp"][n], self.tab["jj_exp"][n] - self.t0
+            if k_lo <= k < k_hi and p >= 0:
+                sv[p] += self.E[n] @ qw[k]
+        nn = 6 * P
+        self.Hv[:nn * nn] = torch.from_numpy((A - S.reshape(nn, nn)).reshape(-1))
+        self.Hv[nn * nn:] = torch.from_numpy(b - sv.reshape(-1))
+
+    def system(self):
+        return self.Hv
+
+    def solve(self, lm, ep, band):
+        nn = 6 * (self.t1 - self.t0)
+        H = self.Hv[:nn * nn].numpy().reshape(nn, nn)
+        assert band >= 0
+        self.dx, _ = self.o.damped_solve(H, self.Hv[nn * nn:].numpy(), lm, ep)
+
+    def retract(self, k_lo, k_hi):
+        o = self.o
+        dz = o.back_substitute(self.E, self.Q, self.wk, self.dx, self.tab, self.t0, self.t1, np.float64)
+        own = np.zeros(len(self.tab["kx"]), bool)
+        own[k_lo:k_hi] = True
+        o.retract(self.poses, self.disps, self.dx, np.where(own[:, None], dz, 0.0), self.tab, self.t0, self.t1)
+
+
+def _worker(rank, world, port, seed, out):
+    for p in (os.path.join(ROOT, "dba-fusion_b200"), os.path.join(ROOT, "oracle")):
+        sys.path.insert(0, p)
+    import dbaf_oracle as oracle
+    from dbaf_b200 import global_ba, synth
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    w = synth.make_window("tiny", seed=seed, n_extra_frames=3)
+    eng = OracleEngine(oracle, w)
+    gba = global_ba.GlobalBA(eng, w["ii"], w["jj"], w["t0"], w["t1"])
+    gba.run(2)
+    d = torch.from_numpy(eng.disps)
+    gba.gather_disps(d)
+    if rank == 0:
+        np.savez(out, poses=eng.poses, disps=d.numpy(), ranges=np.array(gba.ranges))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_sharded_global_ba_matches_single_process_gloo(oracle, synth, tmp_path):
+    out = str(tmp_path / "res.npz")
+    port = 29500 + (os.getpid() % 2000)
+    mp.start_processes(_worker, args=(2, port, 5, out), nprocs=2, join=True, start_method="spawn")
+    res = np.load(out)
+    w = synth.make_window("tiny", seed=5, n_extra_frames=3)
+    p, d = w["poses"].astype(np.float64), w["disps"].astype(np.float64)
+    oracle.ba(p, d, w["intrinsics"], w["disps_sens"], w["targets"], w["weights"], w["eta"], w["ii"], w["jj"],
+              w["t0"], w["t1"], 2, 1e-4, 0.1, False, dtype=np.float64)
+    assert res["ranges"].shape == (2, 2) and res["ranges"][0, 1] == res["ranges"][1, 0]
+    assert relerr(res["poses"], p) < 1e-9 and relerr(res["disps"], d) < 1e-9
+
+
+def test_shard_ranges_and_band(oracle, synth):
+    from dbaf_b200 import global_ba
+    rng = np.random.default_rng(0)
+    for trial in range(10):
+        N = int(rng.integers(5, 60))
+        E = int(rng.integers(1, 300))
+        t0 = 1
+        ii, jj = rng.integers(0, N, E), rng.integers(0, N, E)
+        kx = global_ba.depth_frames(ii, t0, N)
+        assert np.array_equal(kx, oracle.build_tables(ii, jj, t0, N)["kx"])
+        for world in (1, 2, 3, 8):
+            r = global_ba.shard_ranges(ii, t0, N, world)
+            assert len(r) == world and r[0][0] == 0 and r[-1][1] == len(kx)
+            assert all(r[k][1] == r[k + 1][0] and r[k][0] <= r[k][1] for k in range(world - 1))
+        # band = the widest pose pair any Schur triple or edge block couples
+        tab = oracle.build_tables(ii, jj, t0, N)
+        tri = oracle.schur_triples(tab, t0, N)
+        want = int(np.abs(tri[:, 0] - tri[:, 1]).max()) if len(tri) else 0
+        for i, j in zip(ii, jj):
+            if i >= t0 and j >= t0:
+                want = max(want, abs(int(i) - int(j)))
+        assert global_ba.band_blocks(ii, jj, t0, N) == want
+    ii, jj = synth.banded_graph(50, reach=3)
+    assert global_ba.band_blocks(ii, jj, 1, 50) == 6
+
+
+# ------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("band_hint", ["exact", "loose", "dense"])
+def test_large_window_solvers(dev, db, oracle, synth, band_hint):
+    """6P = 240: banded sliding-window Cholesky (exact and over-estimated band) and the dense fallback."""
+    from dbaf_b200 import global_ba
+    w = synth.make_window("g40", seed=1, graph="banded")
+    t = to_torch(w, dev)
+    win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                     t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+    win.prepare()
+    win.linearize(0.05)
+    n = win.n
+    hv = win.Hv().cpu().numpy()
+    H, v = hv[:n * n].reshape(n, n), hv[n * n:]
+    band = global_ba.band_blocks(w["ii"], w["jj"], w["t0"], w["t1"])
+    assert band == 4 and n > 160
+    # nothing outside the band
+    blk = np.abs(H.reshape(n // 6, 6, n // 6, 6)).max(axis=(1, 3))
+    I, J = np.nonzero(blk)
+    assert np.abs(I - J).max() <= band
+    win.solve(1e-4, 0.1, band={"exact": band, "loose": band + 7, "dense": 0}[band_hint])
+    want, ok = oracle.damped_solve(H, v, 1e-4, 0.1)
+    assert ok and int(win.info().cpu()[1]) == 0
+    assert relerr(win.dx().cpu().numpy().reshape(-1), want) < 1e-6
+
+
+@pytest.mark.gpu
+def test_global_ba_single_rank_matches_oracle(dev, db, oracle, synth):
+    from dbaf_b200 import global_ba
+    w = synth.make_window("g40", seed=2, graph="banded")
+    t = to_torch(w, dev)
+    eng = global_ba.CudaEngine(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"],
+                               t["weights"], t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+    gba = global_ba.GlobalBA(eng, w["ii"], w["jj"], w["t0"], w["t1"])
+    gba.run(2)
+    res = {}
+    for dt in (np.float64, np.float32):
+        p, d = w["poses"].astype(dt), w["disps"].astype(dt)
+        oracle.ba(p, d, w["intrinsics"], w["disps_sens"], w["targets"], w["weights"], w["eta"], w["ii"], w["jj"],
+                  w["t0"], w["t1"], 2, 1e-4, 0.1, False, dtype=dt)
+        res[dt] = (p, d)
+    (p64, d64), (p32, d32) = res[np.float64], res[np.float32]
+    assert relerr(t["poses"].cpu().numpy(), p64) < max(1e-4, 3 * relerr(p32, p64))
+    assert relerr(t["disps"].cpu().numpy(), d64) < max(1e-4, 3 * relerr(d32, d64))
+    # sharding the same window in two halves on one GPU gives the same reduced system
+    t2 = to_torch(w, dev)
+    e2 = global_ba.CudaEngine(t2["poses"], t2["disps"], t2["intrinsics"], t2["disps_sens"], t2["targets"],
+                              t2["weights"], t2["eta"], t2["ii"], t2["jj"], w["t0"], w["t1"])
+    (a0, a1), (b0, b1) = global_ba.shard_ranges(w["ii"], w["t0"], w["t1"], 2)
+    e2.linearize(0.05, a0, a1)
+    part = e2.system().clone()
+    e2.linearize(0.05, b0, b1)
+    part += e2.system()
+    e2.linearize(0.05, 0, -1)
+    assert relerr(part.cpu().numpy(), e2.system().cpu().numpy()) < 1e-12
