@@ -764,7 +764,7 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
   } else if (band_blocks > 0 && band_blocks <= kBandMaxB && prior == nullptr) {
     const int B = std::min(band_blocks, P - 1);
     const int NB = B + 2;
-    const size_t smem = ((size_t)NB * NB * 36 + NB * 6 + 36 + 6 + 8) * sizeof(double);
+    const size_t smem = ((size_t)NB * NB * 36 + NB * 6 + 72 + 12 + 8) * sizeof(double);
     static bool band_attr[64] = {};
     int dev_id = 0;
     DBAF_CUDA(cudaGetDevice(&dev_id));
