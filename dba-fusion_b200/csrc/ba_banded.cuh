@@ -15,15 +15,16 @@
 constexpr int kBandThreads = 512;
 constexpr int kBandMaxB = 25;      // (B+2)^2 blocks * 288 B must fit in shared memory
 
-// 1/sqrt(d) from the single-precision hardware estimate plus two Newton steps in double (relative
-// error ~2e-16); the library rsqrt(double) carries special-case handling that sits on the critical
-// path of the pivot chain.
+// 1/sqrt(d) from the single-precision hardware estimate plus one Newton step in double; the library
+// rsqrt(double) is several times longer and sits on the critical path of the pivot chain.
 __device__ __forceinline__ double rsqrt_nr(double d) {
   if (!(d > 1e-30 && d < 1e30)) return rsqrt(d);
-  double y = (double)rsqrtf((float)d);
-  y = y * (1.5 - 0.5 * d * y * y);
-  y = y * (1.5 - 0.5 * d * y * y);
-  return y;
+  // one Newton step written as three dependent FMAs (a dependent float64 operation costs ~35 cycles on
+  // this part and the pivot chain is pure latency): error (3/8) e0^2 with e0 ~ 2^-22, i.e. ~1e-13
+  const double y0 = (double)rsqrtf((float)d);
+  const double t = d * y0;
+  const double e = fma(-t, y0, 1.0);
+  return fma(0.5 * y0, e, y0);
 }
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -74,81 +75,76 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
     }
   };
 
-  // Factorises the (already updated) diagonal block J held in the window, forward-solves its
-  // right-hand side and publishes L_JJ / 1/diag into buffer J & 1.  One thread, all in registers.
-  // `upd` = the panel block L_{J,J-1} whose outer product still has to be subtracted (look-ahead
-  // call from step J-1), or nullptr.
-  auto factor_diag = [&](int J, const double* upd) {
+  // Factorises diagonal block J, forward-solves its right-hand side and publishes L_JJ and 1/diag into
+  // buffer J & 1.  Runs on one whole warp: 21 lanes first apply the pending rank-6 update of the block
+  // (`upd` = panel block L_{J,J-1}, or nullptr) in parallel, lane 0 then runs the serial pivot chain in
+  // registers, and all lanes copy the results to the band store in global memory.
+  auto factor_diag = [&](int J, const double* upd, int ln) {
     double* A = slot(J, J);
-    double a[6][6];
+    if (upd && ln < 21) {
+      int r, c;
+      tri_unpack(ln, r, c);
+      double sum = 0.0;
 #pragma unroll
-    for (int r = 0; r < 6; ++r)
-#pragma unroll
-      for (int c = 0; c < 6; ++c)
-        if (c <= r) a[r][c] = A[r * 6 + c];
-    if (upd) {
-      double l[6][6];
-#pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int c = 0; c < 6; ++c) l[r][c] = upd[r * 6 + c];
+      for (int k = 0; k < 6; ++k) sum += upd[r * 6 + k] * upd[c * 6 + k];
+      A[r * 6 + c] -= sum;
+    }
+    __syncwarp();
+    double* Lj = Ljj + (J & 1) * 36;
+    double* dd = dj + (J & 1) * 6;
+    if (ln == 0) {
+      double a[6][6];
 #pragma unroll
       for (int r = 0; r < 6; ++r)
 #pragma unroll
         for (int c = 0; c < 6; ++c)
-          if (c <= r) {
-            double s = 0.0;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) s += l[r][k] * l[c][k];
-            a[r][c] -= s;
-          }
-    }
-    bool bad = false;
-    double di[6];
-#pragma unroll
-    for (int c = 0; c < 6; ++c) {
-      double d = a[c][c];
-#pragma unroll
-      for (int k = 0; k < 6; ++k)
-        if (k < c) d -= a[c][k] * a[c][k];
-      if (d <= 0.0) { bad = true; d = 1.0; }
-      const double inv = rsqrt_nr(d);
-      a[c][c] = d * inv;
-      di[c] = inv;
-#pragma unroll
-      for (int r = 0; r < 6; ++r)
-        if (r > c) {
-          double s = a[r][c];
-#pragma unroll
-          for (int k = 0; k < 6; ++k)
-            if (k < c) s -= a[r][k] * a[c][k];
-          a[r][c] = s * inv;
-        }
-    }
-    if (bad) fail = 1;
-    double y[6];
-#pragma unroll
-    for (int r = 0; r < 6; ++r) {
-      double s = yw[(J % NB) * 6 + r];
-#pragma unroll
-      for (int k = 0; k < 6; ++k)
-        if (k < r) s -= a[r][k] * y[k];
-      y[r] = s * di[r];
-    }
-    double* Lj = Ljj + (J & 1) * 36;
-    double* dd = dj + (J & 1) * 6;
-#pragma unroll
-    for (int r = 0; r < 6; ++r) {
-      yw[(J % NB) * 6 + r] = y[r];
-      y_g[6 * J + r] = y[r];
-      dd[r] = di[r];
-      dinv_g[6 * J + r] = di[r];
+          if (c <= r) a[r][c] = A[r * 6 + c];
+      bool bad = false;
+      double di[6];
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
-        const double l = c <= r ? a[r][c] : 0.0;
-        Lj[r * 6 + c] = l;
-        Lband[((size_t)J * (B + 1)) * 36 + r * 6 + c] = l;
+        double d = a[c][c];
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (k < c) d -= a[c][k] * a[c][k];
+        if (d <= 0.0) { bad = true; d = 1.0; }
+        const double inv = rsqrt_nr(d);
+        a[c][c] = d * inv;
+        di[c] = inv;
+#pragma unroll
+        for (int r = 0; r < 6; ++r)
+          if (r > c) {
+            double sum = a[r][c];
+#pragma unroll
+            for (int k = 0; k < 6; ++k)
+              if (k < c) sum -= a[r][k] * a[c][k];
+            a[r][c] = sum * inv;
+          }
       }
+      if (bad) fail = 1;
+      double y[6];
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        double sum = yw[(J % NB) * 6 + r];
+#pragma unroll
+        for (int k = 0; k < 6; ++k)
+          if (k < r) sum -= a[r][k] * y[k];
+        y[r] = sum * di[r];
+      }
+#pragma unroll
+      for (int r = 0; r < 6; ++r) {
+        yw[(J % NB) * 6 + r] = y[r];
+        dd[r] = di[r];
+#pragma unroll
+        for (int c = 0; c < 6; ++c) Lj[r * 6 + c] = c <= r ? a[r][c] : 0.0;
+      }
+    }
+    __syncwarp();
+    // band store (needed again only by the back-substitution)
+    for (int e = ln; e < 36; e += 32) Lband[((size_t)J * (B + 1)) * 36 + e] = Lj[e];
+    if (ln < 6) {
+      y_g[6 * J + ln] = yw[(J % NB) * 6 + ln];
+      dinv_g[6 * J + ln] = dd[ln];
     }
   };
 
@@ -156,12 +152,43 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
   for (int I = 0; I <= min(B, P - 1); ++I)
     for (int e = tid; e < row_elems(I); e += nt) place(I, e, fetch(I, e));
   __syncthreads();
-  if (tid == 0) factor_diag(0, nullptr);
+  if (tid >= nt - 32) factor_diag(0, nullptr, tid - (nt - 32));
   __syncthreads();
 
   const int nwork = nt - 32;                         // the last warp runs the look-ahead factorisation
+  // Incoming rows are always full (B+1 blocks + rhs) inside the loop, so each thread's two elements keep a
+  // fixed position inside the row: only the row index moves (pointer += 6n+6 per step).
+  int pf_kind[2], pf_b[2], pf_rc[2];
+  size_t pf_off[2];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const int e = tid + u * nt;
+    pf_kind[u] = 0;
+    pf_b[u] = pf_rc[u] = 0;
+    pf_off[u] = 0;
+    if (e < (B + 1) * 36) {
+      const int bb = e / 36, rc = e - bb * 36, r = rc / 6, c = rc - r * 6;
+      pf_kind[u] = (bb == B && r == c) ? 2 : 1;     // 2 = diagonal entry (damped)
+      pf_b[u] = bb;
+      pf_rc[u] = rc;
+      pf_off[u] = (size_t)r * n + (size_t)(6 * bb + c) - (size_t)6 * B;   // + I*(6n+6), never negative for I >= B
+    } else if (e < (B + 1) * 36 + 6) {
+      pf_kind[u] = 3;                                // right-hand side entry
+      pf_rc[u] = e - (B + 1) * 36;
+    }
+  }
+  int jm = 0;                                        // J % NB, kept incrementally
+#ifdef DBAF_BAND_PROFILE
+  long long tp0 = 0, tp1 = 0, tp2 = 0, tp3 = 0, tla = 0, c0, c1;
+#define BAND_TICK(var) do { c1 = clock64(); var += c1 - c0; c0 = c1; } while (0)
+#else
+#define BAND_TICK(var) do {} while (0)
+#endif
   for (int J = 0; J < P; ++J) {
     if (fail) break;
+#ifdef DBAF_BAND_PROFILE
+    c0 = clock64();
+#endif
     const int last = min(J + B, P - 1);              // last block row inside the band of column J
     const int nbelow = last - J;
     const double* Lj = Ljj + (J & 1) * 36;
@@ -172,10 +199,11 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
     if (Inew < P) {
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        const int e = tid + u * nt;
-        if (e < row_elems(Inew)) pre[u] = fetch(Inew, e);
+        if (pf_kind[u] == 3) pre[u] = ws.v[6 * Inew + pf_rc[u]];
+        else if (pf_kind[u]) pre[u] = ws.H[pf_off[u] + (size_t)Inew * (6 * (size_t)n + 6)];
       }
     }
+    BAND_TICK(tp0);
     // (2) panel: every row (I, r) below the diagonal block: X L_JJ^T = A, and its rhs entry
     for (int t = tid; t < nbelow * 6; t += nt) {
       const int I = J + 1 + t / 6, r = t % 6;
@@ -198,14 +226,15 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
       }
       yw[(I % NB) * 6 + r] = yy;
     }
+    BAND_TICK(tp1);
     __syncthreads();
+    BAND_TICK(tp2);
     // (3) trailing update inside the window: A_IK -= L_IJ L_KJ^T for J < K <= I <= last.  4 threads
     //     share a row (I, r) and split the K range.  The next diagonal block (J+1, J+1) is left to the
     //     last warp, which updates AND factorises it at the same time (look-ahead), so the serial
     //     rsqrt chain of the factorisation overlaps the bulk of the update.
     if (tid < nwork) {
       // one thread = half (3 rows) of one 6x6 block (I, K): 54 shared-memory loads feed 108 FMAs
-      const int jm = J % NB;
       const int npairs = nbelow * (nbelow + 1) / 2;
       for (int t = tid; t < 2 * npairs; t += nwork) {
         const int pair = t >> 1, half = t & 1;
@@ -241,54 +270,117 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
 #pragma unroll
           for (int c = 0; c < 6; ++c) A[r * 6 + c] -= acc[r][c];
       }
-    } else if (tid == nwork && J + 1 < P) {
-      factor_diag(J + 1, nbelow > 0 ? slot(J + 1, J) : nullptr);
+    } else if (J + 1 < P) {
+      factor_diag(J + 1, nbelow > 0 ? slot(J + 1, J) : nullptr, tid - nwork);
     }
+    BAND_TICK(tp3);
     // incoming block row (its slots are unused during this step: NB = B + 2)
     if (Inew < P) {
+      int rs = jm - 1;                               // (J + B + 1) % NB
+      if (rs < 0) rs += NB;
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        const int e = tid + u * nt;
-        if (e < row_elems(Inew)) place(Inew, e, pre[u]);
+        if (pf_kind[u] == 3) {
+          yw[rs * 6 + pf_rc[u]] = pre[u];
+        } else if (pf_kind[u]) {
+          int cs = jm + 1 + pf_b[u];                 // (Inew - B + b) % NB
+          if (cs >= NB) cs -= NB;
+          const double a = pf_kind[u] == 2 ? pre[u] + (epd + lmd * pre[u]) : pre[u];
+          Wd[((size_t)rs * NB + cs) * 36 + pf_rc[u]] = a;
+        }
       }
     }
+    if (++jm == NB) jm = 0;
     __syncthreads();
+    BAND_TICK(tla);
   }
+#ifdef DBAF_BAND_PROFILE
+  if (tid == 0 || tid == nwork) {
+    const int o = tid == 0 ? 6 : 11;      // info[6..10]: thread 0, info[11..15]: look-ahead thread (kilo-cycles)
+    ws.info[o] = (int)(tp0 >> 10); ws.info[o + 1] = (int)(tp1 >> 10); ws.info[o + 2] = (int)(tp2 >> 10);
+    ws.info[o + 3] = (int)(tp3 >> 10); ws.info[o + 4] = (int)(tla >> 10);
+  }
+#endif
   __syncthreads();
   const bool ok = fail == 0;
   if (ok) {
-    // back-substitution L^T x = y, bottom up; yw becomes the window of already-solved x blocks
-    for (int J = P - 1; J >= 0; --J) {
-      const int nbelow = min(J + B, P - 1) - J;
-      // s_c = y_J[c] - sum_{d=1..nbelow} sum_r L_{J+d,J}[r][c] * x_{J+d}[r]; warp c owns component c
-      if (wid < 6) {
-        double s = 0.0;
-        for (int t = lane; t < nbelow * 6; t += 32) {
-          const int d = 1 + t / 6, r = t % 6;
-          s += Lband[((size_t)J * (B + 1) + d) * 36 + r * 6 + wid] * yw[((J + d) % NB) * 6 + r];
-        }
-        s = warp_sum_d(s);
-        if (lane == 0) sred[wid] = y_g[6 * J + wid] - s;
+    // Back-substitution L^T x = y, bottom up, right-looking: once x_J is known every pending
+    // right-hand side above it is updated, y_I -= L_{J,I}^T x_J (I = J-B .. J-1).  The blocks of
+    // block row J of L, the next diagonal block and the next incoming y row are fetched one step
+    // ahead, so a step is one short serial 6x6 solve + one parallel rank-6 update.
+    double* dbuf = Ljj;                              // 2 x 36 diagonal blocks (reused)
+    double* ibuf = dj;                               // 2 x 6 inverse diagonals (reused)
+    double* xs = sred;                               // 6: x_J of the current step
+    auto row_block = [&](int J, int t) {             // thread t's column c of L_{J,I}, I = J-1-t/6
+      return Lband + ((size_t)(J - 1 - t / 6) * (B + 1) + (1 + t / 6)) * 36 + (t % 6);
+    };
+    for (int e = tid; e < NB * 6; e += nt) {
+      const int I = P - 1 - e / 6;                   // rows P-1 .. P-NB
+      if (I >= 0 && e / 6 <= B) yw[(I % NB) * 6 + e % 6] = y_g[6 * I + e % 6];
+    }
+    if (tid < 36) dbuf[((P - 1) & 1) * 36 + tid] = Lband[((size_t)(P - 1) * (B + 1)) * 36 + tid];
+    if (tid < 6) ibuf[((P - 1) & 1) * 6 + tid] = dinv_g[6 * (P - 1) + tid];
+    double cur[6];
+    {
+      const int nab = min(B, P - 1);
+      if (tid < nab * 6) {
+        const double* q = row_block(P - 1, tid);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) cur[r] = q[r * 6];
       }
-      __syncthreads();
+    }
+    __syncthreads();
+    for (int J = P - 1; J >= 0; --J) {
       if (tid == 0) {
-        const double* L = Lband + ((size_t)J * (B + 1)) * 36;
-        double x[6];
+        const double* L = dbuf + (J & 1) * 36;
+        const double* di = ibuf + (J & 1) * 6;
+        double l[6][6], x[6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          x[r] = yw[(J % NB) * 6 + r];
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+            if (c < r) l[r][c] = L[r * 6 + c];
+        }
 #pragma unroll
         for (int c = 5; c >= 0; --c) {
-          double s = sred[c];
+          double sum = x[c];
 #pragma unroll
           for (int k = 0; k < 6; ++k)
-            if (k > c) s -= L[k * 6 + c] * x[k];
-          x[c] = s * dinv_g[6 * J + c];
+            if (k > c) sum -= l[k][c] * x[k];
+          x[c] = sum * di[c];
         }
 #pragma unroll
         for (int c = 0; c < 6; ++c) {
-          yw[(J % NB) * 6 + c] = x[c];
+          xs[c] = x[c];
           ws.dx[6 * J + c] = (float)x[c];
         }
       }
       __syncthreads();
+      const int nab = min(B, J);                     // rows above J inside the band
+      double nxt[6];
+      if (tid < nab * 6) {
+        double sum = 0.0;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) sum += cur[r] * xs[r];
+        yw[((J - 1 - tid / 6) % NB) * 6 + tid % 6] -= sum;
+      }
+      if (J > 0) {
+        const int nab2 = min(B, J - 1);
+        if (tid < nab2 * 6) {
+          const double* q = row_block(J - 1, tid);
+#pragma unroll
+          for (int r = 0; r < 6; ++r) nxt[r] = q[r * 6];
+        }
+        const int u = tid - (nt - 64);               // the last two warps fetch the next diagonal block etc.
+        if (u >= 0 && u < 36) dbuf[((J - 1) & 1) * 36 + u] = Lband[((size_t)(J - 1) * (B + 1)) * 36 + u];
+        if (u >= 36 && u < 42) ibuf[((J - 1) & 1) * 6 + (u - 36)] = dinv_g[6 * (J - 1) + (u - 36)];
+        const int Iin = J - 1 - B;                   // row entering the window for step J-1
+        if (u >= 42 && u < 48 && Iin >= 0) yw[(Iin % NB) * 6 + (u - 42)] = y_g[6 * Iin + (u - 42)];
+      }
+      __syncthreads();
+#pragma unroll
+      for (int r = 0; r < 6; ++r) cur[r] = nxt[r];
     }
   } else {
     for (int i = tid; i < n; i += nt) ws.dx[i] = 0.0f;
