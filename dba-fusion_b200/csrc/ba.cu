@@ -639,6 +639,7 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
 
 #include "ba_fast.cuh"
 #include "ba_banded.cuh"
+#include "ba_lin2.cuh"
 
 int check_dims(int N, int E, int t0, int t1, int ht, int wd) {
   DBAF_REQUIRE(N > 0 && E >= 0 && ht > 0 && wd > 0, "non-positive size");
@@ -706,7 +707,7 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
   const int pxt = pick_pxt(k_cap, HW);
   dim3 grid((HW + 256 * pxt - 1) / (256 * pxt), k_cap);
 #define DBAF_LIN(PX, MO)                                                                       \
-  k_linearize<PX, MO><<<grid, kThreads, 0, st>>>(poses, disps, intrinsics, disps_sens, targets, \
+  k_linearize2<PX, MO><<<grid, kThreads, 0, st>>>(poses, disps, intrinsics, disps_sens, targets, \
                                                  weights, eta, eta_rows, jj, t0, P, HW, wd,    \
                                                  alpha, k_lo, k_hi, ws)
   if (motion_only == 1) {
