@@ -15,18 +15,6 @@
 constexpr int kBandThreads = 512;
 constexpr int kBandMaxB = 25;      // (B+2)^2 blocks * 288 B must fit in shared memory
 
-// 1/sqrt(d) from the single-precision hardware estimate plus one Newton step in double; the library
-// rsqrt(double) is several times longer and sits on the critical path of the pivot chain.
-__device__ __forceinline__ double rsqrt_nr(double d) {
-  if (!(d > 1e-30 && d < 1e30)) return rsqrt(d);
-  // one Newton step written as three dependent FMAs (a dependent float64 operation costs ~35 cycles on
-  // this part and the pivot chain is pure latency): error (3/8) e0^2 with e0 ~ 2^-22, i.e. ~1e-13
-  const double y0 = (double)rsqrtf((float)d);
-  const double t = d * y0;
-  const double e = fma(-t, y0, 1.0);
-  return fma(0.5 * y0, e, y0);
-}
-
 __device__ __forceinline__ double warp_sum_d(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

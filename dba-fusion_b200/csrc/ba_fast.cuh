@@ -121,6 +121,18 @@ k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k
 }
 
 // ------------------------------------------------------------------ solve ----
+// 1/sqrt(d) from the single-precision hardware estimate plus one Newton step in double; the library
+// rsqrt(double) is several times longer and sits on the critical path of the pivot chain.
+__device__ __forceinline__ double rsqrt_nr(double d) {
+  if (!(d > 1e-30 && d < 1e30)) return rsqrt(d);
+  // one Newton step written as three dependent FMAs (a dependent float64 operation costs ~35 cycles on
+  // this part and the pivot chain is pure latency): error (3/8) e0^2 with e0 ~ 2^-22, i.e. ~1e-13
+  const double y0 = (double)rsqrtf((float)d);
+  const double t = d * y0;
+  const double e = fma(-t, y0, 1.0);
+  return fma(0.5 * y0, e, y0);
+}
+
 // Blocked right-looking Cholesky on 6x6 pose blocks, matrix (plus the right-hand side as an extra
 // row, so the forward substitution falls out of the factorisation) resident in shared memory.
 // P block steps with 3 barriers each instead of 6P column steps with 4.
@@ -150,7 +162,7 @@ __device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* din
         for (int kk = 0; kk < 6; ++kk)
           if (kk < c) d -= a[c][kk] * a[c][kk];
         if (d <= 0.0) { bad = true; d = 1.0; }
-        const double inv = rsqrt(d);
+        const double inv = rsqrt_nr(d);
         a[c][c] = d * inv;
         dinv[j0 + c] = inv;
 #pragma unroll

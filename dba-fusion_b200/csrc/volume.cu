@@ -39,8 +39,8 @@ k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, int 
     for (int t = threadIdx.x; t < 32 * kTile; t += 256) {
       const int c = t / kTile, x = t - c * kTile;
       const bool cok = c0 + c < C;
-      As[c][x] = (cok && m0 + x < HW) ? __half2float(A[(size_t)(c0 + c) * HW + m0 + x]) : 0.f;
-      Bs[c][x] = (cok && n0 + x < HW) ? __half2float(B[(size_t)(c0 + c) * HW + n0 + x]) : 0.f;
+      As[c][x] = (cok && m0 + x < HW) ? __half2float(__float2half_rn(__half2float(A[(size_t)(c0 + c) * HW + m0 + x]) * 0.25f)) : 0.f;
+      Bs[c][x] = (cok && n0 + x < HW) ? __half2float(__float2half_rn(__half2float(B[(size_t)(c0 + c) * HW + n0 + x]) * 0.25f)) : 0.f;
     }
     __syncthreads();
 #pragma unroll 8
@@ -62,7 +62,7 @@ k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, int 
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int nn = n0 + tx * 4 + j;
-      if (nn < HW) out[((size_t)e * HW + m) * HW + nn] = __float2half_rn(acc[i][j] * 0.0625f);
+      if (nn < HW) out[((size_t)e * HW + m) * HW + nn] = __float2half_rn(acc[i][j]);   // operands were divided by 4 in fp16, corr.py:67-68
     }
   }
 }

@@ -112,6 +112,18 @@ __device__ __forceinline__ void tc_ld32(uint32_t taddr, float* v) {
   for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// two 32-column TMEM loads issued back to back, one wait: halves the exposed load latency per sub-step
+__device__ __forceinline__ void tc_ld32x2(uint32_t ta, uint32_t tb, uint32_t* a, uint32_t* b) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%64];\n\t"
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%32, %33, %34, %35, %36, %37, %38, %39, %40, %41, %42, %43, %44, %45, %46, %47, %48, %49, %50, %51, %52, %53, %54, %55, %56, %57, %58, %59, %60, %61, %62, %63}, [%65];\n\t"
+      "tcgen05.wait::ld.sync.aligned;"
+      : "=r"(a[0]), "=r"(a[1]), "=r"(a[2]), "=r"(a[3]), "=r"(a[4]), "=r"(a[5]), "=r"(a[6]), "=r"(a[7]), "=r"(a[8]), "=r"(a[9]), "=r"(a[10]), "=r"(a[11]), "=r"(a[12]), "=r"(a[13]), "=r"(a[14]), "=r"(a[15]), "=r"(a[16]), "=r"(a[17]), "=r"(a[18]), "=r"(a[19]), "=r"(a[20]), "=r"(a[21]), "=r"(a[22]), "=r"(a[23]), "=r"(a[24]), "=r"(a[25]), "=r"(a[26]), "=r"(a[27]), "=r"(a[28]), "=r"(a[29]), "=r"(a[30]), "=r"(a[31]),
+        "=r"(b[0]), "=r"(b[1]), "=r"(b[2]), "=r"(b[3]), "=r"(b[4]), "=r"(b[5]), "=r"(b[6]), "=r"(b[7]), "=r"(b[8]), "=r"(b[9]), "=r"(b[10]), "=r"(b[11]), "=r"(b[12]), "=r"(b[13]), "=r"(b[14]), "=r"(b[15]), "=r"(b[16]), "=r"(b[17]), "=r"(b[18]), "=r"(b[19]), "=r"(b[20]), "=r"(b[21]), "=r"(b[22]), "=r"(b[23]), "=r"(b[24]), "=r"(b[25]), "=r"(b[26]), "=r"(b[27]), "=r"(b[28]), "=r"(b[29]), "=r"(b[30]), "=r"(b[31])
+      : "r"(ta), "r"(tb)
+      : "memory");
+}
+
 // K-major, 128-byte swizzle: 8-row groups 1024 B apart (SBO), version 1 (Blackwell), layout type 2.
 __device__ __forceinline__ uint64_t umma_desc_k128(uint32_t smem_addr) {
   uint64_t d = 0;
@@ -138,7 +150,8 @@ struct Pyr {
 
 // ------------------------------------------------------------------ transpose pre-pass ----
 // [n, C, HW] (channel-major) -> [n, HW, C] (pixel-major): 32 px x 64 ch tiles through shared memory
-__global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW) {
+__global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict__ src, __half* __restrict__ dst, int C, int HW,
+                                                        float scale) {
   __shared__ __half tile[64][33];
   const int e = blockIdx.z, p0 = blockIdx.x * 32, c0 = blockIdx.y * 64;
   const __half* s = src + (size_t)e * C * HW;
@@ -146,7 +159,8 @@ __global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   for (int c = ty; c < 64; c += 8) {
     const int p = p0 + tx;
-    tile[c][tx] = (p < HW && c0 + c < C) ? s[(size_t)(c0 + c) * HW + p] : __float2half(0.f);
+    // scale is a power of two: exact in fp16 (barring subnormals), like the reference's two /4.0
+    tile[c][tx] = (p < HW && c0 + c < C) ? __float2half_rn(__half2float(s[(size_t)(c0 + c) * HW + p]) * scale) : __float2half(0.f);
   }
   __syncthreads();
   // each thread writes a pair of channels (4 B) so that a warp writes 128 contiguous bytes of one pixel
@@ -266,33 +280,35 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         for (int j = 0; j < 2; ++j) {
 #pragma unroll
           for (int xb = 0; xb < 2; ++xb) {
-            float v0[32], v1[32];
-            tc_ld32(t0 + (uint32_t)((2 * j) * 64 + xb * 32), v0);
-            tc_ld32(t0 + (uint32_t)((2 * j + 1) * 64 + xb * 32), v1);
-            __half h0[32], h1[32];
+            uint32_t r0[32], r1[32];
+            tc_ld32x2(t0 + (uint32_t)((2 * j) * 64 + xb * 32), t0 + (uint32_t)((2 * j + 1) * 64 + xb * 32), r0, r1);
+            // fp32 -> fp16 two at a time; the pooled value is built from the ROUNDED level-0 values
+            __half2 p0[16], p1[16];
 #pragma unroll
-            for (int i = 0; i < 32; ++i) {
-              h0[i] = __float2half_rn(v0[i] * 0.0625f);
-              h1[i] = __float2half_rn(v1[i] * 0.0625f);
+            for (int i = 0; i < 16; ++i) {
+              p0[i] = __floats2half2_rn(__uint_as_float(r0[2 * i]), __uint_as_float(r0[2 * i + 1]));
+              p1[i] = __floats2half2_rn(__uint_as_float(r1[2 * i]), __uint_as_float(r1[2 * i + 1]));
             }
             {
               uint8_t* b0 = stage + (2 * j) * 4096;
               uint8_t* b1 = stage + (2 * j + 1) * 4096;
+              const uint32_t* w0 = reinterpret_cast<const uint32_t*>(p0);
+              const uint32_t* w1 = reinterpret_cast<const uint32_t*>(p1);
 #pragma unroll
               for (int g = 0; g < 4; ++g) {
-                *swz(b0, lane, xb * 4 + g) =
-                    make_uint4(pack_h2(h0[8 * g], h0[8 * g + 1]), pack_h2(h0[8 * g + 2], h0[8 * g + 3]),
-                               pack_h2(h0[8 * g + 4], h0[8 * g + 5]), pack_h2(h0[8 * g + 6], h0[8 * g + 7]));
-                *swz(b1, lane, xb * 4 + g) =
-                    make_uint4(pack_h2(h1[8 * g], h1[8 * g + 1]), pack_h2(h1[8 * g + 2], h1[8 * g + 3]),
-                               pack_h2(h1[8 * g + 4], h1[8 * g + 5]), pack_h2(h1[8 * g + 6], h1[8 * g + 7]));
+                *swz(b0, lane, xb * 4 + g) = make_uint4(w0[4 * g], w0[4 * g + 1], w0[4 * g + 2], w0[4 * g + 3]);
+                *swz(b1, lane, xb * 4 + g) = make_uint4(w1[4 * g], w1[4 * g + 1], w1[4 * g + 2], w1[4 * g + 3]);
               }
             }
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-              const __half a = pool_h(h0[4 * i], h0[4 * i + 1], h1[4 * i], h1[4 * i + 1]);
-              const __half b = pool_h(h0[4 * i + 2], h0[4 * i + 3], h1[4 * i + 2], h1[4 * i + 3]);
-              l1row[j][xb * 8 + i] = pack_h2(a, b);
+              // level-1 columns 2i and 2i+1 of this half row: ((a+b)+c)+d, *0.25, one rounding
+              const float2 a0 = __half22float2(p0[2 * i]), a1 = __half22float2(p1[2 * i]);
+              const float2 c0 = __half22float2(p0[2 * i + 1]), c1 = __half22float2(p1[2 * i + 1]);
+              const float lo = (((a0.x + a0.y) + a1.x) + a1.y) * 0.25f;
+              const float hi = (((c0.x + c0.y) + c1.x) + c1.y) * 0.25f;
+              const __half2 pr = __floats2half2_rn(lo, hi);
+              l1row[j][xb * 8 + i] = *reinterpret_cast<const uint32_t*>(&pr);
             }
           }
           if (out.l[1]) {
@@ -368,13 +384,13 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                 uint32_t w[4];
 #pragma unroll
                 for (int t = 0; t < 4; ++t)
-                  w[t] = pack_h2(__float2half_rn(v[8 * g + 2 * t] * 0.0625f), __float2half_rn(v[8 * g + 2 * t + 1] * 0.0625f));
+                  w[t] = pack_h2(__float2half_rn(v[8 * g + 2 * t]), __float2half_rn(v[8 * g + 2 * t + 1]));
                 reinterpret_cast<uint4*>(d)[g] = make_uint4(w[0], w[1], w[2], w[3]);
               }
             } else {
 #pragma unroll
               for (int i = 0; i < 32; ++i)
-                if (nb + i < HW) d[i] = __float2half_rn(v[i] * 0.0625f);
+                if (nb + i < HW) d[i] = __float2half_rn(v[i]);
             }
           }
         }
@@ -459,8 +475,8 @@ int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int
   __half* a_t = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
   __half* b_t = a_t + (size_t)n * HW * C;
   dim3 tg((HW + 31) / 32, C / 64, n);
-  k_to_pixel_major<<<tg, 256, 0, st>>>(f1, a_t, C, HW);
-  k_to_pixel_major<<<tg, 256, 0, st>>>(f2, b_t, C, HW);
+  k_to_pixel_major<<<tg, 256, 0, st>>>(f1, a_t, C, HW, 0.25f);   // fmap / 4.0 on both sides, dbaf/modules/corr.py:67-68
+  k_to_pixel_major<<<tg, 256, 0, st>>>(f2, b_t, C, HW, 0.25f);
   DBAF_LAUNCH_CHECK("k_to_pixel_major");
   CUtensorMap mapA, mapB;
   if (int rc = make_map(&mapA, a_t, (size_t)n * HW, kBM)) return rc;
