@@ -14,10 +14,10 @@
 namespace dbaf {
 
 // volume_tc.cu
-int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int wd, int levels,
-                   __half* const* out, void* workspace, size_t workspace_bytes, cudaStream_t st,
-                   int* levels_done);
-size_t corr_volume_tc_workspace(int n, int C, int ht, int wd);
+int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
+                   int ht, int wd, int levels, __half* const* out, void* workspace, size_t workspace_bytes,
+                   cudaStream_t st, int* levels_done);
+size_t corr_volume_tc_workspace(int n1, int n2, int C, int ht, int wd);
 
 namespace {
 
@@ -25,15 +25,15 @@ constexpr int kTile = 64;
 
 // 64x64 output tile per CTA, 256 threads x (4x4), K staged 32 channels at a time.
 __global__ void __launch_bounds__(256)
-k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, int C, int HW,
-              __half* __restrict__ out) {
+k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, const int* __restrict__ idx1,
+              const int* __restrict__ idx2, int C, int HW, __half* __restrict__ out) {
   __shared__ float As[32][kTile + 1];
   __shared__ float Bs[32][kTile + 1];
   const int e = blockIdx.z;
   const int m0 = blockIdx.y * kTile, n0 = blockIdx.x * kTile;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
-  const __half* A = f1 + (size_t)e * C * HW;
-  const __half* B = f2 + (size_t)e * C * HW;
+  const __half* A = f1 + (size_t)(idx1 ? idx1[e] : e) * C * HW;
+  const __half* B = f2 + (size_t)(idx2 ? idx2[e] : e) * C * HW;
   float acc[4][4] = {};
   for (int c0 = 0; c0 < C; c0 += 32) {
     for (int t = threadIdx.x; t < 32 * kTile; t += 256) {
@@ -118,37 +118,34 @@ k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int le
 
 using namespace dbaf;
 
-extern "C" size_t dbaf_corr_volume_workspace_bytes(int n, int C, int ht, int wd) {
-  return corr_volume_tc_workspace(n, C, ht, wd);
+namespace dbaf {
+namespace {
+
+__global__ void k_check_index(const int* __restrict__ idx, int n, int limit, int* __restrict__ bad) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n && (idx[t] < 0 || idx[t] >= limit)) atomicExch(bad, 1);
 }
 
-extern "C" int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, int n, int C, int ht, int wd,
-                                        int levels, void* const* out_host, void* workspace,
-                                        size_t workspace_bytes, void* stream) {
-  DBAF_REQUIRE(n >= 0 && C > 0 && ht > 0 && wd > 0, "bad sizes");
-  DBAF_REQUIRE(levels >= 1 && levels <= 4, "levels must be 1..4");
-  DBAF_REQUIRE(out_host != nullptr, "null output list");
-  if (n == 0) return DBAF_OK;
-  cudaStream_t st = (cudaStream_t)stream;
+int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
+                   int ht, int wd, int levels, void* const* out_host, void* workspace, size_t workspace_bytes,
+                   cudaStream_t st) {
   const int HW = ht * wd;
   __half* outs[4] = {nullptr, nullptr, nullptr, nullptr};
   for (int l = 0; l < levels; ++l) outs[l] = static_cast<__half*>(out_host[l]);
-  const __half* f1 = static_cast<const __half*>(fmap1);
-  const __half* f2 = static_cast<const __half*>(fmap2);
-
   // DBAF_VOLUME_IMPL=simt forces the cross-check kernels (tests use it to validate the
   // tensor-core path against an independent implementation inside the same library).
   const char* impl = std::getenv("DBAF_VOLUME_IMPL");
   const bool force_simt = impl && std::strcmp(impl, "simt") == 0;
   int done = 0;
   if (!force_simt) {
-    const int rc = corr_volume_tc(f1, f2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st, &done);
+    const int rc = corr_volume_tc(f1, n1, f2, n2, idx1, idx2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st,
+                                  &done);
     if (rc != DBAF_OK) return rc;
     if (done >= levels) return DBAF_OK;
   }
   if (done == 0) {
     dim3 grid((HW + kTile - 1) / kTile, (HW + kTile - 1) / kTile, n);
-    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, C, HW, outs[0]);
+    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, idx1, idx2, C, HW, outs[0]);
     DBAF_LAUNCH_CHECK("k_volume_simt");
   }
   if (levels > 1) {
@@ -165,4 +162,54 @@ extern "C" int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, in
     DBAF_LAUNCH_CHECK("k_pyramid");
   }
   return DBAF_OK;
+}
+
+}  // namespace
+}  // namespace dbaf
+
+extern "C" size_t dbaf_corr_volume_workspace_bytes(int n, int C, int ht, int wd) {
+  return corr_volume_tc_workspace(n, n, C, ht, wd);
+}
+
+extern "C" int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, int n, int C, int ht, int wd,
+                                        int levels, void* const* out_host, void* workspace,
+                                        size_t workspace_bytes, void* stream) {
+  DBAF_REQUIRE(n >= 0 && C > 0 && ht > 0 && wd > 0, "bad sizes");
+  DBAF_REQUIRE(levels >= 1 && levels <= 4, "levels must be 1..4");
+  DBAF_REQUIRE(out_host != nullptr, "null output list");
+  if (n == 0) return DBAF_OK;
+  return volume_pyramid(static_cast<const __half*>(fmap1), n, static_cast<const __half*>(fmap2), n, nullptr, nullptr, n,
+                        C, ht, wd, levels, out_host, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" size_t dbaf_corr_volume_indexed_workspace_bytes(int n1, int n2, int C, int ht, int wd) {
+  return corr_volume_tc_workspace(n1, n2, C, ht, wd) + 256;   // + the index check flag
+}
+
+extern "C" int dbaf_corr_volume_pyramid_indexed(const void* fmaps1, int n1, const void* fmaps2, int n2,
+                                                const int32_t* ii, const int32_t* jj, int n_edges, int C, int ht,
+                                                int wd, int levels, void* const* out_host, void* workspace,
+                                                size_t workspace_bytes, void* stream) {
+  DBAF_REQUIRE(n1 > 0 && n2 > 0 && n_edges >= 0 && C > 0 && ht > 0 && wd > 0, "bad sizes");
+  DBAF_REQUIRE(levels >= 1 && levels <= 4, "levels must be 1..4");
+  DBAF_REQUIRE(out_host != nullptr && ii != nullptr && jj != nullptr, "null output list or index array");
+  if (n_edges == 0) return DBAF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  // an index outside its frame stack would read foreign memory: checked on the device before anything is computed
+  // when the caller gives scratch (the flag is read back, which synchronises the stream once)
+  size_t ws_bytes = workspace_bytes;
+  if (workspace != nullptr && workspace_bytes >= 256) {
+    int* flag = reinterpret_cast<int*>((reinterpret_cast<uintptr_t>(workspace) + workspace_bytes - 64) & ~(uintptr_t)63);
+    DBAF_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), st));
+    k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(ii, n_edges, n1, flag);
+    k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(jj, n_edges, n2, flag);
+    DBAF_LAUNCH_CHECK("k_check_index");
+    int bad = 0;
+    DBAF_CUDA(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+    DBAF_CUDA(cudaStreamSynchronize(st));
+    DBAF_REQUIRE(bad == 0, "frame index out of range");
+    ws_bytes = workspace_bytes - 256;
+  }
+  return volume_pyramid(static_cast<const __half*>(fmaps1), n1, static_cast<const __half*>(fmaps2), n2, ii, jj, n_edges,
+                        C, ht, wd, levels, out_host, workspace, ws_bytes, st);
 }

@@ -23,6 +23,8 @@
 
 #include <cuda.h>
 
+#include <algorithm>
+
 namespace dbaf {
 namespace {
 
@@ -177,7 +179,7 @@ template <bool FUSE>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
-            int HW, int m_tiles, Pyr out) {
+            int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
@@ -192,6 +194,8 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
   const int e = blockIdx.x / m_tiles;
   const int m0 = (blockIdx.x - e * m_tiles) * kBM;
   const int n_chunks = (HW + kBN - 1) / kBN;
+  // operand rows: the edge's own maps, or frames picked by index (video.fmaps[ii] / [jj], covisible_graph.py:129-130)
+  const int ea = idx1 ? idx1[e] : e, eb = idx2 ? idx2[e] : e;
 
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bars[0]), 1);
@@ -220,13 +224,13 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
     const uint32_t barA = smem_u32(&bars[0]), barB = smem_u32(&bars[1]), barFree = smem_u32(&bars[2]);
     mbar_expect_tx(barA, kSmemA);
-    tma_load_2d(smem_u32(sA), &mapA, barA, 0, e * HW + m0);
-    tma_load_2d(smem_u32(sA) + kBM * 128, &mapA, barA, kKBlock, e * HW + m0);
+    tma_load_2d(smem_u32(sA), &mapA, barA, 0, ea * HW + m0);
+    tma_load_2d(smem_u32(sA) + kBM * 128, &mapA, barA, kKBlock, ea * HW + m0);
     for (int c = 0; c < n_chunks; ++c) {
       mbar_wait(barFree, (c + 1) & 1);
       mbar_expect_tx(barB, kSmemB);
-      tma_load_2d(smem_u32(sB), &mapB, barB, 0, e * HW + c * kBN);
-      tma_load_2d(smem_u32(sB) + kBN * 128, &mapB, barB, kKBlock, e * HW + c * kBN);
+      tma_load_2d(smem_u32(sB), &mapB, barB, 0, eb * HW + c * kBN);
+      tma_load_2d(smem_u32(sB) + kBN * 128, &mapB, barB, kKBlock, eb * HW + c * kBN);
     }
     }
     __syncwarp();
@@ -460,27 +464,30 @@ int make_map(CUtensorMap* map, const __half* base, size_t rows, int box_rows) {
 
 }  // namespace
 
-size_t corr_volume_tc_workspace(int n, int C, int ht, int wd) {
-  // two pixel-major copies of the feature maps
-  return (size_t)2 * n * ht * wd * C * sizeof(__half) + 512;
+size_t corr_volume_tc_workspace(int n1, int n2, int C, int ht, int wd) {
+  // pixel-major copies of both sets of feature maps
+  return (size_t)(n1 + n2) * ht * wd * C * sizeof(__half) + 512;
 }
 
-int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int wd, int levels,
-                   __half* const* out, void* workspace, size_t workspace_bytes, cudaStream_t st, int* levels_done) {
+// f1 [n1,C,ht,wd], f2 [n2,C,ht,wd]; edge e correlates f1[idx1[e]] with f2[idx2[e]] (idx null: e itself).
+int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
+                   int ht, int wd, int levels, __half* const* out, void* workspace, size_t workspace_bytes,
+                   cudaStream_t st, int* levels_done) {
   *levels_done = 0;
   const int HW = ht * wd;
   if (C != kC) return DBAF_OK;                              // the SIMT kernel takes other channel counts
-  if (workspace == nullptr || workspace_bytes < corr_volume_tc_workspace(n, C, ht, wd)) return DBAF_OK;
-  if ((size_t)n * HW >= (size_t)1 << 31) return DBAF_OK;
+  if (workspace == nullptr || workspace_bytes < corr_volume_tc_workspace(n1, n2, C, ht, wd)) return DBAF_OK;
+  if ((size_t)n * HW >= (size_t)1 << 31 || (size_t)std::max(n1, n2) * HW >= (size_t)1 << 31) return DBAF_OK;
   __half* a_t = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
-  __half* b_t = a_t + (size_t)n * HW * C;
-  dim3 tg((HW + 31) / 32, C / 64, n);
-  k_to_pixel_major<<<tg, 256, 0, st>>>(f1, a_t, C, HW, 0.25f);   // fmap / 4.0 on both sides, dbaf/modules/corr.py:67-68
-  k_to_pixel_major<<<tg, 256, 0, st>>>(f2, b_t, C, HW, 0.25f);
+  __half* b_t = a_t + (size_t)n1 * HW * C;
+  const bool shared_src = f1 == f2 && n1 == n2;             // one set of frames on both sides: transpose it once
+  k_to_pixel_major<<<dim3((HW + 31) / 32, C / 64, n1), 256, 0, st>>>(f1, a_t, C, HW, 0.25f);   // fmap / 4.0, corr.py:67-68
+  if (shared_src) b_t = a_t;
+  else k_to_pixel_major<<<dim3((HW + 31) / 32, C / 64, n2), 256, 0, st>>>(f2, b_t, C, HW, 0.25f);
   DBAF_LAUNCH_CHECK("k_to_pixel_major");
   CUtensorMap mapA, mapB;
-  if (int rc = make_map(&mapA, a_t, (size_t)n * HW, kBM)) return rc;
-  if (int rc = make_map(&mapB, b_t, (size_t)n * HW, kBN)) return rc;
+  if (int rc = make_map(&mapA, a_t, (size_t)n1 * HW, kBM)) return rc;
+  if (int rc = make_map(&mapB, b_t, (size_t)n2 * HW, kBN)) return rc;
   const bool fuse = wd == 64 && ht % 8 == 0;
   const int m_tiles = (HW + kBM - 1) / kBM;
   CUtensorMap mapO0 = mapA, mapO1 = mapA;     // only the fused kernel stores through tensor maps
@@ -499,8 +506,8 @@ int corr_volume_tc(const __half* f1, const __half* f2, int n, int C, int ht, int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr);
-  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr);
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2);
   DBAF_LAUNCH_CHECK("k_volume_tc");
   // fused: all requested levels are written; otherwise only level 0 and the caller pools
   *levels_done = fuse ? levels : 1;

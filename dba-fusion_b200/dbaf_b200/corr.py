@@ -46,6 +46,20 @@ class CorrBlock:
             f1, f2 = f1.half(), f2.half()
         self.corr_pyramid = droid_backends.corr_volume_pyramid(f1, f2, num_levels)
 
+    @classmethod
+    def from_frames(cls, fmaps1, fmaps2, ii, jj, num_levels=4, radius=3):
+        """The construction of dbaf/covisible_graph.py:129-131, CorrBlock(video.fmaps[ii,0][None],
+        video.fmaps[jj,c][None]), without materialising the gathered maps: fmaps1 [n1,dim,ht,wd] and fmaps2
+        [n2,dim,ht,wd] are the per-frame stacks (e.g. video.fmaps[:,0] and video.fmaps[:,c]); same pyramid,
+        bit for bit."""
+        self = cls.__new__(cls)
+        self.num_levels, self.radius = num_levels, radius
+        f1 = fmaps1 if fmaps1.dtype == torch.float16 else fmaps1.half()
+        f2 = f1 if fmaps2 is fmaps1 else (fmaps2 if fmaps2.dtype == torch.float16 else fmaps2.half())
+        self.corr_pyramid = droid_backends.corr_volume_pyramid_indexed(f1.contiguous(), f2.contiguous(), ii, jj,
+                                                                       num_levels)
+        return self
+
     def __call__(self, coords):
         batch, num, ht, wd, _ = coords.shape
         coords = coords.permute(0, 1, 4, 2, 3).contiguous().view(batch * num, 2, ht, wd)

@@ -434,6 +434,33 @@ def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
     return outs
 
 
+def corr_volume_pyramid_indexed(fmaps1, fmaps2, ii, jj, num_levels=4):
+    """CorrBlock(video.fmaps[ii,0], video.fmaps[jj,c]) (dbaf/covisible_graph.py:129-131) without the gather:
+    fmaps1 [n1,C,ht,wd], fmaps2 [n2,C,ht,wd] float16 frame stacks (they may be the same tensor), ii/jj edge
+    lists -> list of `num_levels` tensors [E,ht,wd,ht>>l,wd>>l] float16, bit-identical to
+    corr_volume_pyramid(fmaps1[ii], fmaps2[jj])."""
+    _contig(fmaps1=fmaps1, fmaps2=fmaps2)
+    _cuda(torch.float16, fmaps1=fmaps1, fmaps2=fmaps2)
+    n1, C, ht, wd = fmaps1.shape
+    n2 = fmaps2.shape[0]
+    if fmaps2.shape[1:] != fmaps1.shape[1:]:
+        raise RuntimeError("fmaps1 and fmaps2 must agree in channels and size")
+    if ii.shape != jj.shape or ii.dim() != 1:
+        raise RuntimeError("ii and jj must be 1-D and of equal length")
+    ii32 = ii.to(device=fmaps1.device, dtype=torch.int32).contiguous()
+    jj32 = jj.to(device=fmaps1.device, dtype=torch.int32).contiguous()
+    E = ii32.numel()
+    outs = [torch.empty(E, ht, wd, ht >> l, wd >> l, dtype=torch.float16, device=fmaps1.device)
+            for l in range(num_levels)]
+    nbytes = lib.dbaf_corr_volume_indexed_workspace_bytes(n1, n2, C, ht, wd)
+    ws = torch.empty(max(1, nbytes), dtype=torch.uint8, device=fmaps1.device)
+    arr = (c_void_p * num_levels)(*[o.data_ptr() for o in outs])
+    check(lib.dbaf_corr_volume_pyramid_indexed(_p(fmaps1), n1, _p(fmaps2), n2, _p(ii32), _p(jj32), E, C, ht, wd,
+                                               num_levels, arr, _p(ws), nbytes, _stream()),
+          "dbaf_corr_volume_pyramid_indexed")
+    return outs
+
+
 def corr_lookup_pyramid(pyramid, coords, radius=3):
     """All levels of CorrBlock.__call__ (dbaf/modules/corr.py:40-50) in one launch.
     pyramid[l] [n,h1,w1,h2>>l,w2>>l]; coords [n,2,h1,w1] (level-0 pixels) ->

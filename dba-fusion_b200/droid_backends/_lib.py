@@ -41,6 +41,9 @@ SIGNATURES = {
     "dbaf_corr_volume_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "dbaf_corr_volume_pyramid": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int,
                                          ctypes.POINTER(c_void_p), P, c_size_t, P]),
+    "dbaf_corr_volume_indexed_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
+    "dbaf_corr_volume_pyramid_indexed": (c_int, [P, c_int, P, c_int, P, P, c_int, c_int, c_int, c_int, c_int,
+                                                 ctypes.POINTER(c_void_p), P, c_size_t, P]),
     "dbaf_ba_workspace_layout": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(BaLayout)]),
     "dbaf_ba_prepare": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "dbaf_ba_tables_noalloc": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P, P, P]),

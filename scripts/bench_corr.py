@@ -39,6 +39,14 @@ def ref_volume():
 res = {"config": cfg, "edges": n}
 res["volume_ms_ours"] = timeit(lambda: db.corr_volume_pyramid(f1, f2, 4), flush=flush)
 res["volume_ms_ref_torch"] = timeit(ref_volume, flush=flush)
+# the call the pipeline makes (dbaf/covisible_graph.py:129-131): gather by edge, then CorrBlock
+ii_t, jj_t = torch.from_numpy(w["ii"]).to(dev), torch.from_numpy(w["jj"]).to(dev)
+res["volume_indexed_ms_ours"] = timeit(lambda: db.corr_volume_pyramid_indexed(f, f, ii_t, jj_t, 4), flush=flush)
+def ref_gather_volume():
+    global f1, f2
+    f1, f2 = f[ii_t], f[jj_t]
+    return ref_volume()
+res["volume_indexed_ms_ref_torch"] = timeit(ref_gather_volume, flush=flush)
 pyr = db.corr_volume_pyramid(f1, f2, 4)
 res["lookup_ms_ours_fused"] = timeit(lambda: db.corr_lookup_pyramid(pyr, coords, 3), flush=flush)
 def per_level(mod):

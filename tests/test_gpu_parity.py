@@ -342,6 +342,37 @@ def test_volume_pyramid_vs_torch_reference(dev, db, synth, cfg, n):
         exact = torch.nn.functional.avg_pool2d(exact, 2, stride=2)
 
 
+@pytest.mark.parametrize("cfg", ["tiny", "c2", "c3"])
+@pytest.mark.parametrize("shared", [True, False])
+def test_volume_pyramid_indexed_equals_gathered(dev, db, synth, cfg, shared):
+    """dbaf_corr_volume_pyramid_indexed == dbaf_corr_volume_pyramid on fmaps[ii], fmaps[jj]
+    (dbaf/covisible_graph.py:129-131), bit for bit, for a shared frame stack and for two stacks."""
+    w = synth.make_window(cfg, seed=2)
+    P = w["poses"].shape[0]
+    fa = torch.from_numpy(synth.make_features(cfg, seed=5, n_frames=P)).to(dev)
+    fb = fa if shared else torch.from_numpy(synth.make_features(cfg, seed=6, n_frames=P + 1)).to(dev)
+    ii = torch.from_numpy(np.asarray(w["ii"]))[:10].to(dev)
+    jj = torch.from_numpy(np.asarray(w["jj"]))[:10].to(dev)
+    got = db.corr_volume_pyramid_indexed(fa, fb, ii, jj, 4)
+    want = db.corr_volume_pyramid(fa[ii].contiguous(), fb[jj].contiguous(), 4)
+    for l in range(4):
+        assert got[l].shape == want[l].shape
+        assert torch.equal(got[l].view(torch.int16), want[l].view(torch.int16)), (cfg, shared, l)
+    from dbaf_b200.corr import CorrBlock
+    blk = CorrBlock.from_frames(fa, fb, ii, jj)
+    assert all(torch.equal(a, b) for a, b in zip(blk.corr_pyramid, got))
+
+
+def test_volume_pyramid_indexed_rejects_bad_index(dev, db, synth):
+    fa = torch.from_numpy(synth.make_features("tiny", seed=5, n_frames=3)).to(dev)
+    ii = torch.tensor([0, 1], device=dev)
+    with pytest.raises(RuntimeError, match="out of range"):
+        db.corr_volume_pyramid_indexed(fa, fa, ii, torch.tensor([1, 3], device=dev), 2)
+    with pytest.raises(RuntimeError, match="out of range"):
+        db.corr_volume_pyramid_indexed(fa, fa, torch.tensor([-1, 0], device=dev), ii, 2)
+    db.corr_volume_pyramid_indexed(fa, fa, ii, torch.tensor([1, 2], device=dev), 2)
+
+
 def test_altcorr_vs_oracle_and_volume_path(dev, db, oracle, synth):
     f1, f2, coords = _corr_case(synth, "tiny", 3)
     af1 = np.ascontiguousarray((f1.astype(np.float32) / 4.0).transpose(0, 2, 3, 1))
