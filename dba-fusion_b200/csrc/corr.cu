@@ -11,7 +11,11 @@
 //
 // fp16 arithmetic reproduces the reference's rounding sequence exactly
 // (src/correlation_kernels.cu:43-65: weights rounded to half, every product and every
-// accumulate rounded to half, taps visited x-offset outer / y-offset inner).
+// accumulate rounded to half, taps visited x-offset outer / y-offset inner).  The reference
+// does each at::Half operation as "convert to float, operate, round to half"; for + and * that
+// double rounding is innocuous (24 >= 2*11 + 2 significand bits), so native mul.rn.f16x2 /
+// add.rn.f16x2 give the same bits.  Two neighbouring x offsets share one packed accumulator;
+// every accumulator still receives its four contributions in the reference's order.
 #include "common.cuh"
 
 namespace dbaf {
@@ -33,6 +37,22 @@ __device__ __forceinline__ float round_h(float x) { return __half2float(__float2
 __device__ __forceinline__ int window_base(float floored, int r) {
   const int v = (int)floored;
   return max(-(1 << 24), min(1 << 24, v)) - r;
+}
+
+// non-contractable packed half arithmetic (.rn forbids fusing the pair into an fma)
+__device__ __forceinline__ unsigned int hmul2_rn(unsigned int a, unsigned int b) {
+  unsigned int d;
+  asm("mul.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ unsigned int hadd2_rn(unsigned int a, unsigned int b) {
+  unsigned int d;
+  asm("add.rn.f16x2 %0, %1, %2;" : "=r"(d) : "r"(a), "r"(b));
+  return d;
+}
+__device__ __forceinline__ unsigned int bcast_h(float w) {
+  const unsigned int h = __half_as_ushort(__float2half_rn(w));
+  return h | (h << 16);
 }
 
 __device__ __forceinline__ unsigned long long funnel64(unsigned long long lo, unsigned long long hi, int sh) {
@@ -92,22 +112,23 @@ k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, in
   const float dx = x0 - fx0, dy = y0 - fy0;
   const int bx = window_base(fx0, R), by = window_base(fy0, R);
 
-  float acc[RD][RD];
-#pragma unroll
-  for (int a = 0; a < RD; ++a)
-#pragma unroll
-    for (int b = 0; b < RD; ++b) acc[a][b] = 0.f;
-
   const long long slab = ((long long)e * HW1 + p) * (long long)(h2 * w2);
   const long long total = (long long)n * HW1 * (long long)(h2 * w2);
+  // selected with compares so that the pointer table stays in the parameter bank (no local copy)
+  const void* volp = lv.vol[0];
+#pragma unroll
+  for (int l = 1; l < kMaxLevels; ++l)
+    if (level == l) volp = lv.vol[l];
+  T* o = out + ((size_t)e * ch_total + (size_t)level * RD * RD) * HW1 + p;
 
   if constexpr (sizeof(T) == 2) {
-    const __half* vol = static_cast<const __half*>(lv.vol[level]);
+    const __half* vol = static_cast<const __half*>(volp);
     const bool vec_ok = (reinterpret_cast<size_t>(vol) & 15) == 0;
-    // weights rounded to half, as scalar_t(dx*dy) does
-    const float w11 = round_h(dx * dy), w10 = round_h(dx * (1.0f - dy));
-    const float w01 = round_h((1.0f - dx) * dy), w00 = round_h((1.0f - dx) * (1.0f - dy));
-    unsigned int taps[RD + 1][(RD + 1) / 2];   // [row j][packed x]
+    // weights rounded to half, as scalar_t(dx*dy) does; both lanes of a packed register carry the same weight
+    const unsigned int w11 = bcast_h(dx * dy), w10 = bcast_h(dx * (1.0f - dy));
+    const unsigned int w01 = bcast_h((1.0f - dx) * dy), w00 = bcast_h((1.0f - dx) * (1.0f - dy));
+    static_assert(RD + 1 == 8, "row loader is written for radius 3");
+    unsigned int taps[RD + 1][(RD + 1) / 2];   // [window row][x pair]: lanes = x offsets 2k, 2k+1
     unsigned int rowmask = 0;
 #pragma unroll
     for (int j = 0; j < RD + 1; ++j) {
@@ -115,30 +136,50 @@ k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, in
       const bool rok = y1 >= 0 && y1 < h2;
       if (rok) {
         rowmask |= 1u << j;
-        static_assert(RD + 1 == 8, "row loader is written for radius 3");
         load_row8_h(vol, slab + (long long)y1 * w2, bx, total, vec_ok, w2, taps[j]);
       } else {
 #pragma unroll
         for (int i = 0; i < (RD + 1) / 2; ++i) taps[j][i] = 0u;
       }
     }
+    // lane masks of the taps inside the image: aligned pairs (x = 2k, 2k+1) and shifted pairs (2k+1, 2k+2)
+    unsigned int m_al[4], m_sh[4];
 #pragma unroll
-    for (int i = 0; i < RD + 1; ++i) {
-      const int x1 = bx + i;
-      const bool cok = x1 >= 0 && x1 < w2;
+    for (int k = 0; k < 4; ++k) {
+      const unsigned int c0 = (bx + 2 * k >= 0 && bx + 2 * k < w2) ? 0xffffu : 0u;
+      const unsigned int c1 = (bx + 2 * k + 1 >= 0 && bx + 2 * k + 1 < w2) ? 0xffffu : 0u;
+      const unsigned int c2 = (bx + 2 * k + 2 >= 0 && bx + 2 * k + 2 < w2) ? 0xffffu : 0u;
+      m_al[k] = c0 | (c1 << 16);
+      m_sh[k] = c1 | (c2 << 16);
+    }
+    unsigned short* oh = reinterpret_cast<unsigned short*>(o);
+    // output (x offset a, y offset b) = (((0 + w00 s[a][b]) + w01 s[a][b+1]) + w10 s[a+1][b]) + w11 s[a+1][b+1],
+    // a contribution is skipped (not added as zero) when its tap lies outside the image
 #pragma unroll
-      for (int j = 0; j < RD + 1; ++j) {
-        const bool inb = cok && ((rowmask >> j) & 1u);
-        const unsigned int pk = taps[j][i >> 1];
-        const float s = h2f((unsigned short)((i & 1) ? (pk >> 16) : (pk & 0xffffu)));
-        if (i > 0 && j > 0) { const float r = round_h(acc[i - 1][j - 1] + round_h(s * w11)); acc[i - 1][j - 1] = inb ? r : acc[i - 1][j - 1]; }
-        if (i > 0 && j < RD) { const float r = round_h(acc[i - 1][j] + round_h(s * w10)); acc[i - 1][j] = inb ? r : acc[i - 1][j]; }
-        if (i < RD && j > 0) { const float r = round_h(acc[i][j - 1] + round_h(s * w01)); acc[i][j - 1] = inb ? r : acc[i][j - 1]; }
-        if (i < RD && j < RD) { const float r = round_h(acc[i][j] + round_h(s * w00)); acc[i][j] = inb ? r : acc[i][j]; }
+    for (int b = 0; b < RD; ++b) {
+      const unsigned int r0 = ((rowmask >> b) & 1u) ? 0xffffffffu : 0u;
+      const unsigned int r1 = ((rowmask >> (b + 1)) & 1u) ? 0xffffffffu : 0u;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const unsigned int a0 = taps[b][k], a1 = taps[b + 1][k];
+        const unsigned int s0 = __byte_perm(a0, k < 3 ? taps[b][k + 1] : 0u, 0x5432);
+        const unsigned int s1 = __byte_perm(a1, k < 3 ? taps[b + 1][k + 1] : 0u, 0x5432);
+        unsigned int acc = 0u, m, r;
+        m = m_al[k] & r0; r = hadd2_rn(acc, hmul2_rn(a0, w00)); acc = (r & m) | (acc & ~m);
+        m = m_al[k] & r1; r = hadd2_rn(acc, hmul2_rn(a1, w01)); acc = (r & m) | (acc & ~m);
+        m = m_sh[k] & r0; r = hadd2_rn(acc, hmul2_rn(s0, w10)); acc = (r & m) | (acc & ~m);
+        m = m_sh[k] & r1; r = hadd2_rn(acc, hmul2_rn(s1, w11)); acc = (r & m) | (acc & ~m);
+        oh[(size_t)((2 * k) * RD + b) * HW1] = (unsigned short)(acc & 0xffffu);
+        if (2 * k + 1 < RD) oh[(size_t)((2 * k + 1) * RD + b) * HW1] = (unsigned short)(acc >> 16);
       }
     }
   } else {
-    const float* vol = static_cast<const float*>(lv.vol[level]);
+    const float* vol = static_cast<const float*>(volp);
+    float acc[RD][RD];
+#pragma unroll
+    for (int a = 0; a < RD; ++a)
+#pragma unroll
+      for (int b = 0; b < RD; ++b) acc[a][b] = 0.f;
     const float w11 = dx * dy, w10 = dx * (1.0f - dy);
     const float w01 = (1.0f - dx) * dy, w00 = (1.0f - dx) * (1.0f - dy);
 #pragma unroll
@@ -155,16 +196,12 @@ k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, in
         if (i < RD && j < RD) acc[i][j] = inb ? fmaf(s, w00, acc[i][j]) : acc[i][j];
       }
     }
+#pragma unroll
+    for (int a = 0; a < RD; ++a)
+#pragma unroll
+      for (int b = 0; b < RD; ++b) o[(size_t)(a * RD + b) * HW1] = acc[a][b];
   }
 
-  T* o = out + ((size_t)e * ch_total + (size_t)level * RD * RD) * HW1 + p;
-#pragma unroll
-  for (int a = 0; a < RD; ++a)
-#pragma unroll
-    for (int b = 0; b < RD; ++b) {
-      if constexpr (sizeof(T) == 2) o[(size_t)(a * RD + b) * HW1] = __float2half_rn(acc[a][b]);
-      else o[(size_t)(a * RD + b) * HW1] = acc[a][b];
-    }
 }
 
 // Generic-radius fallback (any r): same arithmetic, taps loaded one by one, outputs
