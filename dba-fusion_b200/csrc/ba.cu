@@ -10,6 +10,10 @@
 //   Q, w float32 [K,HW]                    inverse depth Hessian and depth gradient per depth frame
 //   kx, kk_exp, csr_*, srow_*  int32       graph tables
 #include "common.cuh"
+#include "tc_ptx.cuh"
+
+#include <cstdlib>
+#include <cstring>
 
 #include <algorithm>
 
@@ -640,6 +644,7 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
 #include "ba_fast.cuh"
 #include "ba_banded.cuh"
 #include "ba_lin2.cuh"
+#include "ba_schur_tc.cuh"
 
 int check_dims(int N, int E, int t0, int t1, int ht, int wd) {
   DBAF_REQUIRE(N > 0 && E >= 0 && ht > 0 && wd > 0, "non-positive size");
@@ -725,9 +730,29 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
       DBAF_CUDA(cudaFuncSetAttribute(k_schur_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
       schur_attr[dev_id & 63] = true;
     }
+    // dense graphs (global BA: ~20 out-edges per frame) go to the tensor-core kernel, whose cost does not grow
+    // with the square of the row count; DBAF_SCHUR_IMPL=simt keeps everything on the fp32 SIMT kernels
+    const char* schur_impl = std::getenv("DBAF_SCHUR_IMPL");
+    const bool simt_only = schur_impl != nullptr && std::strcmp(schur_impl, "simt") == 0;
+    const bool use_tc = !simt_only && E >= 4 * k_cap && HW % 32 == 0;   // 128-byte bulk copies need whole slices
+    const int tc_min_m = 8;
+    if (use_tc) {
+      static bool tc_attr[64] = {};
+      if (!tc_attr[dev_id & 63]) {
+        DBAF_CUDA(cudaFuncSetAttribute(k_schur_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStcSmemBytes));
+        tc_attr[dev_id & 63] = true;
+      }
+      // one CTA per frame when there are enough frames to fill the machine, else split the pixels
+      int splits = std::max(1, std::min((2 * 148 + k_cap - 1) / k_cap, (HW + 255) / 256));
+      const int St = (((HW + splits - 1) / splits) + 31) & ~31;
+      splits = (HW + St - 1) / St;
+      k_schur_tc<<<dim3(splits, k_cap), kStcThreads, kStcSmemBytes, st>>>(jj, t0, P, HW, St, tc_min_m, k_lo, k_hi, ws);
+      DBAF_LAUNCH_CHECK("k_schur_tc");
+    }
     const int S = 256;
     dim3 sgrid((HW + S - 1) / S, k_cap);
-    k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, ws);
+    k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, use_tc ? tc_min_m : 1,
+                                                           use_tc ? kStcMaxM : 0, ws);
     DBAF_LAUNCH_CHECK("k_schur_smem");
     if (E + 1 > kSchurMaxRows) {
       // a depth frame can only have more than kSchurMaxRows rows if the graph has that many edges

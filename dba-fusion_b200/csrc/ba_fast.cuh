@@ -28,7 +28,8 @@ constexpr int kSchurMaxRows = kSchurCapFloats / (6 * 32);
 constexpr size_t kSchurSmemBytes = (size_t)(kSchurCapFloats + 2 * 256) * 4 + 2 * kSchurMaxRows * 4;
 
 __global__ void __launch_bounds__(kThreads)
-k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k_lo, int k_hi, Ws ws) {
+k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k_lo, int k_hi, int skip_lo, int skip_hi,
+             Ws ws) {
   extern __shared__ float smf[];
   const int k = k_lo + blockIdx.y;
   const int K = ws.info[0];
@@ -37,6 +38,7 @@ k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k
   const int r_lo = ws.srow_ptr[k];
   const int m = ws.srow_ptr[k + 1] - r_lo;
   if (m == 0 || m > kSchurMaxRows) return;
+  if (m >= skip_lo && m <= skip_hi) return;      // taken by k_schur_tc
   const int rows6 = 6 * m;
   const int tp = min(256, (kSchurCapFloats / rows6) & ~31);
   float* Es = smf;                                // [rows6][tp]

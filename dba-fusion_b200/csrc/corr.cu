@@ -28,7 +28,6 @@ struct LevelPtrs {
   const void* vol[kMaxLevels];
 };
 
-__device__ __forceinline__ float h2f(unsigned short b) { return __half2float(__ushort_as_half(b)); }
 __device__ __forceinline__ float round_h(float x) { return __half2float(__float2half_rn(x)); }
 
 // floor(x) as an int the way the reference converts it (saturating, NaN -> 0), then clamped to

@@ -20,12 +20,13 @@ CONFIGS = {
     "c4": (64, 64, 12, 36, (23.87, 23.87, 31.87, 32.11)),
     "c5": (64, 64, 1000, 20000, (23.87, 23.87, 31.87, 32.11)),
     "tiny": (16, 24, 5, 10, (12.0, 12.5, 11.5, 7.5)),
+    "g24": (64, 64, 24, 480, (23.87, 23.87, 31.87, 32.11)),  # dense banded graph at the full 64x64 frame size
     "g40": (24, 32, 40, 160, (14.0, 14.5, 15.5, 11.5)),     # small banded global graph (6P = 240 > 160)
 }
 
 
 # fixed per-config seed slots: the golden fixtures depend on them, so new configs append
-_SEED_SLOT = {"c1": 0, "c2": 1, "c2_real": 2, "c3": 3, "c4": 4, "c5": 5, "tiny": 6, "g40": 7}
+_SEED_SLOT = {"c1": 0, "c2": 1, "c2_real": 2, "c3": 3, "c4": 4, "c5": 5, "tiny": 6, "g40": 7, "g24": 8}
 
 
 def _qmul(a, b):
@@ -128,7 +129,7 @@ def reproject(poses, disps, intr, ii, jj):
 
 
 def make_window(config="c2", seed=0, t0=1, sensor_frac=0.0, near_frac=0.0, stereo_edges=0,
-                pose_noise=0.01, n_extra_frames=0, heuristics=False, graph="frontend"):
+                pose_noise=0.01, n_extra_frames=0, heuristics=False, graph="frontend", reach=None):
     """Returns a dict of float32/int64 numpy arrays: poses [N,7], disps, disps_sens [N,ht,wd],
     intrinsics [4], targets, weights [E,2,ht,wd], eta [K,ht,wd], ii, jj [E], t0, t1, plus the
     ground truth poses_gt / disps_gt."""
@@ -138,7 +139,7 @@ def make_window(config="c2", seed=0, t0=1, sensor_frac=0.0, near_frac=0.0, stere
     poses_gt = trajectory(rng, n)
     disps_gt = _smooth(rng, (n, ht, wd), 0.3, 2.0)
     if graph == "banded":
-        ii, jj = banded_graph(n, reach=max(1, E // (2 * n)))
+        ii, jj = banded_graph(n, reach=reach or max(1, E // (2 * n)))
     else:
         ii, jj = frame_graph(rng, n, E, t0=t0)
     if stereo_edges:

@@ -153,6 +153,44 @@ def test_large_window_solvers(dev, db, oracle, synth, band_hint):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("reach", [4, 6, 10])
+def test_tensor_core_schur_matches_simt_and_oracle(dev, db, oracle, synth, monkeypatch, reach):
+    """Dense graphs (>= 8 row blocks per depth frame) take k_schur_tc (TF32 x3 on tcgen05): same reduced
+    system as the fp32 SIMT kernels (EEt6x6 / Ev6x1 of src/droid_kernels.cu:1046-1138) and as the float64
+    oracle."""
+    w = synth.make_window("g40", seed=3, graph="banded", reach=reach)
+    assert len(w["ii"]) >= 4 * 40
+
+    def system(impl):
+        if impl:
+            monkeypatch.setenv("DBAF_SCHUR_IMPL", impl)
+        else:
+            monkeypatch.delenv("DBAF_SCHUR_IMPL", raising=False)
+        t = to_torch(w, dev)
+        win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                         t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+        win.prepare()
+        win.linearize(0.05)
+        n = win.n
+        hv = win.Hv().cpu().numpy()
+        return hv[:n * n].reshape(n, n).copy(), hv[n * n:].copy()
+
+    H_tc, v_tc = system(None)
+    H_si, v_si = system("simt")
+    assert not np.array_equal(H_tc, H_si)              # the two paths really are different kernels
+    assert relerr(H_tc, H_tc.T) < 1e-6
+    tr = []
+    p, d = w["poses"].astype(np.float64), w["disps"].astype(np.float64)
+    oracle.ba(p, d, w["intrinsics"], w["disps_sens"], w["targets"], w["weights"], w["eta"], w["ii"], w["jj"],
+              w["t0"], w["t1"], 1, 1e-4, 0.1, False, dtype=np.float64, trace=tr)
+    H64, v64 = tr[0]["H"], tr[0]["v"]
+    # the tensor-core path is as close to the float64 system as the fp32 SIMT path is
+    assert relerr(H_tc, H64) < max(2e-6, 2 * relerr(H_si, H64)), (relerr(H_tc, H64), relerr(H_si, H64))
+    assert relerr(v_tc, v64) < max(2e-6, 2 * relerr(v_si, v64)), (relerr(v_tc, v64), relerr(v_si, v64))
+    assert relerr(H_tc, H_si) < 1e-5 and relerr(v_tc, v_si) < 1e-5
+
+
+@pytest.mark.gpu
 def test_global_ba_single_rank_matches_oracle(dev, db, oracle, synth):
     from dbaf_b200 import global_ba
     w = synth.make_window("g40", seed=2, graph="banded")
