@@ -798,8 +798,36 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       DBAF_CUDA(cudaFuncSetAttribute(k_solve_banded, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
       band_attr[dev_id & 63] = true;
     }
-    k_solve_banded<<<1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, ws);
+    BandPlan plan{};
+    const char* band_impl = std::getenv("DBAF_BAND_IMPL");       // "single" keeps the one-CTA sweep (tests)
+    const bool single = band_impl != nullptr && std::strcmp(band_impl, "single") == 0;
+    if (!single && P >= kBandTwistMinP && P >= 3 * B + 2) {
+      // two sweeps meeting at the separator [m, m+B)
+      const int m = (P - B) / 2;
+      plan.twisted = 1;
+      plan.m = m;
+      plan.part[0] = BandPart{0, m + B, m, 0};
+      plan.part[1] = BandPart{1, P - m, P - m - B, band_store_doubles(m + B, B)};
+      plan.sep = plan.part[1].store + band_store_doubles(P - m, B);
+    } else {
+      plan.part[0] = BandPart{0, P, P, 0};
+      plan.part[1] = plan.part[0];
+    }
+    k_solve_banded<<<plan.twisted ? 2 : 1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
     DBAF_LAUNCH_CHECK("k_solve_banded");
+    if (plan.twisted) {
+      const int ns = 6 * B;
+      const size_t ssm = ((size_t)(ns + 1) * (ns | 1) + 2 * ns) * sizeof(double);
+      static bool sep_attr[64] = {};
+      if (!sep_attr[dev_id & 63]) {
+        DBAF_CUDA(cudaFuncSetAttribute(k_band_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+        sep_attr[dev_id & 63] = true;
+      }
+      k_band_sep<<<1, kThreads, ssm, st>>>(P, B, lm, ep, plan, ws);
+      DBAF_LAUNCH_CHECK("k_band_sep");
+      k_band_back<<<2, kBandThreads, 0, st>>>(P, B, plan, ws);
+      DBAF_LAUNCH_CHECK("k_band_back");
+    }
     if (rezero) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, ((size_t)n * n + n) * 8, st));
   } else {
     k_solve<<<1, kThreads, 0, st>>>(n, lm, ep, prior, prior_rows, prior_cols, 0, ws);

@@ -10,9 +10,35 @@
 // back-substitution walks in reverse.  6000 x 6000 with B = 20: 1000 steps of ~45k FMAs instead
 // of 72 GFLOP dense.  The reference solves this system on one CPU core with Eigen::SimplicialLLT
 // (src/droid_kernels.cu:1248-1269).
+//
+// Long chains are factorised from both ends at once ("twisted" factorisation): CTA 0 eliminates blocks
+// 0 .. m-1 top down, CTA 1 eliminates blocks P-1 .. m+B bottom up (the same sweep on the block-reversed
+// ordering, read straight from the symmetric H).  The two parts are not coupled to each other (they are
+// more than B blocks apart), both only touch the B-block separator [m, m+B) in between.  Each CTA leaves
+// its updated copy of the separator in global memory; k_band_sep adds them (S = S_top + S_bottom - A_ss),
+// solves the dense 6B x 6B system with the shared-memory Cholesky of ba_fast.cuh, and k_band_back runs the
+// two back-substitutions outwards in parallel.  Same arithmetic, half the serial pivot chain.
 #pragma once
 
 constexpr int kBandThreads = 512;
+constexpr int kBandTwistMinP = 64;   // below this the single sweep is just as fast
+
+// One sweep of the (possibly reversed) chain: logical block I is physical block  rev ? P-1-I : I.
+struct BandPart {
+  int rev;               // 1: bottom-up sweep
+  int Plog;              // logical size of this part's leading submatrix (eliminated blocks + separator)
+  int n_elim;            // number of block columns this sweep eliminates
+  long long store;       // offset (doubles) of this part's band store inside ws.Lfac
+};
+struct BandPlan {
+  int twisted;           // 0: one CTA, everything (including the back-substitution) in k_solve_banded
+  int m;                 // first physical block of the separator
+  BandPart part[2];
+  long long sep;         // offset (doubles) of the separator exchange area inside ws.Lfac:
+                         // 2 x (B*B*36 window dump + 6B rhs dump), 6B solution, 4 flags
+};
+__host__ __device__ inline long long band_store_doubles(int Plog, int B) { return (long long)Plog * (B + 1) * 36 + 12LL * Plog; }
+__host__ __device__ inline long long band_dump_doubles(int B) { return (long long)B * B * 36 + 6LL * B; }
 constexpr int kBandMaxB = 25;      // (B+2)^2 blocks * 288 B must fit in shared memory
 
 __device__ __forceinline__ double warp_sum_d(double v) {
@@ -21,12 +47,113 @@ __device__ __forceinline__ double warp_sum_d(double v) {
   return v;
 }
 
-// Lband: [P][B+1][36] (block d = I-J of column J, row-major 6x6), then dinv [6P], then y [6P].
+// Back-substitution L^T x = y of one part, bottom up, right-looking: once x_J is known every pending
+// right-hand side above it is updated, y_I -= L_{J,I}^T x_J (I = J-B .. J-1).  The blocks of block row J of
+// L, the next diagonal block and the next incoming y row are fetched one step ahead, so a step is one short
+// serial 6x6 solve + one parallel rank-6 update.  Rows J >= n_elim are not solved: their x comes from `xsep`
+// (the separator solution, physical order, separator-local) and only the update is applied.
+__device__ void band_backsub(int Pphys, int B, const BandPart& pt, int m, const double* __restrict__ xsep,
+                             double* yw, double* dbuf, double* ibuf, double* xs, Ws ws) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int P = pt.Plog, NB = B + 2;
+  const double* Lband = ws.Lfac + pt.store;
+  const double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
+  const double* y_g = dinv_g + 6 * P;
+  auto phys = [&](int I) { return pt.rev ? Pphys - 1 - I : I; };
+  auto row_block = [&](int J, int t) {             // thread t's column c of L_{J,I}, I = J-1-t/6
+    return Lband + ((size_t)(J - 1 - t / 6) * (B + 1) + (1 + t / 6)) * 36 + (t % 6);
+  };
+  for (int e = tid; e < NB * 6; e += nt) {
+    const int I = P - 1 - e / 6;                   // rows P-1 .. P-NB
+    if (I >= 0 && e / 6 <= B) yw[(I % NB) * 6 + e % 6] = I < pt.n_elim ? y_g[6 * I + e % 6] : 0.0;
+  }
+  if (P - 1 < pt.n_elim) {
+    if (tid < 36) dbuf[((P - 1) & 1) * 36 + tid] = Lband[((size_t)(P - 1) * (B + 1)) * 36 + tid];
+    if (tid < 6) ibuf[((P - 1) & 1) * 6 + tid] = dinv_g[6 * (P - 1) + tid];
+  }
+  double cur[6];
+  {
+    const int nab = min(B, P - 1);
+    if (tid < nab * 6) {
+      const bool have = P - 2 - tid / 6 < pt.n_elim;             // column block I of L_{J,I} was eliminated
+      const double* q = row_block(P - 1, tid);
+#pragma unroll
+      for (int r = 0; r < 6; ++r) cur[r] = have ? q[r * 6] : 0.0;
+    }
+  }
+  __syncthreads();
+  for (int J = P - 1; J >= 0; --J) {
+    if (tid == 0) {
+      double x[6];
+      if (J >= pt.n_elim) {
+#pragma unroll
+        for (int c = 0; c < 6; ++c) x[c] = xsep[6 * (phys(J) - m) + c];
+      } else {
+        const double* L = dbuf + (J & 1) * 36;
+        const double* di = ibuf + (J & 1) * 6;
+        double l[6][6];
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          x[r] = yw[(J % NB) * 6 + r];
+#pragma unroll
+          for (int c = 0; c < 6; ++c)
+            if (c < r) l[r][c] = L[r * 6 + c];
+        }
+#pragma unroll
+        for (int c = 5; c >= 0; --c) {
+          double sum = x[c];
+#pragma unroll
+          for (int k = 0; k < 6; ++k)
+            if (k > c) sum -= l[k][c] * x[k];
+          x[c] = sum * di[c];
+        }
+#pragma unroll
+        for (int c = 0; c < 6; ++c) ws.dx[6 * phys(J) + c] = (float)x[c];
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) xs[c] = x[c];
+    }
+    __syncthreads();
+    const int nab = min(B, J);                     // rows above J inside the band
+    double nxt[6];
+    if (tid < nab * 6) {
+      double sum = 0.0;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) sum += cur[r] * xs[r];
+      yw[((J - 1 - tid / 6) % NB) * 6 + tid % 6] -= sum;
+    }
+    if (J > 0) {
+      const int nab2 = min(B, J - 1);
+      if (tid < nab2 * 6) {
+        const bool have = J - 2 - tid / 6 < pt.n_elim;
+        const double* q = row_block(J - 1, tid);
+#pragma unroll
+        for (int r = 0; r < 6; ++r) nxt[r] = have ? q[r * 6] : 0.0;
+      }
+      const int u = tid - (nt - 64);               // the last two warps fetch the next diagonal block etc.
+      if (J - 1 < pt.n_elim) {
+        if (u >= 0 && u < 36) dbuf[((J - 1) & 1) * 36 + u] = Lband[((size_t)(J - 1) * (B + 1)) * 36 + u];
+        if (u >= 36 && u < 42) ibuf[((J - 1) & 1) * 6 + (u - 36)] = dinv_g[6 * (J - 1) + (u - 36)];
+      }
+      const int Iin = J - 1 - B;                   // row entering the window for step J-1
+      if (u >= 42 && u < 48 && Iin >= 0) yw[(Iin % NB) * 6 + (u - 42)] = Iin < pt.n_elim ? y_g[6 * Iin + (u - 42)] : 0.0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 6; ++r) cur[r] = nxt[r];
+  }
+}
+
+// Band store of a part: [Plog][B+1][36] (block d = I-J of column J, row-major 6x6), then dinv [6 Plog],
+// then y [6 Plog].
 __global__ void __launch_bounds__(kBandThreads)
-k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
+k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, Ws ws) {
   extern __shared__ double smb[];
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, wid = tid >> 5;
-  const int n = 6 * P;
+  (void)lane; (void)wid;
+  const BandPart pt = plan.part[blockIdx.x];
+  const int P = pt.Plog;                             // logical size seen by this sweep
+  const int n = 6 * Pphys;                           // leading dimension of H
   const int NB = B + 2;
   double* Wd = smb;                                  // NB x NB blocks of 36
   double* yw = Wd + (size_t)NB * NB * 36;            // NB x 6 (right-hand side window, later x window)
@@ -34,9 +161,11 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
   double* dj = Ljj + 72;                             // 2 x 6 (1 / diag), double-buffered like Ljj (2 x 36)
   double* sred = dj + 12;                            // 8 (back-substitution partial sums)
   __shared__ int fail;
-  double* Lband = ws.Lfac;
+  double* Lband = ws.Lfac + pt.store;
   double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
-  double* y_g = dinv_g + n;
+  double* y_g = dinv_g + 6 * P;
+  // logical -> physical block index: p0 + sd * I
+  const int p0 = pt.rev ? Pphys - 1 : 0, sd = pt.rev ? -1 : 1;
   auto slot = [&](int I, int K) { return Wd + ((size_t)(I % NB) * NB + (K % NB)) * 36; };
   const double epd = (double)ep, lmd = (double)lm;
 
@@ -47,11 +176,11 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
     if (e < nb * 36) {
       const int b = e / 36, rc = e - b * 36, r = rc / 6, c = rc - r * 6;
       const int K = I - (nb - 1) + b;
-      double a = ws.H[(size_t)(6 * I + r) * n + 6 * K + c];
+      double a = ws.H[(size_t)(6 * (p0 + sd * I) + r) * n + 6 * (p0 + sd * K) + c];
       if (K == I && r == c) a += epd + lmd * a;
       return a;
     }
-    return ws.v[6 * I + (e - nb * 36)];
+    return ws.v[6 * (p0 + sd * I) + (e - nb * 36)];
   };
   auto place = [&](int I, int e, double a) {
     const int nb = min(I, B) + 1;
@@ -67,7 +196,16 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
   // buffer J & 1.  Runs on one whole warp: 21 lanes first apply the pending rank-6 update of the block
   // (`upd` = panel block L_{J,J-1}, or nullptr) in parallel, lane 0 then runs the serial pivot chain in
   // registers, and all lanes copy the results to the band store in global memory.
-  auto factor_diag = [&](int J, const double* upd, int ln) {
+#ifdef DBAF_BAND_PROFILE
+  long long fd[5] = {0, 0, 0, 0, 0};
+#endif
+  auto factor_diag = [&](int J, const double* upd, int ln, bool factorise) {
+#ifdef DBAF_BAND_PROFILE
+    long long f0 = clock64(), f1;
+#define FD_TICK(i) do { f1 = clock64(); fd[i] += f1 - f0; f0 = f1; } while (0)
+#else
+#define FD_TICK(i) do {} while (0)
+#endif
     double* A = slot(J, J);
     if (upd && ln < 21) {
       int r, c;
@@ -78,6 +216,8 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
       A[r * 6 + c] -= sum;
     }
     __syncwarp();
+    FD_TICK(0);
+    if (!factorise) return;                           // first separator block: updated, never eliminated here
     double* Lj = Ljj + (J & 1) * 36;
     double* dd = dj + (J & 1) * 6;
     if (ln == 0) {
@@ -110,6 +250,7 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
           }
       }
       if (bad) fail = 1;
+      FD_TICK(1);
       double y[6];
 #pragma unroll
       for (int r = 0; r < 6; ++r) {
@@ -126,28 +267,32 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
 #pragma unroll
         for (int c = 0; c < 6; ++c) Lj[r * 6 + c] = c <= r ? a[r][c] : 0.0;
       }
+      FD_TICK(2);
     }
     __syncwarp();
+    FD_TICK(3);
     // band store (needed again only by the back-substitution)
     for (int e = ln; e < 36; e += 32) Lband[((size_t)J * (B + 1)) * 36 + e] = Lj[e];
     if (ln < 6) {
       y_g[6 * J + ln] = yw[(J % NB) * 6 + ln];
       dinv_g[6 * J + ln] = dd[ln];
     }
+    FD_TICK(4);
   };
 
   if (tid == 0) fail = 0;
   for (int I = 0; I <= min(B, P - 1); ++I)
     for (int e = tid; e < row_elems(I); e += nt) place(I, e, fetch(I, e));
   __syncthreads();
-  if (tid >= nt - 32) factor_diag(0, nullptr, tid - (nt - 32));
+  if (tid >= nt - 32 && pt.n_elim > 0) factor_diag(0, nullptr, tid - (nt - 32), true);
   __syncthreads();
 
   const int nwork = nt - 32;                         // the last warp runs the look-ahead factorisation
   // Incoming rows are always full (B+1 blocks + rhs) inside the loop, so each thread's two elements keep a
   // fixed position inside the row: only the row index moves (pointer += 6n+6 per step).
   int pf_kind[2], pf_b[2], pf_rc[2];
-  size_t pf_off[2];
+  long long pf_off[2];
+  const long long pf_stride = (long long)sd * (6LL * n + 6);
 #pragma unroll
   for (int u = 0; u < 2; ++u) {
     const int e = tid + u * nt;
@@ -159,7 +304,8 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
       pf_kind[u] = (bb == B && r == c) ? 2 : 1;     // 2 = diagonal entry (damped)
       pf_b[u] = bb;
       pf_rc[u] = rc;
-      pf_off[u] = (size_t)r * n + (size_t)(6 * bb + c) - (size_t)6 * B;   // + I*(6n+6), never negative for I >= B
+      // H[(6 phys(I) + r) n + 6 phys(I - B + bb) + c] = pf_off + I * pf_stride
+      pf_off[u] = (long long)r * n + c + (6LL * n + 6) * p0 + 6LL * sd * (bb - B);
     } else if (e < (B + 1) * 36 + 6) {
       pf_kind[u] = 3;                                // right-hand side entry
       pf_rc[u] = e - (B + 1) * 36;
@@ -172,7 +318,7 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
 #else
 #define BAND_TICK(var) do {} while (0)
 #endif
-  for (int J = 0; J < P; ++J) {
+  for (int J = 0; J < pt.n_elim; ++J) {
     if (fail) break;
 #ifdef DBAF_BAND_PROFILE
     c0 = clock64();
@@ -187,8 +333,8 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
     if (Inew < P) {
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        if (pf_kind[u] == 3) pre[u] = ws.v[6 * Inew + pf_rc[u]];
-        else if (pf_kind[u]) pre[u] = ws.H[pf_off[u] + (size_t)Inew * (6 * (size_t)n + 6)];
+        if (pf_kind[u] == 3) pre[u] = ws.v[6 * (p0 + sd * Inew) + pf_rc[u]];
+        else if (pf_kind[u]) pre[u] = ws.H[pf_off[u] + (long long)Inew * pf_stride];
       }
     }
     BAND_TICK(tp0);
@@ -259,7 +405,7 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
           for (int c = 0; c < 6; ++c) A[r * 6 + c] -= acc[r][c];
       }
     } else if (J + 1 < P) {
-      factor_diag(J + 1, nbelow > 0 ? slot(J + 1, J) : nullptr, tid - nwork);
+      factor_diag(J + 1, nbelow > 0 ? slot(J + 1, J) : nullptr, tid - nwork, J + 1 < pt.n_elim);
     }
     BAND_TICK(tp3);
     // incoming block row (its slots are unused during this step: NB = B + 2)
@@ -287,92 +433,92 @@ k_solve_banded(int P, int B, float lm, float ep, int rezero, Ws ws) {
     const int o = tid == 0 ? 6 : 11;      // info[6..10]: thread 0, info[11..15]: look-ahead thread (kilo-cycles)
     ws.info[o] = (int)(tp0 >> 10); ws.info[o + 1] = (int)(tp1 >> 10); ws.info[o + 2] = (int)(tp2 >> 10);
     ws.info[o + 3] = (int)(tp3 >> 10); ws.info[o + 4] = (int)(tla >> 10);
+    if (tid == nwork) for (int i = 0; i < 5; ++i) ws.info[11 + i] = (int)(fd[i] >> 10);
   }
 #endif
   __syncthreads();
   const bool ok = fail == 0;
+  if (plan.twisted) {
+    // leave this sweep's view of the separator (blocks [n_elim, Plog) of the window and their rhs) for k_band_sep
+    double* dump = ws.Lfac + plan.sep + (long long)blockIdx.x * band_dump_doubles(B);
+    for (int e = tid; e < B * B * 36; e += nt) {
+      const int blk = e / 36, ai = blk / B, ak = blk - ai * B;
+      if (ai >= ak) dump[e] = slot(pt.n_elim + ai, pt.n_elim + ak)[e - blk * 36];
+    }
+    for (int e = tid; e < 6 * B; e += nt) dump[(size_t)B * B * 36 + e] = yw[((pt.n_elim + e / 6) % NB) * 6 + e % 6];
+    if (tid == 0) reinterpret_cast<int*>(ws.Lfac + plan.sep + 2 * band_dump_doubles(B) + 6 * B)[blockIdx.x] = ok ? 0 : 1;
+    return;
+  }
   if (ok) {
-    // Back-substitution L^T x = y, bottom up, right-looking: once x_J is known every pending
-    // right-hand side above it is updated, y_I -= L_{J,I}^T x_J (I = J-B .. J-1).  The blocks of
-    // block row J of L, the next diagonal block and the next incoming y row are fetched one step
-    // ahead, so a step is one short serial 6x6 solve + one parallel rank-6 update.
-    double* dbuf = Ljj;                              // 2 x 36 diagonal blocks (reused)
-    double* ibuf = dj;                               // 2 x 6 inverse diagonals (reused)
-    double* xs = sred;                               // 6: x_J of the current step
-    auto row_block = [&](int J, int t) {             // thread t's column c of L_{J,I}, I = J-1-t/6
-      return Lband + ((size_t)(J - 1 - t / 6) * (B + 1) + (1 + t / 6)) * 36 + (t % 6);
-    };
-    for (int e = tid; e < NB * 6; e += nt) {
-      const int I = P - 1 - e / 6;                   // rows P-1 .. P-NB
-      if (I >= 0 && e / 6 <= B) yw[(I % NB) * 6 + e % 6] = y_g[6 * I + e % 6];
-    }
-    if (tid < 36) dbuf[((P - 1) & 1) * 36 + tid] = Lband[((size_t)(P - 1) * (B + 1)) * 36 + tid];
-    if (tid < 6) ibuf[((P - 1) & 1) * 6 + tid] = dinv_g[6 * (P - 1) + tid];
-    double cur[6];
-    {
-      const int nab = min(B, P - 1);
-      if (tid < nab * 6) {
-        const double* q = row_block(P - 1, tid);
-#pragma unroll
-        for (int r = 0; r < 6; ++r) cur[r] = q[r * 6];
-      }
-    }
-    __syncthreads();
-    for (int J = P - 1; J >= 0; --J) {
-      if (tid == 0) {
-        const double* L = dbuf + (J & 1) * 36;
-        const double* di = ibuf + (J & 1) * 6;
-        double l[6][6], x[6];
-#pragma unroll
-        for (int r = 0; r < 6; ++r) {
-          x[r] = yw[(J % NB) * 6 + r];
-#pragma unroll
-          for (int c = 0; c < 6; ++c)
-            if (c < r) l[r][c] = L[r * 6 + c];
-        }
-#pragma unroll
-        for (int c = 5; c >= 0; --c) {
-          double sum = x[c];
-#pragma unroll
-          for (int k = 0; k < 6; ++k)
-            if (k > c) sum -= l[k][c] * x[k];
-          x[c] = sum * di[c];
-        }
-#pragma unroll
-        for (int c = 0; c < 6; ++c) {
-          xs[c] = x[c];
-          ws.dx[6 * J + c] = (float)x[c];
-        }
-      }
-      __syncthreads();
-      const int nab = min(B, J);                     // rows above J inside the band
-      double nxt[6];
-      if (tid < nab * 6) {
-        double sum = 0.0;
-#pragma unroll
-        for (int r = 0; r < 6; ++r) sum += cur[r] * xs[r];
-        yw[((J - 1 - tid / 6) % NB) * 6 + tid % 6] -= sum;
-      }
-      if (J > 0) {
-        const int nab2 = min(B, J - 1);
-        if (tid < nab2 * 6) {
-          const double* q = row_block(J - 1, tid);
-#pragma unroll
-          for (int r = 0; r < 6; ++r) nxt[r] = q[r * 6];
-        }
-        const int u = tid - (nt - 64);               // the last two warps fetch the next diagonal block etc.
-        if (u >= 0 && u < 36) dbuf[((J - 1) & 1) * 36 + u] = Lband[((size_t)(J - 1) * (B + 1)) * 36 + u];
-        if (u >= 36 && u < 42) ibuf[((J - 1) & 1) * 6 + (u - 36)] = dinv_g[6 * (J - 1) + (u - 36)];
-        const int Iin = J - 1 - B;                   // row entering the window for step J-1
-        if (u >= 42 && u < 48 && Iin >= 0) yw[(Iin % NB) * 6 + (u - 42)] = y_g[6 * Iin + (u - 42)];
-      }
-      __syncthreads();
-#pragma unroll
-      for (int r = 0; r < 6; ++r) cur[r] = nxt[r];
-    }
+    band_backsub(Pphys, B, pt, 0, nullptr, yw, Ljj, dj, sred, ws);
   } else {
     for (int i = tid; i < n; i += nt) ws.dx[i] = 0.0f;
     if (tid == 0) atomicAdd(&ws.info[1], 1);
   }
   (void)rezero;
+}
+
+// Separator of the twisted factorisation: S = S_top + S_bottom - A_ss (A_ss damped like everywhere else),
+// rhs likewise, dense Cholesky in shared memory, x_sep to global memory and to dx.
+__global__ void __launch_bounds__(kThreads)
+k_band_sep(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
+  extern __shared__ double sms[];
+  __shared__ int fail;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int n = 6 * Pphys, ns = 6 * B, m = plan.m;
+  const int ld = ns | 1;
+  double* L = sms;                                   // (ns+1) x ld
+  double* x = L + (size_t)(ns + 1) * ld;             // ns
+  double* dinv = x + ns;                             // ns
+  const double* top = ws.Lfac + plan.sep;
+  const double* bot = top + band_dump_doubles(B);
+  double* xsep = ws.Lfac + plan.sep + 2 * band_dump_doubles(B);
+  int* flags = reinterpret_cast<int*>(xsep + ns);
+  const bool sweeps_ok = flags[0] == 0 && flags[1] == 0;
+  for (int e = tid; e < B * B * 36; e += nt) {
+    const int blk = e / 36, a = blk / B, b = blk - a * B;
+    if (a < b) continue;
+    const int rc = e - blk * 36, r = rc / 6, c = rc - r * 6;
+    if (a == b && c > r) continue;
+    // the bottom sweep works on the block-reversed ordering: physical block (m+a, m+b), a >= b, is its upper
+    // triangle, i.e. the transpose of its logical block (B-1-b, B-1-a)
+    double h = ws.H[(size_t)(6 * (m + a) + r) * n + 6 * (m + b) + c];
+    if (a == b && r == c) h += (double)ep + (double)lm * h;
+    // (diagonal blocks are symmetric in themselves; only their lower triangle is kept up to date by the sweeps)
+    const int brc = a == b ? r * 6 + c : c * 6 + r;
+    L[(size_t)(6 * a + r) * ld + 6 * b + c] =
+        top[(size_t)(a * B + b) * 36 + r * 6 + c] + bot[(size_t)((B - 1 - b) * B + (B - 1 - a)) * 36 + brc] - h;
+  }
+  for (int e = tid; e < ns; e += nt) {
+    const int a = e / 6, r = e - a * 6;
+    L[(size_t)ns * ld + e] = top[(size_t)B * B * 36 + e] + bot[(size_t)B * B * 36 + (B - 1 - a) * 6 + r] - ws.v[6 * m + e];
+  }
+  __syncthreads();
+  const bool ok = cholesky6_solve(L, ld, B, x, dinv, &fail) && sweeps_ok;
+  __syncthreads();
+  for (int e = tid; e < ns; e += nt) {
+    xsep[e] = ok ? x[e] : 0.0;
+    ws.dx[6 * m + e] = ok ? (float)x[e] : 0.0f;
+  }
+  if (tid == 0) {
+    flags[2] = ok ? 0 : 1;
+    if (!ok) atomicAdd(&ws.info[1], 1);
+  }
+}
+
+__global__ void __launch_bounds__(kBandThreads)
+k_band_back(int Pphys, int B, BandPlan plan, Ws ws) {
+  __shared__ double yw[(kBandMaxB + 2) * 6], dbuf[72], ibuf[12], xs[6];
+  const BandPart pt = plan.part[blockIdx.x];
+  const double* xsep = ws.Lfac + plan.sep + 2 * band_dump_doubles(B);
+  const int* flags = reinterpret_cast<const int*>(xsep + 6 * B);
+  if (flags[2] != 0) {
+    // a pivot failed somewhere: the whole step is dropped (dx = 0), like the single sweep does
+    for (int I = threadIdx.x; I < pt.n_elim * 6; I += blockDim.x) {
+      const int J = I / 6;
+      ws.dx[6 * (pt.rev ? Pphys - 1 - J : J) + I % 6] = 0.0f;
+    }
+    return;
+  }
+  band_backsub(Pphys, B, pt, plan.m, xsep, yw, dbuf, ibuf, xs, ws);
 }

@@ -153,6 +153,51 @@ def test_large_window_solvers(dev, db, oracle, synth, band_hint):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("extra,reach", [(40, 2), (40, 5), (90, 3), (27, 1)])
+def test_twisted_banded_solve(dev, db, oracle, synth, monkeypatch, extra, reach):
+    """Long chains are factorised from both ends (two CTAs meeting at a B-block separator): same dx as the
+    single sweep and as the float64 dense solve of the oracle."""
+    from dbaf_b200 import global_ba
+    w = synth.make_window("g40", seed=4, graph="banded", reach=reach, n_extra_frames=extra)
+    band = global_ba.band_blocks(w["ii"], w["jj"], w["t0"], w["t1"])
+    P = w["t1"] - w["t0"]
+    assert P >= 64 and P >= 3 * band + 2              # the twisted path is taken
+    out = {}
+    for impl in ("twisted", "single"):
+        if impl == "single":
+            monkeypatch.setenv("DBAF_BAND_IMPL", "single")
+        else:
+            monkeypatch.delenv("DBAF_BAND_IMPL", raising=False)
+        t = to_torch(w, dev)
+        win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                         t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+        win.prepare()
+        win.linearize(0.05)
+        n = win.n
+        hv = win.Hv().cpu().numpy()
+        H, v = hv[:n * n].reshape(n, n).copy(), hv[n * n:].copy()
+        win.solve(1e-4, 0.1, band=band)
+        assert int(win.info().cpu()[1]) == 0
+        out[impl] = win.dx().cpu().numpy().reshape(-1).copy()
+    want, ok = oracle.damped_solve(H, v, 1e-4, 0.1)
+    assert ok
+    assert relerr(out["twisted"], want) < 1e-6, relerr(out["twisted"], want)
+    assert relerr(out["single"], want) < 1e-6
+    # a non-positive pivot anywhere drops the whole step in both variants
+    t = to_torch(w, dev)
+    win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                     t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+    win.prepare()
+    win.linearize(0.05)
+    n = win.n
+    i = (n // 6 - 3) * 6
+    win.H()[i, i] = -1.0e9                             # a diagonal entry inside the bottom sweep's part
+    win.solve(1e-4, 0.1, band=band)
+    assert int(win.info().cpu()[1]) == 1
+    assert float(win.dx().abs().max()) == 0.0
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("reach", [4, 6, 10])
 def test_tensor_core_schur_matches_simt_and_oracle(dev, db, oracle, synth, monkeypatch, reach):
     """Dense graphs (>= 8 row blocks per depth frame) take k_schur_tc (TF32 x3 on tcgen05): same reduced
