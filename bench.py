@@ -39,6 +39,25 @@ import torch  # noqa: E402
 
 
 # ----------------------------------------------------------------------------- helpers
+# DRAM bytes per launch read from committed ncu captures (profiles/), keyed by (workload, kernel)
+NCU_TRAFFIC_BYTES = {("c2", "k_linearize2"): 3.79e6, ("c2", "k_volume_tc"): 2.137e9, ("c2", "k_corr_lookup"): 3.67e8}
+
+
+def write_only_peak(dev):
+    """HBM write-only bandwidth measured here and now (GB/s): a 2 GiB fill, best of 5.  The copy figure in
+    MEASURED_PEAKS.json counts read + write bytes; a kernel that only writes cannot exceed this one."""
+    x = torch.empty(1 << 30, dtype=torch.int16, device=dev)
+    best = 1e9
+    for _ in range(7):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        x.fill_(1)
+        b.record()
+        b.synchronize()
+        best = min(best, a.elapsed_time(b))
+    return x.numel() * 2 / (best * 1e-3) / 1e9
+
+
 def measured_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -170,9 +189,13 @@ def bench_local(args, dev, rank, world):
         stage[name] = statistics.mean(timed_steps(fn, max(5, args.steps), 3, flush, reset))
     lin_ms = stage["linearize"]
     lin_bytes = E * HW * 20 + K * HW * 12          # algorithmic bytes of the linearise kernel
-    roof = dict(bound="hbm", kernel="k_linearize", achieved=lin_bytes / (lin_ms * 1e-3) / 1e9, peak=peaks["hbm"],
-                unit="GB/s", peak_source=peaks["src"] + " (burst, kernel timed alone)", traffic=None,
-                algorithmic_bytes=lin_bytes, ms=lin_ms)
+    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of one k_linearize2 launch on this workload from the
+    # committed `ncu --set full` capture (profiles/r1_ncu_ba_c2.md); it cannot be measured outside a profiler
+    traffic = NCU_TRAFFIC_BYTES.get((cfg, "k_linearize2"))
+    roof = dict(bound="hbm", kernel="k_linearize2", achieved=lin_bytes / (lin_ms * 1e-3) / 1e9, peak=peaks["hbm"],
+                unit="GB/s", peak_source=peaks["src"] + " (burst, kernel timed alone)", traffic=traffic,
+                algorithmic_bytes=lin_bytes, ms=lin_ms,
+                note="latency-bound at this size: 48 edges x 4096 px is 4.5 MB, far below what fills the machine")
     roof["frac"] = roof["achieved"] / roof["peak"]
 
     # ---- end to end through the public API with host buffers
@@ -255,6 +278,9 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
     steps = max(3, min(args.steps, 10))
     pyr = db.corr_volume_pyramid(f1, f2, 4)
     vol_ms = statistics.mean(timed_steps(lambda: db.corr_volume_pyramid(f1, f2, 4), steps, 3, flush))
+    # the call the pipeline makes (dbaf/covisible_graph.py:129-131): per-frame maps + edge lists, no gather
+    idx_ms = statistics.mean(timed_steps(lambda: db.corr_volume_pyramid_indexed(feats, feats, ii, jj, 4), steps, 3, flush))
+    wpeak = write_only_peak(dev)
     look_ms = statistics.mean(timed_steps(lambda: db.corr_lookup_pyramid(pyr, coords, 3), steps, 3, flush))
     # the reference's own path for the same work, on this GPU, in this run: torch.matmul (cuBLAS) + 3x
     # avg_pool2d (dbaf/modules/corr.py:24-38,63-71) and its corr_index_forward kernel (oracle/_ref)
@@ -271,6 +297,13 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
         return out
 
     ref = dict(volume_pyramid_ms=statistics.mean(timed_steps(ref_volume, steps, 3, flush)))
+
+    def ref_gather_volume():
+        nonlocal f1, f2
+        f1, f2 = feats[ii], feats[jj]
+        return ref_volume()
+    ref["gather_volume_pyramid_ms"] = statistics.mean(timed_steps(ref_gather_volume, steps, 3, flush))
+    f1, f2 = feats[ii].contiguous(), feats[jj].contiguous()
     try:
         import build_ref
         rmod = build_ref.load()
@@ -284,15 +317,25 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
     vol_bytes = n * (2 * HW * 128 * 2 + 2 * HW * lvl)             # read both fmaps, write 4 levels
     vol_flop = n * 2.0 * HW * HW * 128
     look_bytes = n * HW * 912                                     # 64 taps + 49 outputs per level + coords
+    idx_bytes = n * 2 * HW * lvl + 2 * feats.numel() * 2          # write 4 levels; read + write the frame maps once
     return dict(
+        volume_pyramid_indexed=dict(
+            edges_per_s=n / (idx_ms * 1e-3), ms=idx_ms,
+            roofline=dict(bound="hbm", kernel="k_volume_tc", achieved=idx_bytes / (idx_ms * 1e-3) / 1e9, peak=peaks["hbm"],
+                          unit="GB/s", frac=idx_bytes / (idx_ms * 1e-3) / 1e9 / peaks["hbm"],
+                          traffic=NCU_TRAFFIC_BYTES.get((cfg, "k_volume_tc")),
+                          write_only_peak=wpeak, frac_of_write_only_peak=idx_bytes / (idx_ms * 1e-3) / 1e9 / wpeak,
+                          note="97 % of the bytes are writes; write_only_peak is a fill measured in this run")),
         volume_pyramid=dict(edges_per_s=n / (vol_ms * 1e-3), ms=vol_ms,
                             roofline=dict(bound="hbm", achieved=vol_bytes / (vol_ms * 1e-3) / 1e9, peak=peaks["hbm"],
-                                          unit="GB/s", frac=vol_bytes / (vol_ms * 1e-3) / 1e9 / peaks["hbm"]),
+                                          unit="GB/s", frac=vol_bytes / (vol_ms * 1e-3) / 1e9 / peaks["hbm"],
+                                          write_only_peak=wpeak),
                             tensor=dict(achieved=vol_flop / (vol_ms * 1e-3) / 1e12, peak=peaks["tf_burst"], unit="TFLOP/s",
                                         frac=vol_flop / (vol_ms * 1e-3) / 1e12 / peaks["tf_burst"])),
         lookup=dict(edges_per_s=n / (look_ms * 1e-3), ms=look_ms,
-                    roofline=dict(bound="hbm", achieved=look_bytes / (look_ms * 1e-3) / 1e9, peak=peaks["hbm"],
-                                  unit="GB/s", frac=look_bytes / (look_ms * 1e-3) / 1e9 / peaks["hbm"])),
+                    roofline=dict(bound="hbm", kernel="k_corr_lookup", achieved=look_bytes / (look_ms * 1e-3) / 1e9,
+                                  peak=peaks["hbm"], unit="GB/s", frac=look_bytes / (look_ms * 1e-3) / 1e9 / peaks["hbm"],
+                                  traffic=NCU_TRAFFIC_BYTES.get((cfg, "k_corr_lookup")))),
         edges=n, reference_same_gpu=ref)
 
 
@@ -396,6 +439,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-global", action="store_true", help="skip the 1-GPU run of the c5 global-BA workload")
     args = ap.parse_args()
     args.warmup = max(3, args.warmup)
     rank = int(os.environ.get("RANK", "0"))
@@ -422,8 +466,18 @@ def main():
         from dbaf_b200 import global_ba
         line, clk = global_ba.bench(args, dev, rank, world, ClockSampler, L2Flusher, measured_peaks())
     else:
+        default_run = args.workload is None
         args.workload = args.workload or "c2"
         line, clk = bench_local(args, dev, rank, world)
+        if default_run and not args.no_global:
+            # `--gpus N` for N > 1 runs the edge-sharded global BA (BASELINE.json configs[4]); its 1-GPU point is
+            # measured here so that the 1/2/4/8 series has a base on the same workload
+            from dbaf_b200 import global_ba
+            import copy
+            ga = copy.copy(args)
+            ga.workload, ga.steps = "c5", min(args.steps, 10)
+            gl, _ = global_ba.bench(ga, dev, rank, world, ClockSampler, L2Flusher, measured_peaks())
+            line["global_ba_1gpu"] = {k: gl[k] for k in ("value", "unit", "ms_per_step", "config", "stages_ms", "roofline")}
 
     if world > 1:
         v = torch.tensor([line["ms_per_step"]], device=dev, dtype=torch.float64)

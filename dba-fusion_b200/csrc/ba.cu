@@ -734,7 +734,8 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
     // with the square of the row count; DBAF_SCHUR_IMPL=simt keeps everything on the fp32 SIMT kernels
     const char* schur_impl = std::getenv("DBAF_SCHUR_IMPL");
     const bool simt_only = schur_impl != nullptr && std::strcmp(schur_impl, "simt") == 0;
-    const bool use_tc = !simt_only && E >= 4 * k_cap && HW % 32 == 0;   // 128-byte bulk copies need whole slices
+    // mean out-degree >= 7, i.e. frames with >= 8 row blocks exist; whole 32-pixel slices for the 16-byte copies
+    const bool use_tc = !simt_only && E >= 7 * k_cap && HW % 32 == 0;
     const int tc_min_m = 8;
     if (use_tc) {
       static bool tc_attr[64] = {};

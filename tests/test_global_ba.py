@@ -66,7 +66,7 @@ class OracleEngine:
         o.retract(self.poses, self.disps, self.dx, np.where(own[:, None], dz, 0.0), self.tab, self.t0, self.t1)
 
 
-def _worker(rank, world, port, seed, out):
+def _worker(rank, world, port, seed, out, graph="frontend"):
     for p in (os.path.join(ROOT, "dba-fusion_b200"), os.path.join(ROOT, "oracle")):
         sys.path.insert(0, p)
     import dbaf_oracle as oracle
@@ -74,9 +74,11 @@ def _worker(rank, world, port, seed, out):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
-    w = synth.make_window("tiny", seed=seed, n_extra_frames=3)
+    w = _gloo_window(synth, seed, graph)
     eng = OracleEngine(oracle, w)
     gba = global_ba.GlobalBA(eng, w["ii"], w["jj"], w["t0"], w["t1"])
+    # the banded graph exchanges only the band of H; the frontend-style one the whole system
+    assert (gba.band_index(torch.device("cpu")) is not None) == (graph == "banded")
     gba.run(2)
     d = torch.from_numpy(eng.disps)
     gba.gather_disps(d)
@@ -86,12 +88,19 @@ def _worker(rank, world, port, seed, out):
     dist.destroy_process_group()
 
 
-def test_sharded_global_ba_matches_single_process_gloo(oracle, synth, tmp_path):
+def _gloo_window(synth, seed, graph):
+    if graph == "banded":
+        return synth.make_window("tiny", seed=seed, n_extra_frames=10, graph="banded", reach=1)
+    return synth.make_window("tiny", seed=seed, n_extra_frames=3)
+
+
+@pytest.mark.parametrize("graph", ["frontend", "banded"])
+def test_sharded_global_ba_matches_single_process_gloo(oracle, synth, tmp_path, graph):
     out = str(tmp_path / "res.npz")
-    port = 29500 + (os.getpid() % 2000)
-    mp.start_processes(_worker, args=(2, port, 5, out), nprocs=2, join=True, start_method="spawn")
+    port = 29500 + (os.getpid() % 2000) + (7 if graph == "banded" else 0)
+    mp.start_processes(_worker, args=(2, port, 5, out, graph), nprocs=2, join=True, start_method="spawn")
     res = np.load(out)
-    w = synth.make_window("tiny", seed=5, n_extra_frames=3)
+    w = _gloo_window(synth, 5, graph)
     p, d = w["poses"].astype(np.float64), w["disps"].astype(np.float64)
     oracle.ba(p, d, w["intrinsics"], w["disps_sens"], w["targets"], w["weights"], w["eta"], w["ii"], w["jj"],
               w["t0"], w["t1"], 2, 1e-4, 0.1, False, dtype=np.float64)
@@ -204,7 +213,7 @@ def test_tensor_core_schur_matches_simt_and_oracle(dev, db, oracle, synth, monke
     system as the fp32 SIMT kernels (EEt6x6 / Ev6x1 of src/droid_kernels.cu:1046-1138) and as the float64
     oracle."""
     w = synth.make_window("g40", seed=3, graph="banded", reach=reach)
-    assert len(w["ii"]) >= 4 * 40
+    assert len(w["ii"]) >= 7 * 40
 
     def system(impl):
         if impl:
