@@ -679,9 +679,10 @@ extern "C" int dbaf_ba_prepare(void* workspace, const int64_t* ii, const int64_t
 
 namespace {
 int pick_pxt(int Kcap, int HW) {
-  // keep at least ~2 CTAs per SM busy; more pixels per thread amortise the per-edge reduction
+  // keep at least ~2 CTAs per SM busy; two pixels per thread amortise the per-edge reduction.  Four pixels per
+  // thread were measured slower everywhere since the next edge's inputs are prefetched into registers
+  // (170 registers, one CTA per SM): C5 linearise+Schur 2.82 ms with 4, 2.56 ms with 2, 3.19 ms with 1.
   const long ctas1 = (long)Kcap * ((HW + 255) / 256);
-  if (ctas1 >= 148L * 16) return 4;
   if (ctas1 >= 148L * 6) return 2;
   return 1;
 }

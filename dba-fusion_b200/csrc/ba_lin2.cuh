@@ -88,6 +88,20 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
   }
 
   const int e_lo = ws.csr_ptr[k], e_hi = ws.csr_ptr[k + 1];
+  // targets and weights of the next edge are requested while the current edge is being worked on (the
+  // kernel is otherwise exposed to one full memory latency per edge): tw[s] = {wu, wv, tu, tv}
+  float4 tw_next[PXT];
+  auto fetch_edge = [&](int pos) {
+    if (pos < e_hi) {
+      const int e = ws.csr_idx[pos];
+#pragma unroll
+      for (int s = 0; s < PXT; ++s) {
+        const size_t o = ((size_t)e * 2) * HW + (ok[s] ? px[s] : 0);
+        tw_next[s] = make_float4(__ldg(weights + o), __ldg(weights + o + HW), __ldg(targets + o), __ldg(targets + o + HW));
+      }
+    }
+  };
+  fetch_edge(e_lo);
   for (int base = e_lo; base < e_hi; base += kLinChunk) {
     const int cnt = min(kLinChunk, e_hi - base);
     __syncthreads();                                   // previous chunk's transforms no longer in use
@@ -106,6 +120,10 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
       float h[32];     // [0,21): lower triangle of Hjj row by row, [21,27): vj
 #pragma unroll
       for (int l = 0; l < 32; ++l) h[l] = 0.f;
+      float4 tw_cur[PXT];
+#pragma unroll
+      for (int s = 0; s < PXT; ++s) tw_cur[s] = tw_next[s];
+      fetch_edge(base + a + 1);
 
 #pragma unroll
       for (int s = 0; s < PXT; ++s) {
@@ -118,11 +136,10 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
         const bool near = Xj[2] < kMinDepth;
         const float d = near ? 0.0f : 1.0f / Xj[2];
         const float d2 = d * d;
-        const size_t tw = ((size_t)e * 2) * HW + p;
-        float wu = near ? 0.0f : (float)(0.001 * (double)__ldg(weights + tw));
-        float wv = near ? 0.0f : (float)(0.001 * (double)__ldg(weights + tw + HW));
-        const float ru = __ldg(targets + tw) - (fx * d * x + cx);
-        const float rv = __ldg(targets + tw + HW) - (fy * d * y + cy);
+        float wu = near ? 0.0f : (float)(0.001 * (double)tw_cur[s].x);
+        float wv = near ? 0.0f : (float)(0.001 * (double)tw_cur[s].y);
+        const float ru = tw_cur[s].z - (fx * d * x + cx);
+        const float rv = tw_cur[s].w - (fy * d * y + cy);
         const float Ju[6] = {fx * (hh * d), fx * 0.f, fx * (-x * hh * d2), fx * (-x * y * d2),
                              fx * (1.0f + x * x * d2), fx * (-y * d)};
         const float Jv[6] = {fy * 0.f, fy * (hh * d), fy * (-y * hh * d2), fy * (-1.0f - y * y * d2),
