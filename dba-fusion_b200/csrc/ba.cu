@@ -792,7 +792,7 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
   } else if (band_blocks > 0 && band_blocks <= kBandMaxB && prior == nullptr) {
     const int B = std::min(band_blocks, P - 1);
     const int NB = B + 2;
-    const size_t smem = ((size_t)NB * NB * 36 + NB * 6 + 72 + 12 + 8) * sizeof(double);
+    const size_t smem = std::max((size_t)NB * NB * 36 + NB * 6 + 72 + 12 + 8, (size_t)band_back_smem_doubles(B)) * sizeof(double);
     static bool band_attr[64] = {};
     int dev_id = 0;
     DBAF_CUDA(cudaGetDevice(&dev_id));
@@ -827,7 +827,7 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       }
       k_band_sep<<<1, kThreads, ssm, st>>>(P, B, lm, ep, plan, ws);
       DBAF_LAUNCH_CHECK("k_band_sep");
-      k_band_back<<<2, kBandThreads, 0, st>>>(P, B, plan, ws);
+      k_band_back<<<2, 32, band_back_smem_doubles(B) * sizeof(double), st>>>(P, B, plan, ws);
       DBAF_LAUNCH_CHECK("k_band_back");
     }
     if (rezero) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, ((size_t)n * n + n) * 8, st));

@@ -47,65 +47,98 @@ __device__ __forceinline__ double warp_sum_d(double v) {
   return v;
 }
 
-// Back-substitution L^T x = y of one part, bottom up, right-looking: once x_J is known every pending
-// right-hand side above it is updated, y_I -= L_{J,I}^T x_J (I = J-B .. J-1).  The blocks of block row J of
-// L, the next diagonal block and the next incoming y row are fetched one step ahead, so a step is one short
-// serial 6x6 solve + one parallel rank-6 update.  Rows J >= n_elim are not solved: their x comes from `xsep`
-// (the separator solution, physical order, separator-local) and only the update is applied.
-__device__ void band_backsub(int Pphys, int B, const BandPart& pt, int m, const double* __restrict__ xsep,
-                             double* yw, double* dbuf, double* ibuf, double* xs, Ws ws) {
-  const int tid = threadIdx.x, nt = blockDim.x;
-  const int P = pt.Plog, NB = B + 2;
+// Back-substitution L^T x = y of one part, bottom up, right-looking, on ONE warp: once x_J is known every
+// pending right-hand side above it is updated, y_I -= L_{J,I}^T x_J (I = J-B .. J-1).  A step is a short serial
+// 6x6 solve on lane 0 plus 6B dot products of length 6 spread over the lanes, so a second warp would only add
+// barriers.  Everything a step reads (the B blocks of block row J of L, L_JJ, 1/diag, the y row entering the
+// window) is brought into a kBackDepth-deep shared-memory ring with 16-byte asynchronous copies issued
+// kBackDepth-1 steps ahead: the L2 latency of the band store never shows.  Rows J >= n_elim are not solved:
+// their x comes from `xsep` (the separator solution, physical order, separator-local) and only the update
+// is applied.
+constexpr int kBackDepth = 4;
+__host__ __device__ inline int band_back_stage_doubles(int B) { return (B + 1) * 36 + 12; }   // L row (d = 0..B) | dinv | y_in
+__host__ __device__ inline int band_back_smem_doubles(int B) {
+  return kBackDepth * band_back_stage_doubles(B) + (B + 2) * 6 + 6 * B + 8;            // ring | yw | xsep | xs
+}
+
+__device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, const double* __restrict__ xsep_g,
+                                  double* sm, Ws ws) {
+  const int lane = threadIdx.x & 31;
+  const int P = pt.Plog, NB = B + 2, SD = band_back_stage_doubles(B), RD = (B + 1) * 36;
   const double* Lband = ws.Lfac + pt.store;
   const double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
   const double* y_g = dinv_g + 6 * P;
+  double* ring = sm;
+  double* yw = ring + kBackDepth * SD;
+  double* xsep = yw + NB * 6;
+  double* xs = xsep + 6 * B;
   auto phys = [&](int I) { return pt.rev ? Pphys - 1 - I : I; };
-  auto row_block = [&](int J, int t) {             // thread t's column c of L_{J,I}, I = J-1-t/6
-    return Lband + ((size_t)(J - 1 - t / 6) * (B + 1) + (1 + t / 6)) * 36 + (t % 6);
+  auto cp16 = [&](double* dst, const double* src, int bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src),
+                 "r"(bytes)
+                 : "memory");
   };
-  for (int e = tid; e < NB * 6; e += nt) {
-    const int I = P - 1 - e / 6;                   // rows P-1 .. P-NB
-    if (I >= 0 && e / 6 <= B) yw[(I % NB) * 6 + e % 6] = I < pt.n_elim ? y_g[6 * I + e % 6] : 0.0;
-  }
-  if (P - 1 < pt.n_elim) {
-    if (tid < 36) dbuf[((P - 1) & 1) * 36 + tid] = Lband[((size_t)(P - 1) * (B + 1)) * 36 + tid];
-    if (tid < 6) ibuf[((P - 1) & 1) * 6 + tid] = dinv_g[6 * (P - 1) + tid];
-  }
-  double cur[6];
-  {
-    const int nab = min(B, P - 1);
-    if (tid < nab * 6) {
-      const bool have = P - 2 - tid / 6 < pt.n_elim;             // column block I of L_{J,I} was eliminated
-      const double* q = row_block(P - 1, tid);
-#pragma unroll
-      for (int r = 0; r < 6; ++r) cur[r] = have ? q[r * 6] : 0.0;
+  // stage for step J: block row J of the band store (L_JJ, L_{J,J-1}, .. L_{J,J-B}; entries whose column was
+  // never eliminated hold garbage and are skipped below), then 1/diag(J) and y of row J-B
+  auto issue = [&](int J) {
+    if (J >= 0) {
+      double* dst = ring + (J % kBackDepth) * SD;
+      const double* src = Lband + (size_t)J * RD;
+      for (int q = lane; q < RD / 2; q += 32) cp16(dst + 2 * q, src + 2 * q, 16);
+      if (lane < 3) cp16(dst + RD + 2 * lane, dinv_g + 6 * (J < pt.n_elim ? J : 0) + 2 * lane, 16);
+      if (lane >= 3 && lane < 6) {
+        const int I = J - B, ok = I >= 0 && I < pt.n_elim;
+        cp16(dst + RD + 2 * lane, y_g + 6 * (ok ? I : 0) + 2 * (lane - 3), ok ? 16 : 0);
+      }
     }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+
+  for (int J = P - 1; J > P - kBackDepth; --J) issue(J);
+  // window rows P-1 .. P-B (row P-1-B arrives with the first stage)
+  for (int e = lane; e < B * 6; e += 32) {
+    const int I = P - 1 - e / 6;
+    if (I >= 0) yw[(I % NB) * 6 + e % 6] = I < pt.n_elim ? y_g[6 * I + e % 6] : 0.0;
   }
-  __syncthreads();
+  if (xsep_g != nullptr)
+    for (int e = lane; e < 6 * B; e += 32) xsep[e] = xsep_g[e];
+  __syncwarp();
+
+#ifdef DBAF_BAND_PROFILE
+  long long bt[4] = {0, 0, 0, 0}, b0, b1;
+#define BK_TICK(i) do { b1 = clock64(); bt[i] += b1 - b0; b0 = b1; } while (0)
+#else
+#define BK_TICK(i) do {} while (0)
+#endif
   for (int J = P - 1; J >= 0; --J) {
-    if (tid == 0) {
+#ifdef DBAF_BAND_PROFILE
+    b0 = clock64();
+#endif
+    issue(J - (kBackDepth - 1));
+    BK_TICK(0);
+    asm volatile("cp.async.wait_group %0;" ::"n"(kBackDepth - 1) : "memory");
+    __syncwarp();
+    BK_TICK(1);
+    const double* st = ring + (J % kBackDepth) * SD;
+    if (lane < 6 && J - B >= 0) yw[((J - B) % NB) * 6 + lane] = st[RD + 6 + lane];
+    if (lane == 0) {
       double x[6];
       if (J >= pt.n_elim) {
 #pragma unroll
         for (int c = 0; c < 6; ++c) x[c] = xsep[6 * (phys(J) - m) + c];
       } else {
-        const double* L = dbuf + (J & 1) * 36;
-        const double* di = ibuf + (J & 1) * 6;
-        double l[6][6];
+        const double* L = st;
+        const double* di = st + RD;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) {
-          x[r] = yw[(J % NB) * 6 + r];
-#pragma unroll
-          for (int c = 0; c < 6; ++c)
-            if (c < r) l[r][c] = L[r * 6 + c];
-        }
+        for (int r = 0; r < 6; ++r) x[r] = yw[(J % NB) * 6 + r];
+        // column sweep: as soon as x[c] is final the rows above it are corrected, so the serial chain per
+        // unknown is one multiply and one fused multiply-add
 #pragma unroll
         for (int c = 5; c >= 0; --c) {
-          double sum = x[c];
+          x[c] *= di[c];
 #pragma unroll
           for (int k = 0; k < 6; ++k)
-            if (k > c) sum -= l[k][c] * x[k];
-          x[c] = sum * di[c];
+            if (k < c) x[k] -= L[c * 6 + k] * x[c];
         }
 #pragma unroll
         for (int c = 0; c < 6; ++c) ws.dx[6 * phys(J) + c] = (float)x[c];
@@ -113,38 +146,36 @@ __device__ void band_backsub(int Pphys, int B, const BandPart& pt, int m, const 
 #pragma unroll
       for (int c = 0; c < 6; ++c) xs[c] = x[c];
     }
-    __syncthreads();
-    const int nab = min(B, J);                     // rows above J inside the band
-    double nxt[6];
-    if (tid < nab * 6) {
-      double sum = 0.0;
+    __syncwarp();
+    BK_TICK(2);
+    double xv[6];
 #pragma unroll
-      for (int r = 0; r < 6; ++r) sum += cur[r] * xs[r];
-      yw[((J - 1 - tid / 6) % NB) * 6 + tid % 6] -= sum;
-    }
-    if (J > 0) {
-      const int nab2 = min(B, J - 1);
-      if (tid < nab2 * 6) {
-        const bool have = J - 2 - tid / 6 < pt.n_elim;
-        const double* q = row_block(J - 1, tid);
+    for (int r = 0; r < 6; ++r) xv[r] = xs[r];
+    const int nab = min(B, J);                       // rows above J inside the band
+    // fixed trip count (6B <= 150 items over 32 lanes) so that the five dot products overlap
 #pragma unroll
-        for (int r = 0; r < 6; ++r) nxt[r] = have ? q[r * 6] : 0.0;
+    for (int u = 0; u < 5; ++u) {
+      const int t = lane + 32 * u;
+      const int o = t / 6, c = t - o * 6;
+      if (t < nab * 6 && J - 1 - o < pt.n_elim) {    // (separator x separator blocks are never formed)
+        const double* q = st + (o + 1) * 36 + c;
+        double sum = 0.0;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) sum += q[r * 6] * xv[r];
+        yw[((J - 1 - o) % NB) * 6 + c] -= sum;
       }
-      const int u = tid - (nt - 64);               // the last two warps fetch the next diagonal block etc.
-      if (J - 1 < pt.n_elim) {
-        if (u >= 0 && u < 36) dbuf[((J - 1) & 1) * 36 + u] = Lband[((size_t)(J - 1) * (B + 1)) * 36 + u];
-        if (u >= 36 && u < 42) ibuf[((J - 1) & 1) * 6 + (u - 36)] = dinv_g[6 * (J - 1) + (u - 36)];
-      }
-      const int Iin = J - 1 - B;                   // row entering the window for step J-1
-      if (u >= 42 && u < 48 && Iin >= 0) yw[(Iin % NB) * 6 + (u - 42)] = Iin < pt.n_elim ? y_g[6 * Iin + (u - 42)] : 0.0;
     }
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < 6; ++r) cur[r] = nxt[r];
+    // no barrier here: the one after the next wait_group orders these updates before lane 0 reads them
+    BK_TICK(3);
   }
+#ifdef DBAF_BAND_PROFILE
+  if (lane == 0 && pt.rev == 0) for (int i = 0; i < 4; ++i) ws.info[6 + i] = (int)(bt[i] >> 10);
+#endif
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
-// Band store of a part: [Plog][B+1][36] (block d = I-J of column J, row-major 6x6), then dinv [6 Plog],
+// Band store of a part: [Plog][B+1][36] (entry (I, d) = L_{I, I-d}, row-major 6x6: a block row of L is one
+// contiguous run, which is what the back-substitution streams), then dinv [6 Plog],
 // then y [6 Plog].
 __global__ void __launch_bounds__(kBandThreads)
 k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, Ws ws) {
@@ -159,7 +190,6 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
   double* yw = Wd + (size_t)NB * NB * 36;            // NB x 6 (right-hand side window, later x window)
   double* Ljj = yw + NB * 6;                         // 36
   double* dj = Ljj + 72;                             // 2 x 6 (1 / diag), double-buffered like Ljj (2 x 36)
-  double* sred = dj + 12;                            // 8 (back-substitution partial sums)
   __shared__ int fail;
   double* Lband = ws.Lfac + pt.store;
   double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
@@ -355,7 +385,7 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
         A[c] = x[c];
-        Lband[((size_t)J * (B + 1) + (I - J)) * 36 + r * 6 + c] = x[c];
+        Lband[((size_t)I * (B + 1) + (I - J)) * 36 + r * 6 + c] = x[c];
         yy -= x[c] * yw[(J % NB) * 6 + c];
       }
       yw[(I % NB) * 6 + r] = yy;
@@ -450,7 +480,8 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
     return;
   }
   if (ok) {
-    band_backsub(Pphys, B, pt, 0, nullptr, yw, Ljj, dj, sred, ws);
+    // the window is no longer needed: its shared memory becomes the back-substitution's staging ring
+    if (tid < 32) band_backsub_warp(Pphys, B, pt, 0, nullptr, smb, ws);
   } else {
     for (int i = tid; i < n; i += nt) ws.dx[i] = 0.0f;
     if (tid == 0) atomicAdd(&ws.info[1], 1);
@@ -506,9 +537,9 @@ k_band_sep(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   }
 }
 
-__global__ void __launch_bounds__(kBandThreads)
+__global__ void __launch_bounds__(32)
 k_band_back(int Pphys, int B, BandPlan plan, Ws ws) {
-  __shared__ double yw[(kBandMaxB + 2) * 6], dbuf[72], ibuf[12], xs[6];
+  extern __shared__ double smk[];
   const BandPart pt = plan.part[blockIdx.x];
   const double* xsep = ws.Lfac + plan.sep + 2 * band_dump_doubles(B);
   const int* flags = reinterpret_cast<const int*>(xsep + 6 * B);
@@ -520,5 +551,5 @@ k_band_back(int Pphys, int B, BandPlan plan, Ws ws) {
     }
     return;
   }
-  band_backsub(Pphys, B, pt, plan.m, xsep, yw, dbuf, ibuf, xs, ws);
+  band_backsub_warp(Pphys, B, pt, plan.m, xsep, smk, ws);
 }

@@ -11,4 +11,4 @@ gba = global_ba.GlobalBA(eng, win["ii"], win["jj"], win["t0"], win["t1"])
 for _ in range(int(sys.argv[2]) if len(sys.argv) > 2 else 2):
     gba.iterate()
 torch.cuda.synchronize()
-print("ok", eng.w.info().cpu().tolist())
+print("ok", eng.w.info().cpu()[:5].tolist())
