@@ -127,8 +127,9 @@ k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k
 // rsqrt(double) is several times longer and sits on the critical path of the pivot chain.
 __device__ __forceinline__ double rsqrt_nr(double d) {
   if (!(d > 1e-30 && d < 1e30)) return rsqrt(d);
-  // one Newton step written as three dependent FMAs (a dependent float64 operation costs ~35 cycles on
-  // this part and the pivot chain is pure latency): error (3/8) e0^2 with e0 ~ 2^-22, i.e. ~1e-13
+  // one Newton step written as three dependent FMAs (a dependent DFMA takes ~9 cycles on this part,
+  // scripts/experiments/fp64_rate_probe.cu, and the pivot chain is pure latency): error (3/8) e0^2 with
+  // e0 ~ 2^-22, i.e. ~1e-13
   const double y0 = (double)rsqrtf((float)d);
   const double t = d * y0;
   const double e = fma(-t, y0, 1.0);

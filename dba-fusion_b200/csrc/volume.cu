@@ -80,17 +80,26 @@ k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int le
   extern __shared__ __half sm[];
   const int s0 = h2 * w2;
   const int h1 = h2 >> 1, w1 = w2 >> 1, hq = h2 >> 2, wq = w2 >> 2, he = h2 >> 3, we = w2 >> 3;
-  __half* a0 = sm;
-  __half* a1 = a0 + s0;
+  // the slab is fetched with aligned 16-byte loads whatever its own alignment (h2*w2 is odd for 55 x 55): the
+  // raw copy starts up to 7 halves before the slab, `a0` points at the slab inside it
+  __half* raw = sm;
+  __half* a1 = raw + ((s0 + 15) & ~7);
   __half* a2 = a1 + h1 * w1;
-  const bool vec = (s0 % 8 == 0) && ((reinterpret_cast<size_t>(L0) & 15) == 0);
+  const bool vec = (reinterpret_cast<size_t>(L0) & 15) == 0;
   for (long long s = blockIdx.x; s < slabs; s += gridDim.x) {
-    const __half* src = L0 + s * s0;
+    const long long first = s * s0;
+    const int off = vec ? (int)(first & 7) : 0;
+    const __half* a0 = raw + off;
     if (vec) {
-      for (int t = threadIdx.x; t < s0 / 8; t += 128)
-        reinterpret_cast<uint4*>(a0)[t] = __ldg(reinterpret_cast<const uint4*>(src) + t);
+      const uint4* src = reinterpret_cast<const uint4*>(L0 + (first - off));
+      const int nvec = (off + s0 + 7) >> 3;
+      // the last vector may reach past the end of the whole volume: it is then read element-wise
+      const bool tail_ok = first - off + (long long)nvec * 8 <= slabs * (long long)s0;
+      for (int t = threadIdx.x; t < nvec - (tail_ok ? 0 : 1); t += 128) reinterpret_cast<uint4*>(raw)[t] = __ldg(src + t);
+      if (!tail_ok)
+        for (int t = (nvec - 1) * 8 + threadIdx.x; t < off + s0; t += 128) raw[t] = L0[first - off + t];
     } else {
-      for (int t = threadIdx.x; t < s0; t += 128) a0[t] = src[t];
+      for (int t = threadIdx.x; t < s0; t += 128) raw[t] = L0[first + t];
     }
     __syncthreads();
     for (int t = threadIdx.x; t < h1 * w1; t += 128) {
@@ -149,7 +158,7 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
     DBAF_LAUNCH_CHECK("k_volume_simt");
   }
   if (levels > 1) {
-    const size_t smem = ((size_t)HW + (size_t)(ht / 2) * (wd / 2) + (size_t)(ht / 4) * (wd / 4)) * 2 + 16;
+    const size_t smem = ((size_t)((HW + 15) & ~7) + (size_t)(ht / 2) * (wd / 2) + (size_t)(ht / 4) * (wd / 4)) * 2 + 16;
     DBAF_REQUIRE(smem <= 200 * 1024, "feature map too large for the pyramid kernel");
     static bool attr = false;
     if (!attr) {

@@ -169,7 +169,6 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     const int m = m0 + q * 32 + lane;                 // this thread's source pixel
     const bool mok = m < HW;
     const size_t row = (size_t)e * HW + (mok ? m : 0);
-    __half* o0 = out.l[0] + row * (size_t)HW;
     uint32_t carry2[8];                               // level-2 row of the even chunk (FUSE)
 #pragma unroll
     for (int i = 0; i < 8; ++i) carry2[i] = 0;
@@ -276,35 +275,43 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
               make_uint4(l3[0], l3[1], l3[2], l3[3]);
         }
       } else {
-        // generic shapes: level 0 only, 256 consecutive target pixels per chunk
+        // generic shapes: level 0 only, 256 consecutive target pixels per chunk.  A row of the volume is
+        // HW halves, in general neither 16- nor 4-byte aligned (55 x 55, 28 x 107), so the lane-per-row
+        // accumulator layout is turned around through shared memory: the warp's 32 x 256 tile is staged with a
+        // 129-word row pitch (conflict-free both ways) and written out row by row, every store instruction
+        // covering 64 contiguous bytes of one row.
         const int n0 = c * kBN;
+        uint32_t* tile = reinterpret_cast<uint32_t*>(sStage + q * kStageWarp);      // [32][129] words
+        __syncwarp();                                    // the previous chunk's rows have been read out
 #pragma unroll 1
         for (int b = 0; b < kBN / 32; ++b) {
           float v[32];
           tc_ld32(t0 + (uint32_t)(b * 32), v);
-          const int nb = n0 + b * 32;
-          if (mok && nb < HW) {
-            __half* d = o0 + nb;
-            const bool vec = (nb + 32 <= HW) && ((reinterpret_cast<uintptr_t>(d) & 15) == 0);
-            if (vec) {
 #pragma unroll
-              for (int g = 0; g < 4; ++g) {
-                uint32_t w[4];
-#pragma unroll
-                for (int t = 0; t < 4; ++t)
-                  w[t] = pack_h2(__float2half_rn(v[8 * g + 2 * t]), __float2half_rn(v[8 * g + 2 * t + 1]));
-                reinterpret_cast<uint4*>(d)[g] = make_uint4(w[0], w[1], w[2], w[3]);
-              }
-            } else {
-#pragma unroll
-              for (int i = 0; i < 32; ++i)
-                if (nb + i < HW) d[i] = __float2half_rn(v[i]);
-            }
-          }
+          for (int i = 0; i < 16; ++i)
+            tile[lane * 129 + b * 16 + i] = pack_h2(__float2half_rn(v[2 * i]), __float2half_rn(v[2 * i + 1]));
         }
+        // the accumulator stage is free as soon as it sits in shared memory
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&bars[5 + s]));
+        const int ncol = min(kBN, HW - n0);
+        const int mrow0 = m0 + q * 32;
+        // (explicit shared-space loads, all eight issued before the first store: as generic loads with a store
+        //  behind each one this loop cost 20 k cycles per chunk)
+        const uint32_t tbase = smem_u32(tile) + (uint32_t)lane * 2u;
+        const int nrow = min(32, HW - mrow0);
+#pragma unroll 2
+        for (int r = 0; r < nrow; ++r) {
+          unsigned short* dst = reinterpret_cast<unsigned short*>(out.l[0]) + ((size_t)e * HW + mrow0 + r) * (size_t)HW + n0 + lane;
+          unsigned short v[kBN / 32];
+#pragma unroll
+          for (int k = 0; k < kBN / 32; ++k)
+            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v[k]) : "r"(tbase + (uint32_t)(r * 516 + k * 64)));
+#pragma unroll
+          for (int k = 0; k < kBN / 32; ++k)
+            if (k * 32 + lane < ncol) dst[k * 32] = v[k];
+        }
       }
     }
   }

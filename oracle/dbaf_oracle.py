@@ -12,8 +12,9 @@ Pinning status: DBA-Fusion ships no tests or golden vectors for this path
 (SURVEY.md section 4), so this restatement is pinned against outputs of the
 reference CUDA extension itself, rebuilt for sm_100a by ``oracle/build_ref.py``
 and run on the B200 box (``tests/test_ref_parity.py``; fixtures produced by
-``tests/golden/make_golden.py``).  Until those fixtures are committed the
-header of DESIGN.md says "parity unpinned".
+``tests/golden/make_golden.py``).  The fixtures are committed
+(``tests/golden/ref_tiny.npz``, ``ref_c1.npz``) and ``tests/test_golden.py``
+checks this file against them on CPU: parity is pinned.
 
 All arithmetic is done in ``dtype`` (float64 = "truth", float32 = same
 precision as the reference's kernels; numpy never fuses multiply-adds, the GPU
