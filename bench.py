@@ -201,18 +201,18 @@ def bench_local(args, dev, rank, world):
     # ---- end to end through the public API with host buffers
     host = {k: torch.from_numpy(win[k]).pin_memory() for k in
             ("poses", "disps", "disps_sens", "targets", "weights", "eta", "ii", "jj", "intrinsics")}
-    out_dx = torch.empty(t1 - t0, 6).pin_memory()
-    out_p = torch.empty(t1 - t0, 7).pin_memory()
     h2d = sum(host[k].numel() * host[k].element_size() for k in host)
-    d2h = out_dx.numel() * 4 + out_p.numel() * 4
+
+    hp0, hd0 = host["poses"].clone(), host["disps"].clone()
+    d2h = (t1 - t0) * 7 * 4 + host["disps"].numel() * 4 + (t1 - t0) * 6 * 4
 
     def e2e_step():
-        g = {k: v.to(dev, non_blocking=True) for k, v in host.items()}
-        dx, dz = db.ba(g["poses"], g["disps"], g["intrinsics"], g["disps_sens"], g["targets"], g["weights"],
-                       g["eta"], g["ii"], g["jj"], t0, t1, iters, 1e-4, 0.1, False)
-        out_dx.copy_(dx, non_blocking=True)
-        out_p.copy_(g["poses"][t0:t1], non_blocking=True)
-        torch.cuda.synchronize()
+        # the host-buffer entry point: inputs copied from pinned memory, iterations on the device, updated poses,
+        # disparities and dx copied back, stream synchronised before it returns
+        host["poses"].copy_(hp0)
+        host["disps"].copy_(hd0)
+        db.ba_host(host["poses"], host["disps"], host["intrinsics"], host["disps_sens"], host["targets"],
+                   host["weights"], host["eta"], host["ii"], host["jj"], t0, t1, iters, 1e-4, 0.1, False)
 
     for _ in range(args.warmup):
         e2e_step()

@@ -905,6 +905,80 @@ extern "C" int dbaf_ba(void* workspace, float* poses, float* disps, const float*
   return DBAF_OK;
 }
 
+// ------------------------------------------------------- host-buffer entry point ----
+namespace {
+struct HostStage {
+  size_t poses, disps, intr, sens, targets, weights, eta, ii, jj, dx, total;
+};
+HostStage host_stage_layout(int N, int E, int t0, int t1, int ht, int wd, int eta_rows) {
+  HostStage L{};
+  size_t off = 0;
+  auto take = [&](size_t bytes) { const size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+  const size_t HW = (size_t)ht * wd;
+  L.poses = take((size_t)N * 7 * 4);
+  L.disps = take((size_t)N * HW * 4);
+  L.intr = take(16);
+  L.sens = take((size_t)N * HW * 4);
+  L.targets = take((size_t)E * 2 * HW * 4);
+  L.weights = take((size_t)E * 2 * HW * 4);
+  L.eta = take((size_t)std::max(eta_rows, 1) * HW * 4);
+  L.ii = take((size_t)E * 8);
+  L.jj = take((size_t)E * 8);
+  L.dx = take((size_t)std::max(t1 - t0, 1) * 6 * 4);
+  L.total = off;
+  return L;
+}
+}  // namespace
+
+extern "C" size_t dbaf_ba_host_staging_bytes(int n_frames, int n_edges, int t0, int t1, int ht, int wd, int eta_rows) {
+  return host_stage_layout(n_frames, n_edges, t0, t1, ht, wd, eta_rows).total;
+}
+
+extern "C" int dbaf_ba_host(void* workspace, void* staging, size_t staging_bytes, float* poses_h, float* disps_h,
+                            const float* intrinsics_h, const float* disps_sens_h, const float* targets_h,
+                            const float* weights_h, const float* eta_h, int eta_rows, const int64_t* ii_h,
+                            const int64_t* jj_h, int E, int N, int t0, int t1, int ht, int wd, int iterations,
+                            float lm, float ep, int motion_only, float* dx_out_h, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr && staging != nullptr, "null workspace or staging buffer");
+  if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
+  DBAF_REQUIRE(poses_h && disps_h && intrinsics_h && disps_sens_h && ii_h && jj_h && (E == 0 || (targets_h && weights_h)),
+               "null host input");
+  DBAF_REQUIRE(motion_only == 1 || (eta_h != nullptr && eta_rows >= 1), "eta needs at least one row");
+  const HostStage L = host_stage_layout(N, E, t0, t1, ht, wd, eta_rows);
+  DBAF_REQUIRE(staging_bytes >= L.total, "staging buffer smaller than dbaf_ba_host_staging_bytes()");
+  cudaStream_t st = (cudaStream_t)stream;
+  char* d = static_cast<char*>(staging);
+  const size_t HW = (size_t)ht * wd;
+  const int P = t1 - t0;
+  auto up = [&](size_t off, const void* src, size_t bytes) {
+    return bytes == 0 ? cudaSuccess : cudaMemcpyAsync(d + off, src, bytes, cudaMemcpyHostToDevice, st);
+  };
+  DBAF_CUDA(up(L.poses, poses_h, (size_t)N * 7 * 4));
+  DBAF_CUDA(up(L.disps, disps_h, (size_t)N * HW * 4));
+  DBAF_CUDA(up(L.intr, intrinsics_h, 16));
+  DBAF_CUDA(up(L.sens, disps_sens_h, (size_t)N * HW * 4));
+  DBAF_CUDA(up(L.targets, targets_h, (size_t)E * 2 * HW * 4));
+  DBAF_CUDA(up(L.weights, weights_h, (size_t)E * 2 * HW * 4));
+  if (eta_h != nullptr) DBAF_CUDA(up(L.eta, eta_h, (size_t)eta_rows * HW * 4));
+  DBAF_CUDA(up(L.ii, ii_h, (size_t)E * 8));
+  DBAF_CUDA(up(L.jj, jj_h, (size_t)E * 8));
+  float* poses_d = reinterpret_cast<float*>(d + L.poses);
+  float* disps_d = reinterpret_cast<float*>(d + L.disps);
+  float* dx_d = reinterpret_cast<float*>(d + L.dx);
+  if (int rc = dbaf_ba(workspace, poses_d, disps_d, reinterpret_cast<const float*>(d + L.intr),
+                       reinterpret_cast<const float*>(d + L.sens), reinterpret_cast<const float*>(d + L.targets),
+                       reinterpret_cast<const float*>(d + L.weights), reinterpret_cast<const float*>(d + L.eta), eta_rows,
+                       reinterpret_cast<const int64_t*>(d + L.ii), reinterpret_cast<const int64_t*>(d + L.jj), E, N, t0, t1,
+                       ht, wd, iterations, lm, ep, motion_only, dx_out_h ? dx_d : nullptr, nullptr, stream))
+    return rc;
+  if (iterations > 0) {
+    if (P > 0) DBAF_CUDA(cudaMemcpyAsync(poses_h + (size_t)t0 * 7, poses_d + (size_t)t0 * 7, (size_t)P * 7 * 4, cudaMemcpyDeviceToHost, st));
+    if (!motion_only) DBAF_CUDA(cudaMemcpyAsync(disps_h, disps_d, (size_t)N * HW * 4, cudaMemcpyDeviceToHost, st));
+    if (dx_out_h && P > 0) DBAF_CUDA(cudaMemcpyAsync(dx_out_h, dx_d, (size_t)P * 6 * 4, cudaMemcpyDeviceToHost, st));
+  }
+  return DBAF_OK;
+}
+
 // ------------------------------------------------------- allocation-free graph tables ----
 //
 // dbaf_ba_tables_noalloc: the graph bookkeeping kernel (k_tables) for hosts that must not

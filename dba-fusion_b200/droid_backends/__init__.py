@@ -189,6 +189,55 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj,
     return [dx, dz]
 
 
+_host_cache = {}
+
+
+def ba_host(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj,
+            t0, t1, iterations, lm, ep, motion_only, device=None):
+    """`ba` for a window that lives in HOST memory (C entry point dbaf_ba_host; no reference counterpart, the
+    reference only takes CUDA tensors).  All arguments are CPU tensors with the shapes and dtypes of `ba`, ideally
+    pinned; poses[t0:t1] and disps are updated in place, dx [P,6] (CPU, pinned) is returned.  The inputs are
+    copied to a cached device staging buffer, the iterations run there, the results are copied back, and the call
+    returns after synchronising the stream."""
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    for name, t, dt in (("poses", poses, torch.float32), ("disps", disps, torch.float32),
+                        ("intrinsics", intrinsics, torch.float32), ("disps_sens", disps_sens, torch.float32),
+                        ("targets", targets, torch.float32), ("weights", weights, torch.float32),
+                        ("eta", eta, torch.float32), ("ii", ii, torch.int64), ("jj", jj, torch.int64)):
+        if t.is_cuda or t.dtype != dt or not t.is_contiguous():
+            raise RuntimeError(f"{name} must be a contiguous CPU tensor of {dt}")
+    if disps.dim() != 3 or poses.dim() != 2 or poses.shape[1] != 7:
+        raise RuntimeError("poses must be [N,7] and disps [N,ht,wd]")
+    N, ht, wd = disps.shape
+    E, HW = ii.numel(), ht * wd
+    if jj.numel() != E or targets.numel() != E * 2 * HW or weights.numel() != targets.numel():
+        raise RuntimeError("targets/weights must be [E,2,ht,wd] with E = len(ii) = len(jj)")
+    if poses.shape[0] < t1 or disps_sens.shape != disps.shape or not (0 <= t0 <= t1 <= N):
+        raise RuntimeError("need 0 <= t0 <= t1 <= N and matching poses/disps/disps_sens")
+    rows = eta.numel() // HW
+    if rows * HW != eta.numel() or (rows < 1 and not motion_only):
+        raise RuntimeError("eta must be [K,ht,wd]")
+    key = (dev.index, N, E, int(t0), int(t1), ht, wd, rows)
+    ent = _host_cache.get(key)
+    if ent is None:
+        L = _layout(N, E, int(t0), int(t1), ht, wd)
+        nstage = lib.dbaf_ba_host_staging_bytes(N, E, int(t0), int(t1), ht, wd, rows)
+        ent = (torch.empty(L.total_bytes, dtype=torch.uint8, device=dev),
+               torch.empty(nstage, dtype=torch.uint8, device=dev), nstage,
+               torch.empty(max(int(t1 - t0), 1), 6, dtype=torch.float32).pin_memory())
+        _host_cache.clear()            # one window shape at a time is the common case; do not hoard device memory
+        _host_cache[key] = ent
+    ws, stage, nstage, dx = ent
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream()
+        check(lib.dbaf_ba_host(_p(ws), _p(stage), nstage, _p(poses), _p(disps), _p(intrinsics), _p(disps_sens),
+                               _p(targets), _p(weights), _p(eta), rows, _p(ii), _p(jj), E, N, int(t0), int(t1), ht,
+                               wd, int(iterations), float(lm), float(ep), int(bool(motion_only)), _p(dx),
+                               c_void_p(stream.cuda_stream)), "dbaf_ba_host")
+        stream.synchronize()
+    return dx[:int(t1 - t0)]
+
+
 def _export(w, H, v):
     """Copy the undamped reduced system to the caller's float64 CPU tensors
     (src/droid_kernels.cu:1632-1640, 1889-1897: only H.size(0) x H.size(1) entries are written)."""

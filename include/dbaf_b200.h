@@ -217,6 +217,19 @@ int dbaf_ba(void* workspace, float* poses, float* disps, const float* intrinsics
             int n_edges, int n_frames, int t0, int t1, int ht, int wd, int iterations,
             float lm, float ep, int motion_only, float* dx_out, float* dz_out, void* stream);
 
+/* The same call for callers whose window lives in HOST memory (a frontend that assembles targets/weights on the
+ * CPU, a process that receives them over IPC): every input is copied to `staging` (device scratch of
+ * dbaf_ba_host_staging_bytes() bytes) with cudaMemcpyAsync on `stream`, dbaf_ba runs on the copies, and the updated
+ * poses[t0:t1], disps (unless motion_only) and dx_out_h [P,6] (may be NULL) are copied back.  Everything is enqueued
+ * on `stream`; the host buffers must stay valid, and should be pinned, until the caller has synchronised it.  No
+ * reference counterpart: droid_backends.ba only accepts CUDA tensors (src/droid.cpp:16-18 CHECK_INPUT). */
+size_t dbaf_ba_host_staging_bytes(int n_frames, int n_edges, int t0, int t1, int ht, int wd, int eta_rows);
+int dbaf_ba_host(void* workspace, void* staging, size_t staging_bytes, float* poses_h, float* disps_h,
+                 const float* intrinsics_h, const float* disps_sens_h, const float* targets_h,
+                 const float* weights_h, const float* eta_h, int eta_rows, const int64_t* ii_h,
+                 const int64_t* jj_h, int n_edges, int n_frames, int t0, int t1, int ht, int wd,
+                 int iterations, float lm, float ep, int motion_only, float* dx_out_h, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -413,3 +413,26 @@ def test_corrblock_mirror(dev, db, synth):
         assert alt.shape == out.shape
         tol = 6 * 2.0 ** -11 * blk.corr_pyramid[0].float().abs().max().item() + 1e-3
         assert (alt - out.float()).abs().max().item() <= tol
+
+
+def test_ba_host_matches_ba(dev, db, synth):
+    """dbaf_ba_host (host buffers in, host buffers out) gives the same poses, disparities and dx as ba on device
+    tensors, for full and motion-only BA; the second call reuses the cached staging buffers."""
+    for motion_only in (False, True):
+        w = synth.make_window("tiny", seed=7, sensor_frac=0.3)
+        t = to_torch(w, dev)
+        dx, _ = db.ba(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], t["eta"],
+                      t["ii"], t["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, motion_only)
+        h = {k: torch.from_numpy(w[k].copy()).pin_memory() for k in
+             ("poses", "disps", "intrinsics", "disps_sens", "targets", "weights", "eta", "ii", "jj")}
+        for _ in range(2):
+            hp, hd = h["poses"].clone().pin_memory(), h["disps"].clone().pin_memory()
+            dxh = db.ba_host(hp, hd, h["intrinsics"], h["disps_sens"], h["targets"], h["weights"], h["eta"], h["ii"],
+                             h["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, motion_only)
+            # same kernels on the same numbers; only the order of the float64 atomics may differ between runs
+            assert relerr(hp.numpy(), t["poses"].cpu().numpy()) < 1e-6
+            assert relerr(hd.numpy(), t["disps"].cpu().numpy()) < 1e-6
+            assert relerr(dxh.numpy(), dx.cpu().numpy()) < 1e-5
+    with pytest.raises(RuntimeError, match="CPU tensor"):
+        db.ba_host(t["poses"], h["disps"], h["intrinsics"], h["disps_sens"], h["targets"], h["weights"], h["eta"],
+                   h["ii"], h["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, False)
