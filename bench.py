@@ -313,6 +313,10 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
                 steps, 3, flush))
     except Exception as ex:      # the reference extension is optional on the box
         ref["error"] = str(ex)[:200]
+    # the caller that feeds the lookup: DepthVideo.reproject as one kernel (4 B read + 12 B written per pixel-edge)
+    tw = window_tensors(win, dev)
+    rep_ms = statistics.mean(timed_steps(lambda: db.reproject(tw["poses"], tw["disps"], tw["intrinsics"], ii, jj), steps, 3, flush))
+    rep_bytes = n * HW * 16
     lvl = sum((ht >> l) * (wd >> l) for l in range(4))
     vol_bytes = n * (2 * HW * 128 * 2 + 2 * HW * lvl)             # read both fmaps, write 4 levels
     vol_flop = n * 2.0 * HW * HW * 128
@@ -336,6 +340,10 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
                     roofline=dict(bound="hbm", kernel="k_corr_lookup", achieved=look_bytes / (look_ms * 1e-3) / 1e9,
                                   peak=peaks["hbm"], unit="GB/s", frac=look_bytes / (look_ms * 1e-3) / 1e9 / peaks["hbm"],
                                   traffic=NCU_TRAFFIC_BYTES.get((cfg, "k_corr_lookup")))),
+        reproject=dict(ms=rep_ms, edges_per_s=n / (rep_ms * 1e-3),
+                       roofline=dict(bound="hbm", kernel="k_reproject", achieved=rep_bytes / (rep_ms * 1e-3) / 1e9,
+                                     peak=peaks["hbm"], unit="GB/s", frac=rep_bytes / (rep_ms * 1e-3) / 1e9 / peaks["hbm"]),
+                       note="reference: ~10 torch elementwise ops + lietorch act4 (not installed here), not timed"),
         edges=n, reference_same_gpu=ref)
 
 

@@ -47,6 +47,36 @@ k_projmap(const float* __restrict__ poses, const float* __restrict__ disps,
   valid[(size_t)e * HW + p] = Xj[2] > kMinDepth ? 1.0f : 0.0f;
 }
 
+// DepthVideo.reproject -> pops.projective_transform without Jacobians (dbaf/depth_video.py:221-229,
+// dbaf/geom/projective_ops.py:96-125,38-50): X0 = iproj(disps[ii]) with the intrinsics of frame ii, Gij = Tj Ti^-1
+// (stereo edge ii == jj: t = (-0.1, 0, 0), identity rotation), X1 = Gij X0, pinhole projection with the
+// intrinsics of frame jj where Z < 0.1 is replaced by 1, valid = X1.z > 0.2 (MIN_DEPTH of geom, not the 0.25
+// of the CUDA backend).  The reference builds this from ~10 elementwise torch ops over poses repeated per
+// pixel; here it is one pass: 4 B read and 12 B written per pixel-edge.
+__global__ void __launch_bounds__(kThreads)
+k_reproject(const float* __restrict__ poses, const float* __restrict__ disps, const float* __restrict__ intr,
+            int intr_stride, const int64_t* __restrict__ ii, const int64_t* __restrict__ jj, int HW, int wd,
+            float2* __restrict__ coords, float* __restrict__ valid) {
+  const int e = blockIdx.y;
+  const int p = blockIdx.x * kThreads + threadIdx.x;
+  if (p >= HW) return;
+  const int ix = (int)ii[e], jx = (int)jj[e];
+  const float* Ki = intr + (size_t)ix * intr_stride;
+  const float* Kj = intr + (size_t)jx * intr_stride;
+  Se3 G;
+  if (ix == jx) G = stereo_baseline();
+  else G = load_relative(poses, ix, jx);
+  const int i = p / wd, j = p - i * wd;
+  const float Xi[4] = {((float)j - __ldg(Ki + 2)) / __ldg(Ki), ((float)i - __ldg(Ki + 3)) / __ldg(Ki + 1), 1.0f,
+                       __ldg(disps + (size_t)ix * HW + p)};
+  float Xj[4];
+  act(G, Xi, Xj);
+  const float z = Xj[2] < 0.1f ? 1.0f : Xj[2];
+  const float d = 1.0f / z;
+  coords[(size_t)e * HW + p] = make_float2(__ldg(Kj) * (Xj[0] * d) + __ldg(Kj + 2), __ldg(Kj + 1) * (Xj[1] * d) + __ldg(Kj + 3));
+  valid[(size_t)e * HW + p] = Xj[2] > 0.2f ? 1.0f : 0.0f;
+}
+
 // frame_distance_kernel, src/droid_kernels.cu:562-702.  One CTA per pair; three block sums.
 __global__ void __launch_bounds__(kThreads)
 k_frame_distance(const float* __restrict__ poses, const float* __restrict__ disps,
@@ -180,6 +210,20 @@ extern "C" int dbaf_projmap(const float* poses, const float* disps, const float*
   dim3 grid((HW + kThreads - 1) / kThreads, E);
   k_projmap<<<grid, kThreads, 0, (cudaStream_t)stream>>>(poses, disps, intrinsics, ii, jj, HW, wd, coords, valid);
   DBAF_LAUNCH_CHECK("k_projmap");
+  return DBAF_OK;
+}
+
+extern "C" int dbaf_reproject(const float* poses, const float* disps, const float* intrinsics, int per_frame_intrinsics,
+                              const int64_t* ii, const int64_t* jj, int E, int ht, int wd, float* coords,
+                              float* valid, void* stream) {
+  DBAF_REQUIRE(E >= 0 && ht > 0 && wd > 0, "bad sizes");
+  DBAF_REQUIRE((reinterpret_cast<uintptr_t>(coords) & 7) == 0, "coords must be 8-byte aligned");
+  if (E == 0) return DBAF_OK;
+  const int HW = ht * wd;
+  dim3 grid((HW + kThreads - 1) / kThreads, E);
+  k_reproject<<<grid, kThreads, 0, (cudaStream_t)stream>>>(poses, disps, intrinsics, per_frame_intrinsics ? 4 : 0, ii, jj, HW,
+                                                          wd, reinterpret_cast<float2*>(coords), valid);
+  DBAF_LAUNCH_CHECK("k_reproject");
   return DBAF_OK;
 }
 

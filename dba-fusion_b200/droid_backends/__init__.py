@@ -465,6 +465,25 @@ def altcorr_backward(fmap1, fmap2, coords, corr_grad, radius):
     return [g1, g2, gc]
 
 
+def reproject(poses, disps, intrinsics, ii, jj):
+    """DepthVideo.reproject (dbaf/depth_video.py:221-229 -> geom/projective_ops.py:96-125, no Jacobians) in one
+    kernel.  poses [N,7], disps [N,ht,wd], intrinsics [4] or [N,4], ii/jj [E] -> coords [1,E,ht,wd,2] and
+    valid [1,E,ht,wd,1], the shapes the reference returns for its batch of one."""
+    _contig(poses=poses, disps=disps, intrinsics=intrinsics, ii=ii, jj=jj)
+    _cuda(torch.float32, poses=poses, disps=disps, intrinsics=intrinsics)
+    _cuda(torch.int64, ii=ii, jj=jj)
+    N, ht, wd = disps.shape
+    per_frame = intrinsics.dim() == 2
+    if intrinsics.numel() != (4 * N if per_frame else 4) or ii.shape != jj.shape:
+        raise RuntimeError("intrinsics must be [4] or [N,4]; ii and jj must have the same length")
+    E = ii.numel()
+    coords = torch.empty(1, E, ht, wd, 2, dtype=torch.float32, device=poses.device)
+    valid = torch.empty(1, E, ht, wd, 1, dtype=torch.float32, device=poses.device)
+    check(lib.dbaf_reproject(_p(poses), _p(disps), _p(intrinsics), int(per_frame), _p(ii), _p(jj), E, ht, wd,
+                             _p(coords), _p(valid), _stream()), "dbaf_reproject")
+    return coords, valid
+
+
 def corr_volume_pyramid(fmap1, fmap2, num_levels=4):
     """Native CorrBlock.__init__ (dbaf/modules/corr.py:24-38,63-71): fmap1, fmap2 [n,C,ht,wd]
     float16 -> list of `num_levels` tensors [n,ht,wd,ht>>l,wd>>l] float16."""

@@ -38,6 +38,7 @@ SIGNATURES = {
     "dbaf_corr_index_backward": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P, P]),
     "dbaf_altcorr_forward": (c_int, [P, P, P] + [c_int] * 8 + [P, P]),
     "dbaf_altcorr_backward": (c_int, [P, P, P, P] + [c_int] * 8 + [P, P, P, P]),
+    "dbaf_reproject": (c_int, [P, P, P, c_int, P, P, c_int, c_int, c_int, P, P, P]),
     "dbaf_corr_volume_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
     "dbaf_corr_volume_pyramid": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int,
                                          ctypes.POINTER(c_void_p), P, c_size_t, P]),

@@ -44,6 +44,16 @@ int dbaf_projmap(const float* poses, const float* disps, const float* intrinsics
                  const int64_t* ii, const int64_t* jj, int n_edges, int ht, int wd,
                  float* coords, float* valid, void* stream);
 
+/* DepthVideo.reproject / pops.projective_transform without Jacobians, dbaf/depth_video.py:221-229,
+ * dbaf/geom/projective_ops.py:96-125 (a "next" row of the scope table: the caller that produces the lookup
+ * coordinates).  intrinsics: [4] shared, or [N,4] per frame with per_frame_intrinsics = 1 (frame ii for the
+ * back-projection, frame jj for the projection, as the reference indexes them).  coords [E,ht,wd,2],
+ * valid [E,ht,wd] (1.0 where the transformed depth exceeds 0.2).  Stereo edges (ii == jj) use the fixed
+ * baseline (-0.1, 0, 0). */
+int dbaf_reproject(const float* poses, const float* disps, const float* intrinsics, int per_frame_intrinsics,
+                   const int64_t* ii, const int64_t* jj, int n_edges, int ht, int wd, float* coords,
+                   float* valid, void* stream);
+
 /* droid_backends.frame_distance, src/droid.cpp:181-197, src/droid_kernels.cu:562-702.  dist [M]. */
 int dbaf_frame_distance(const float* poses, const float* disps, const float* intrinsics,
                         const int64_t* ii, const int64_t* jj, int n_pairs, int ht, int wd,

@@ -492,6 +492,36 @@ def projmap(poses, disps, intr, ii, jj, dtype=np.float32):
     return coords.reshape(n, ht, wd, 3), valid.reshape(n, ht, wd, 1)
 
 
+def reproject(poses, disps, intr, ii, jj, dtype=np.float32):
+    """DepthVideo.reproject, dbaf/depth_video.py:221-229 -> projective_transform without Jacobians,
+    dbaf/geom/projective_ops.py:96-125: iproj with the intrinsics of frame ii (:18-31), Gij = Tj * Ti^-1 with
+    the stereo special case (:104-106), act (:67-69), proj with Z < 0.5*MIN_DEPTH -> 1 (:38-46),
+    valid = X1.z > MIN_DEPTH(0.2) & X0.z(=1) > MIN_DEPTH (:114-115).  intr: [4] or [N,4].
+    Returns coords [E,ht,wd,2], valid [E,ht,wd,1]."""
+    poses = np.asarray(poses, dtype)
+    N, ht, wd = disps.shape
+    HW = ht * wd
+    K = np.asarray(intr, dtype)
+    K = np.broadcast_to(K, (N, 4)) if K.ndim == 1 else K
+    ii, jj = np.asarray(ii), np.asarray(jj)
+    n = len(ii)
+    v, u = np.meshgrid(np.arange(ht, dtype=dtype), np.arange(wd, dtype=dtype), indexing="ij")
+    u, v = u.reshape(1, HW), v.reshape(1, HW)
+    Ki, Kj = K[ii], K[jj]
+    X0 = (u - Ki[:, 2:3]) / Ki[:, 0:1]
+    X1 = (v - Ki[:, 3:4]) / Ki[:, 1:2]
+    tij, qij = _edge_transforms(poses, ii, jj, stereo_special=True)
+    d0 = np.asarray(disps, dtype).reshape(N, HW)[ii]
+    Xi = np.stack([X0, X1, np.ones((n, HW), dtype), d0], -1)
+    Xj = act_se3(tij[:, None], qij[:, None], Xi)
+    z = Xj[..., 2]
+    zc = np.where(z < dtype(0.1), dtype(1.0), z)
+    d = dtype(1.0) / zc
+    coords = np.stack([Kj[:, 0:1] * (Xj[..., 0] * d) + Kj[:, 2:3], Kj[:, 1:2] * (Xj[..., 1] * d) + Kj[:, 3:4]], -1)
+    valid = (z > dtype(0.2)).astype(dtype)
+    return coords.reshape(n, ht, wd, 2).astype(dtype), valid.reshape(n, ht, wd, 1)
+
+
 def frame_distance(poses, disps, intr, ii, jj, beta, dtype=np.float32):
     """frame_distance_kernel, src/droid_kernels.cu:562-702 (one direction only, n<1 loop)."""
     poses = np.asarray(poses, dtype)

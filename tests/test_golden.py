@@ -208,3 +208,43 @@ def test_cuda_geometry_and_correlation_match_golden(dev, db, oracle, synth):
     ac = ct.permute(0, 2, 3, 1)[:, None].contiguous()
     alt, = db.altcorr_forward(af1, af2, ac, 3)
     assert relerr(alt.cpu().numpy(), g["altcorr"]) < 1e-5
+
+
+# ----------------------------------------------------------------- reproject
+def _reproject_cases():
+    g = np.load(os.path.join(HERE, "golden", "ref_reproject.npz"))
+    for name in ("tiny", "c3"):
+        yield name, {k[len(name) + 1:]: g[k] for k in g.files if k.startswith(name + "_")}
+
+
+def test_oracle_reproject_matches_reference_python(oracle):
+    """oracle.reproject against dbaf/geom/projective_ops.py run on CPU (tests/golden/make_golden_reproject.py):
+    coordinates to 2e-3 px where the point is in front of the camera (fp32 evaluation order differs), validity
+    exact away from the 0.2 threshold; stereo edges and per-frame intrinsics are in the fixture."""
+    for name, c in _reproject_cases():
+        assert (c["ii"] == c["jj"]).any()
+        for dt, tol in ((np.float64, 2e-3), (np.float32, 4e-3)):
+            coords, valid = oracle.reproject(c["poses"], c["disps"], c["intr"], c["ii"], c["jj"], dtype=dt)
+            front = c["valid"][..., 0] > 0
+            assert np.abs(coords - c["coords"])[front].max() < tol, (name, dt)
+            assert (valid != c["valid"]).mean() < 1e-3, name
+
+
+@pytest.mark.gpu
+def test_reproject_matches_golden_and_oracle(dev, db, oracle):
+    import torch
+    for name, c in _reproject_cases():
+        t = {k: torch.from_numpy(v).to(dev) for k, v in c.items()}
+        coords, valid = db.reproject(t["poses"], t["disps"], t["intr"], t["ii"], t["jj"])
+        assert coords.shape == (1,) + c["coords"].shape and valid.shape == (1,) + c["valid"].shape
+        front = c["valid"][..., 0] > 0
+        got = coords[0].cpu().numpy()
+        assert np.abs(got - c["coords"])[front].max() < 4e-3, name
+        assert (valid[0].cpu().numpy() != c["valid"]).mean() < 1e-3
+        want, wv = oracle.reproject(c["poses"], c["disps"], c["intr"], c["ii"], c["jj"], dtype=np.float64)
+        assert np.abs(got - want)[front].max() < 4e-3
+        # shared intrinsics: a [4] vector gives the same as the same row repeated
+        K1 = t["intr"][0].contiguous()
+        a, _ = db.reproject(t["poses"], t["disps"], K1, t["ii"], t["jj"])
+        b, _ = db.reproject(t["poses"], t["disps"], K1[None].repeat(t["poses"].shape[0], 1).contiguous(), t["ii"], t["jj"])
+        assert torch.equal(a, b)
