@@ -643,6 +643,7 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
 
 #include "ba_fast.cuh"
 #include "ba_banded.cuh"
+#include "ba_banded_reg.cuh"
 #include "ba_lin2.cuh"
 #include "ba_schur_tc.cuh"
 
@@ -815,8 +816,23 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       plan.part[0] = BandPart{0, P, P, 0};
       plan.part[1] = plan.part[0];
     }
-    k_solve_banded<<<plan.twisted ? 2 : 1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
-    DBAF_LAUNCH_CHECK("k_solve_banded");
+    // B <= 20: the sweep that keeps the window in registers; DBAF_BAND_SWEEP=smem keeps the shared-memory window
+    const char* sweep_impl = std::getenv("DBAF_BAND_SWEEP");
+    const bool smem_sweep = B > kBandRegMaxB || (sweep_impl != nullptr && std::strcmp(sweep_impl, "smem") == 0);
+    if (smem_sweep) {
+      k_solve_banded<<<plan.twisted ? 2 : 1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
+      DBAF_LAUNCH_CHECK("k_solve_banded");
+    } else {
+      const size_t rsm = std::max((size_t)NB * (2 * kPnS + 6) + 84 + 4 + (size_t)NB * (NB - 1) * 18 + NB * 42,
+                                  (size_t)band_back_smem_doubles(B)) * sizeof(double);
+      static bool reg_attr[64] = {};
+      if (!reg_attr[dev_id & 63]) {
+        DBAF_CUDA(cudaFuncSetAttribute(k_solve_banded_reg, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        reg_attr[dev_id & 63] = true;
+      }
+      k_solve_banded_reg<<<plan.twisted ? 2 : 1, kBandThreads, rsm, st>>>(P, B, lm, ep, plan, ws);
+      DBAF_LAUNCH_CHECK("k_solve_banded_reg");
+    }
     if (plan.twisted) {
       const int ns = 6 * B;
       const size_t ssm = ((size_t)(ns + 1) * (ns | 1) + 2 * ns) * sizeof(double);

@@ -80,15 +80,19 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
   };
   // stage for step J: block row J of the band store (L_JJ, L_{J,J-1}, .. L_{J,J-B}; entries whose column was
   // never eliminated hold garbage and are skipped below), then 1/diag(J) and y of row J-B
+  const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring) + lane * 16;
+  const int npiece = RD / 2;                         // 16-byte pieces of a block row of L
   auto issue = [&](int J) {
     if (J >= 0) {
-      double* dst = ring + (J % kBackDepth) * SD;
-      const double* src = Lband + (size_t)J * RD;
-      for (int q = lane; q < RD / 2; q += 32) cp16(dst + 2 * q, src + 2 * q, 16);
-      if (lane < 3) cp16(dst + RD + 2 * lane, dinv_g + 6 * (J < pt.n_elim ? J : 0) + 2 * lane, 16);
+      const unsigned dst = ring_s + (unsigned)((J % kBackDepth) * SD * 8);
+      const double* src = Lband + (size_t)J * RD + 2 * lane;
+      for (int q = 0; q * 32 + lane < npiece; ++q)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + q * 512), "l"(src + q * 64) : "memory");
+      double* dtail = ring + (J % kBackDepth) * SD + RD;
+      if (lane < 3) cp16(dtail + 2 * lane, dinv_g + 6 * (J < pt.n_elim ? J : 0) + 2 * lane, 16);
       if (lane >= 3 && lane < 6) {
         const int I = J - B, ok = I >= 0 && I < pt.n_elim;
-        cp16(dst + RD + 2 * lane, y_g + 6 * (ok ? I : 0) + 2 * (lane - 3), ok ? 16 : 0);
+        cp16(dtail + 2 * lane, y_g + 6 * (ok ? I : 0) + 2 * (lane - 3), ok ? 16 : 0);
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -104,6 +108,16 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
     for (int e = lane; e < 6 * B; e += 32) xsep[e] = xsep_g[e];
   __syncwarp();
 
+  // per-lane constants of the update: item u is (block offset o, component c) = divmod(lane + 32 u, 6)
+  int it_o[5], it_c[5];
+#pragma unroll
+  for (int u = 0; u < 5; ++u) {
+    it_o[u] = (lane + 32 * u) / 6;
+    it_c[u] = (lane + 32 * u) - 6 * it_o[u];
+  }
+  int jr = (P - 1) % NB;                             // J mod NB, kept incrementally
+  int jb = ((P - 1 - B) % NB + NB) % NB;             // (J - B) mod NB
+  int slot = (P - 1) % kBackDepth;                   // J mod kBackDepth
 #ifdef DBAF_BAND_PROFILE
   long long bt[4] = {0, 0, 0, 0}, b0, b1;
 #define BK_TICK(i) do { b1 = clock64(); bt[i] += b1 - b0; b0 = b1; } while (0)
@@ -119,8 +133,8 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
     asm volatile("cp.async.wait_group %0;" ::"n"(kBackDepth - 1) : "memory");
     __syncwarp();
     BK_TICK(1);
-    const double* st = ring + (J % kBackDepth) * SD;
-    if (lane < 6 && J - B >= 0) yw[((J - B) % NB) * 6 + lane] = st[RD + 6 + lane];
+    const double* st = ring + slot * SD;
+    if (lane < 6 && J - B >= 0) yw[jb * 6 + lane] = st[RD + 6 + lane];
     if (lane == 0) {
       double x[6];
       if (J >= pt.n_elim) {
@@ -130,7 +144,7 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
         const double* L = st;
         const double* di = st + RD;
 #pragma unroll
-        for (int r = 0; r < 6; ++r) x[r] = yw[(J % NB) * 6 + r];
+        for (int r = 0; r < 6; ++r) x[r] = yw[jr * 6 + r];
         // column sweep: as soon as x[c] is final the rows above it are corrected, so the serial chain per
         // unknown is one multiply and one fused multiply-add
 #pragma unroll
@@ -140,8 +154,9 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
           for (int k = 0; k < 6; ++k)
             if (k < c) x[k] -= L[c * 6 + k] * x[c];
         }
+        float* dxo = ws.dx + 6 * phys(J);
 #pragma unroll
-        for (int c = 0; c < 6; ++c) ws.dx[6 * phys(J) + c] = (float)x[c];
+        for (int c = 0; c < 6; ++c) dxo[c] = (float)x[c];
       }
 #pragma unroll
       for (int c = 0; c < 6; ++c) xs[c] = x[c];
@@ -152,20 +167,25 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
 #pragma unroll
     for (int r = 0; r < 6; ++r) xv[r] = xs[r];
     const int nab = min(B, J);                       // rows above J inside the band
+    const int first_elim = J - pt.n_elim;            // items with o < first_elim belong to separator x separator blocks
     // fixed trip count (6B <= 150 items over 32 lanes) so that the five dot products overlap
 #pragma unroll
     for (int u = 0; u < 5; ++u) {
-      const int t = lane + 32 * u;
-      const int o = t / 6, c = t - o * 6;
-      if (t < nab * 6 && J - 1 - o < pt.n_elim) {    // (separator x separator blocks are never formed)
+      const int o = it_o[u], c = it_c[u];
+      if (o < nab && o >= first_elim) {
         const double* q = st + (o + 1) * 36 + c;
         double sum = 0.0;
 #pragma unroll
         for (int r = 0; r < 6; ++r) sum += q[r * 6] * xv[r];
-        yw[((J - 1 - o) % NB) * 6 + c] -= sum;
+        int row = jr - 1 - o;
+        if (row < 0) row += NB;
+        yw[row * 6 + c] -= sum;
       }
     }
     // no barrier here: the one after the next wait_group orders these updates before lane 0 reads them
+    jr = jr == 0 ? NB - 1 : jr - 1;
+    jb = jb == 0 ? NB - 1 : jb - 1;
+    slot = slot == 0 ? kBackDepth - 1 : slot - 1;
     BK_TICK(3);
   }
 #ifdef DBAF_BAND_PROFILE
