@@ -68,6 +68,7 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
   __shared__ float part[kLinChunk][kWarps][28];      // per-warp sums of the 27 terms of every edge of the chunk
   __shared__ float tot[kLinChunk][28];
   __shared__ float Tm[kLinChunk][36];
+  __shared__ int sedge[kLinChunk + 1];               // edge ids of the chunk and the first one of the next chunk
 
   int px[PXT];
   bool ok[PXT];
@@ -91,9 +92,8 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
   // targets and weights of the next edge are requested while the current edge is being worked on (the
   // kernel is otherwise exposed to one full memory latency per edge): tw[s] = {wu, wv, tu, tv}
   float4 tw_next[PXT];
-  auto fetch_edge = [&](int pos) {
+  auto fetch_edge = [&](int pos, int e) {
     if (pos < e_hi) {
-      const int e = ws.csr_idx[pos];
 #pragma unroll
       for (int s = 0; s < PXT; ++s) {
         const size_t o = ((size_t)e * 2) * HW + (ok[s] ? px[s] : 0);
@@ -101,14 +101,18 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
       }
     }
   };
-  fetch_edge(e_lo);
+  fetch_edge(e_lo, e_lo < e_hi ? ws.csr_idx[e_lo] : 0);
   for (int base = e_lo; base < e_hi; base += kLinChunk) {
     const int cnt = min(kLinChunk, e_hi - base);
     __syncthreads();                                   // previous chunk's transforms no longer in use
-    if (tid < cnt) edge_xf(poses, ix, (int)jj[ws.csr_idx[base + tid]], sx[tid]);
+    if (tid <= cnt && base + tid < e_hi) {
+      const int eid = ws.csr_idx[base + tid];
+      sedge[tid] = eid;
+      if (tid < cnt) edge_xf(poses, ix, (int)jj[eid], sx[tid]);
+    }
     __syncthreads();
     for (int a = 0; a < cnt; ++a) {
-      const int e = ws.csr_idx[base + a];
+      const int e = sedge[a];
       const EdgeXf& X = sx[a];
       const bool stereo = X.stereo != 0;
       Se3 G;
@@ -123,7 +127,7 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
       float4 tw_cur[PXT];
 #pragma unroll
       for (int s = 0; s < PXT; ++s) tw_cur[s] = tw_next[s];
-      fetch_edge(base + a + 1);
+      fetch_edge(base + a + 1, sedge[a + 1]);
 
 #pragma unroll
       for (int s = 0; s < PXT; ++s) {
@@ -140,9 +144,10 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
         float wv = near ? 0.0f : (float)(0.001 * (double)tw_cur[s].y);
         const float ru = tw_cur[s].z - (fx * d * x + cx);
         const float rv = tw_cur[s].w - (fy * d * y + cy);
-        const float Ju[6] = {fx * (hh * d), fx * 0.f, fx * (-x * hh * d2), fx * (-x * y * d2),
+        // Ju[1] and Jv[0] are structural zeros (src/droid_kernels.cu:356-361,389-394): their terms are skipped
+        const float Ju[6] = {fx * (hh * d), 0.f, fx * (-x * hh * d2), fx * (-x * y * d2),
                              fx * (1.0f + x * x * d2), fx * (-y * d)};
-        const float Jv[6] = {fy * 0.f, fy * (hh * d), fy * (-y * hh * d2), fy * (-1.0f - y * y * d2),
+        const float Jv[6] = {0.f, fy * (hh * d), fy * (-y * hh * d2), fy * (-1.0f - y * y * d2),
                              fy * (x * y * d2), fy * (x * d)};
         const float Jzu = fx * (G.t[0] * d - G.t[2] * (x * d2));
         const float Jzv = fy * (G.t[1] * d - G.t[2] * (y * d2));
@@ -152,14 +157,23 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
         }
         if (stereo) { wu = 0.f; wv = 0.f; }            // stereo edges feed the depth blocks only
         {
+          float wJu[6], wJv[6];
+#pragma unroll
+          for (int n = 0; n < 6; ++n) { wJu[n] = wu * Ju[n]; wJv[n] = wv * Jv[n]; }
           int l = 0;
 #pragma unroll
           for (int n = 0; n < 6; ++n)
 #pragma unroll
-            for (int m = 0; m <= n; ++m) { h[l] += wu * Ju[n] * Ju[m] + wv * Jv[n] * Jv[m]; ++l; }
-          const float wru = wu * ru, wrv = wv * rv;
+            for (int m = 0; m <= n; ++m) {
+              if (n != 1 && m != 1) h[l] = fmaf(wJu[n], Ju[m], h[l]);
+              if (n != 0 && m != 0) h[l] = fmaf(wJv[n], Jv[m], h[l]);
+              ++l;
+            }
 #pragma unroll
-          for (int n = 0; n < 6; ++n) h[21 + n] += wru * Ju[n] + wrv * Jv[n];
+          for (int n = 0; n < 6; ++n) {
+            if (n != 1) h[21 + n] = fmaf(wJu[n], ru, h[21 + n]);
+            if (n != 0) h[21 + n] = fmaf(wJv[n], rv, h[21 + n]);
+          }
         }
         if (!MOTION_ONLY) {
           const float wzu = wu * Jzu, wzv = wv * Jzv;
@@ -167,7 +181,7 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
           float* Eo = ws.Eij + (size_t)e * 6 * HW + p;
 #pragma unroll
           for (int n = 0; n < 6; ++n) {
-            Ej[n] = wzu * Ju[n] + wzv * Jv[n];
+            Ej[n] = n == 0 ? wzu * Ju[0] : n == 1 ? wzv * Jv[1] : wzu * Ju[n] + wzv * Jv[n];
             Eo[(size_t)n * HW] = Ej[n];
           }
           if (has_self) {
