@@ -273,3 +273,40 @@ def test_global_ba_single_rank_matches_oracle(dev, db, oracle, synth):
     part += e2.system()
     e2.linearize(0.05, 0, -1)
     assert relerr(part.cpu().numpy(), e2.system().cpu().numpy()) < 1e-12
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P,B", [(64, 1), (65, 3), (70, 20), (97, 7), (128, 20), (203, 13), (66, 21), (90, 25), (40, 5), (63, 20)])
+def test_banded_solvers_on_random_band_systems(dev, db, oracle, synth, monkeypatch, P, B):
+    """Every banded code path (register window B <= 20, shared-memory window B <= 25, twisted for P >= 64 and
+    P >= 3B+2, single sweep otherwise) on random block-banded SPD systems written straight into the workspace:
+    dx against numpy's dense float64 solve."""
+    rng = np.random.default_rng(100 * P + B)
+    w = synth.make_window("tiny", seed=1, n_extra_frames=P + 1 - 5, graph="banded", reach=1)
+    assert w["t1"] - w["t0"] == P
+    n = 6 * P
+    G = rng.normal(0, 1, (n, n))
+    blk = np.arange(n) // 6
+    G[np.abs(blk[:, None] - blk[None, :]) > B // 2 + (B % 2)] = 0.0      # G G^T then has block bandwidth <= B
+    H = G @ G.T
+    H[np.abs(blk[:, None] - blk[None, :]) > B] = 0.0
+    H += np.diag(rng.uniform(1.0, 2.0, n)) * n * 0.05
+    v = rng.normal(0, 1, n)
+    want, ok = oracle.damped_solve(H, v, 1e-4, 0.1)
+    assert ok
+    res = {}
+    for sweep in ("reg", "smem"):
+        for impl in ("auto", "single"):
+            monkeypatch.setenv("DBAF_BAND_SWEEP", "smem") if sweep == "smem" else monkeypatch.delenv("DBAF_BAND_SWEEP", raising=False)
+            monkeypatch.setenv("DBAF_BAND_IMPL", "single") if impl == "single" else monkeypatch.delenv("DBAF_BAND_IMPL", raising=False)
+            t = to_torch(w, dev)
+            win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                             t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+            win.prepare()                                   # initialises the info words
+            win.H().copy_(torch.from_numpy(H).to(dev))
+            win.v().copy_(torch.from_numpy(v).to(dev))
+            win.solve(1e-4, 0.1, band=B)
+            assert int(win.info().cpu()[1]) == 0
+            got = win.dx().cpu().numpy().reshape(-1)
+            res[(sweep, impl)] = got
+            assert relerr(got, want) < 2e-6, (sweep, impl, relerr(got, want))
