@@ -310,3 +310,51 @@ def test_banded_solvers_on_random_band_systems(dev, db, oracle, synth, monkeypat
             got = win.dx().cpu().numpy().reshape(-1)
             res[(sweep, impl)] = got
             assert relerr(got, want) < 2e-6, (sweep, impl, relerr(got, want))
+
+
+@pytest.mark.gpu
+def test_c5_full_size_properties(dev, db, synth):
+    """BASELINE.json configs[4] at full size (1000 keyframes, 19 890 edges, 64x64): too large for the oracle, so
+    the checks are size-independent properties: the reduced system of two shards sums to the unsharded one
+    (linearity of the edge partition), it is symmetric and confined to the band, the banded solve satisfies the
+    damped normal equations to float64 accuracy, and one Gauss-Newton step lowers the reprojection cost."""
+    from dbaf_b200 import global_ba
+    w = synth.make_window("c5", seed=0, graph="banded", pose_noise=0.005)
+    t = to_torch(w, dev)
+    eng = global_ba.CudaEngine(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                               t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+    gba = global_ba.GlobalBA(eng, w["ii"], w["jj"], w["t0"], w["t1"])
+    assert gba.band == 20
+    n = eng.w.n
+    (a0, a1), (b0, b1) = global_ba.shard_ranges(w["ii"], w["t0"], w["t1"], 2)
+    eng.linearize(0.05, a0, a1)
+    part = eng.system().clone()
+    eng.linearize(0.05, b0, b1)
+    part += eng.system()
+    eng.linearize(0.05, 0, -1)
+    full = eng.system().clone()
+    assert float((part - full).norm() / full.norm()) < 1e-10
+    H, v = full[:n * n].view(n, n), full[n * n:]
+    assert float((H - H.T).norm() / H.norm()) < 1e-6
+    blk = torch.arange(n, device=dev) // 6
+    outside = (blk[:, None] - blk[None, :]).abs() > gba.band
+    assert float(H[outside].abs().max()) == 0.0
+    idx = gba.band_index(dev)
+    assert idx is not None and idx.numel() < 0.05 * full.numel()
+    lm, ep = 1e-4, 0.1
+    eng.solve(lm, ep, gba.band)
+    assert int(eng.w.info().cpu()[1]) == 0
+    dx = eng.w.dx().double().reshape(-1)
+    Hd = H + torch.diag(ep + lm * torch.diagonal(H))
+    Hl = torch.tril(Hd) + torch.tril(Hd, -1).T                  # the solver reads the lower triangle
+    res = Hl @ dx - v
+    assert float(res.norm() / v.norm()) < 1e-5                   # dx is stored in float32
+    # one full iteration lowers the weighted reprojection cost
+    def cost():
+        c, valid = db.reproject(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"])
+        r = c[0].permute(0, 3, 1, 2) - t["targets"]
+        # points behind or too close to the target camera carry no weight in the BA either
+        return float((t["weights"] * valid[0].permute(0, 3, 1, 2) * (r * r).clamp(max=1e4)).sum())
+    c0 = cost()
+    eng.retract(0, -1)
+    assert cost() < c0
