@@ -436,3 +436,33 @@ def test_ba_host_matches_ba(dev, db, synth):
     with pytest.raises(RuntimeError, match="CPU tensor"):
         db.ba_host(t["poses"], h["disps"], h["intrinsics"], h["disps_sens"], h["targets"], h["weights"], h["eta"],
                    h["ii"], h["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, False)
+
+
+def test_lookup_at_integer_coordinates_returns_volume_entries_c2_full_size(dev, db, synth):
+    """Size-independent property at the full C2 size (48 edges, 64x64, 4 levels): where the level-l coordinates
+    are integers the bilinear weights are (1,0,0,0) and output (a, b) is exactly the volume entry at
+    (y0 - r + b, x0 - r + a), zero outside the image; the volume is the indexed tcgen05 build."""
+    w = synth.make_window("c2", seed=0)
+    f = torch.from_numpy(synth.make_features("c2", seed=0, n_frames=w["poses"].shape[0])).to(dev)
+    ii, jj = torch.from_numpy(w["ii"]).to(dev), torch.from_numpy(w["jj"]).to(dev)
+    pyr = db.corr_volume_pyramid_indexed(f, f, ii, jj, 4)
+    E, ht, wd = ii.numel(), w["ht"], w["wd"]
+    g = torch.Generator(device="cpu").manual_seed(3)
+    # multiples of 8 stay integer on every level; a margin lets windows hang over the border
+    cx = (torch.randint(-1, wd // 8 + 1, (E, ht, wd), generator=g) * 8).float()
+    cy = (torch.randint(-1, ht // 8 + 1, (E, ht, wd), generator=g) * 8).float()
+    coords = torch.stack([cx, cy], 1).to(dev).contiguous()
+    out = db.corr_lookup_pyramid(pyr, coords, 3).view(E, 4, 7, 7, ht, wd)
+    for l in range(4):
+        h2, w2 = ht >> l, wd >> l
+        x0 = (coords[:, 0] / 2 ** l).long()
+        y0 = (coords[:, 1] / 2 ** l).long()
+        vol = pyr[l]                                                     # [E, ht, wd, h2, w2]
+        for a in (0, 3, 6):
+            for b in (0, 2, 6):
+                x, y = x0 - 3 + a, y0 - 3 + b
+                inb = (x >= 0) & (x < w2) & (y >= 0) & (y < h2)
+                flat = (y.clamp(0, h2 - 1) * w2 + x.clamp(0, w2 - 1)).unsqueeze(-1)
+                want = torch.gather(vol.reshape(E, ht, wd, h2 * w2), 3, flat).squeeze(-1)
+                want = torch.where(inb, want, torch.zeros_like(want))
+                assert torch.equal(out[:, l, a, b].view(torch.int16), want.view(torch.int16)), (l, a, b)
