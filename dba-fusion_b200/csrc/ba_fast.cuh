@@ -140,55 +140,53 @@ __device__ __forceinline__ double rsqrt_nr(double d) {
 // row, so the forward substitution falls out of the factorisation) resident in shared memory.
 // P block steps with 3 barriers each instead of 6P column steps with 4.
 // Layout: L[(n+1)][ld], lower triangle used; dinv[n] = 1 / L[c][c].
+// One thread: factor the 6x6 diagonal block at (j0, j0) in place (right-looking, in registers) and publish
+// 1/diag.  Sets *fail when a pivot is not positive.
+__device__ __forceinline__ void factor_diag6(double* L, int ld, int j0, double* dinv, int* fail) {
+  double a[6][6];
+#pragma unroll
+  for (int r = 0; r < 6; ++r)
+#pragma unroll
+    for (int c = 0; c < 6; ++c)
+      if (c <= r) a[r][c] = L[(size_t)(j0 + r) * ld + j0 + c];
+  bool bad = false;
+#pragma unroll
+  for (int c = 0; c < 6; ++c) {
+    double d = a[c][c];
+    if (d <= 0.0) { bad = true; d = 1.0; }
+    const double inv = rsqrt_nr(d);
+    a[c][c] = d * inv;
+    dinv[j0 + c] = inv;
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+      if (r > c) a[r][c] *= inv;
+#pragma unroll
+    for (int r = 0; r < 6; ++r)
+#pragma unroll
+      for (int k = 0; k < 6; ++k)
+        if (r > c && k > c && k <= r) a[r][k] -= a[r][c] * a[k][c];
+  }
+  if (bad) *fail = 1;
+#pragma unroll
+  for (int r = 0; r < 6; ++r)
+#pragma unroll
+    for (int c = 0; c < 6; ++c)
+      if (c <= r) L[(size_t)(j0 + r) * ld + j0 + c] = a[r][c];
+}
+
 __device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* dinv, int* fail) {
   const int tid = threadIdx.x, nt = blockDim.x;
   const int n = 6 * P;
-  if (tid == 0) *fail = 0;
+  if (tid == 0) {
+    *fail = 0;
+    factor_diag6(L, ld, 0, dinv, fail);
+  }
   __syncthreads();
   for (int J = 0; J < P; ++J) {
     const int j0 = 6 * J;
-    // (1) factor the 6x6 diagonal block (one thread; 56 flops)
-    if (tid == 0) {
-      // whole lower triangle into registers first (21 independent loads), then a fully
-      // unrolled in-register factorisation: the only serial chain left is 6 x (rsqrt + a few FMAs)
-      double a[6][6];
-#pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int c = 0; c < 6; ++c)
-          if (c <= r) a[r][c] = L[(size_t)(j0 + r) * ld + j0 + c];
-      bool bad = false;
-#pragma unroll
-      for (int c = 0; c < 6; ++c) {
-        double d = a[c][c];
-#pragma unroll
-        for (int kk = 0; kk < 6; ++kk)
-          if (kk < c) d -= a[c][kk] * a[c][kk];
-        if (d <= 0.0) { bad = true; d = 1.0; }
-        const double inv = rsqrt_nr(d);
-        a[c][c] = d * inv;
-        dinv[j0 + c] = inv;
-#pragma unroll
-        for (int r = 0; r < 6; ++r) {
-          if (r > c) {
-            double s = a[r][c];
-#pragma unroll
-            for (int kk = 0; kk < 6; ++kk)
-              if (kk < c) s -= a[r][kk] * a[c][kk];
-            a[r][c] = s * inv;
-          }
-        }
-      }
-      if (bad) *fail = 1;
-#pragma unroll
-      for (int r = 0; r < 6; ++r)
-#pragma unroll
-        for (int c = 0; c < 6; ++c)
-          if (c <= r) L[(size_t)(j0 + r) * ld + j0 + c] = a[r][c];
-    }
-    __syncthreads();
+    // the diagonal block of this column was factorised during the previous step (look-ahead, see below)
     if (*fail) return false;
-    // (2) panel below the block (rows j0+6 .. n, row n = rhs): X L_JJ^T = A
+    // (1) panel below the block (rows j0+6 .. n, row n = rhs): X L_JJ^T = A
     for (int r = j0 + 6 + tid; r <= n; r += nt) {
       double row[6];
 #pragma unroll
@@ -203,25 +201,46 @@ __device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* din
       for (int c = 0; c < 6; ++c) L[(size_t)r * ld + j0 + c] = row[c];
     }
     __syncthreads();
-    // (3) trailing update A[r][c] -= sum_k L[r][j0+k] L[c][j0+k] for j0+6 <= c <= min(r, n-1), r <= n
+    // (2) trailing update A[r][c] -= sum_k L[r][j0+k] L[c][j0+k] for j0+6 <= c <= min(r, n-1), r <= n.
+    //     Look-ahead: the last warp first updates the next diagonal block (21 entries, one lane each) and
+    //     its lane 0 factorises it at once, so the serial pivot chain of column J+1 runs under the bulk of this
+    //     update instead of after it; the other warps skip that block.
     const int r0 = j0 + 6;
     const int mrows = n - r0 + 1;
+    const int nwork = nt - 32;
     if (mrows > 1) {
-      // 16x16 thread grid over the (rows x cols) triangle: no integer division, the row's six
-      // panel values are loaded once per row and reused along it
-      const int ty = tid >> 4, tx = tid & 15;
-      for (int ro = ty; ro < mrows; ro += (nt >> 4)) {
-        const double* lr = L + (size_t)(r0 + ro) * ld + j0;
-        double a[6];
+      if (tid >= nwork) {
+        const int ln = tid - nwork;
+        if (ln < 21) {
+          int r, c;
+          tri_unpack(ln, r, c);
+          const double* lr = L + (size_t)(r0 + r) * ld + j0;
+          const double* lc = L + (size_t)(r0 + c) * ld + j0;
+          double sum = 0.0;
 #pragma unroll
-        for (int kk = 0; kk < 6; ++kk) a[kk] = lr[kk];
-        const int cmax = min(ro, mrows - 2);
-        for (int co = tx; co <= cmax; co += 16) {
-          const double* lc = L + (size_t)(r0 + co) * ld + j0;
-          double s = 0.0;
+          for (int kk = 0; kk < 6; ++kk) sum += lr[kk] * lc[kk];
+          L[(size_t)(r0 + r) * ld + r0 + c] -= sum;
+        }
+        __syncwarp();
+        if (ln == 0) factor_diag6(L, ld, r0, dinv, fail);
+      } else {
+        // 15 x 16 thread grid over the (rows x cols) triangle: no integer division, the row's six panel
+        // values are loaded once per row and reused along it
+        const int ty = tid >> 4, tx = tid & 15;
+        for (int ro = ty; ro < mrows; ro += (nwork >> 4)) {
+          const double* lr = L + (size_t)(r0 + ro) * ld + j0;
+          double a[6];
 #pragma unroll
-          for (int kk = 0; kk < 6; ++kk) s += a[kk] * lc[kk];
-          L[(size_t)(r0 + ro) * ld + r0 + co] -= s;
+          for (int kk = 0; kk < 6; ++kk) a[kk] = lr[kk];
+          const int cmax = min(ro, mrows - 2);
+          for (int co = tx; co <= cmax; co += 16) {
+            if (ro < 6 && co < 6) continue;            // next diagonal block: look-ahead warp
+            const double* lc = L + (size_t)(r0 + co) * ld + j0;
+            double sum = 0.0;
+#pragma unroll
+            for (int kk = 0; kk < 6; ++kk) sum += a[kk] * lc[kk];
+            L[(size_t)(r0 + ro) * ld + r0 + co] -= sum;
+          }
         }
       }
     }
