@@ -17,7 +17,7 @@
 #pragma once
 
 constexpr int kBandRegMaxB = 20;     // (B + 2)^2 <= 512 threads
-constexpr int kPnS = 37;
+constexpr int kPnS = 38;             // block stride of the panel buffers: 16-byte aligned rows, conflict-free 128-bit reads
 
 __global__ void __launch_bounds__(kBandThreads)
 k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
@@ -28,9 +28,10 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   const int P = pt.Plog;
   const int n = 6 * Pphys;
   const int NB = B + 2;
-  // panel blocks are kPnS = 37 doubles apart: lanes that read different blocks then hit different banks
-  double* Pn = smr;                       // NB x 37: panel blocks L_{I,J} of the current column, by I mod NB
-  double* Praw = Pn + NB * kPnS;          // NB x 37: the same blocks before the triangular solve
+  // panel blocks are kPnS = 38 doubles apart: lanes that read different blocks hit different banks, and every
+  // block starts on a 16-byte boundary so that two doubles come with one load
+  double* Pn = smr;                       // NB x 38: panel blocks L_{I,J} of the current column, by I mod NB
+  double* Praw = Pn + NB * kPnS;          // NB x 38: the same blocks before the triangular solve
   double* yw = Praw + NB * kPnS;          // NB x 6: right-hand-side window
   double* Ljj = yw + NB * 6;              // 2 x 36
   double* dj = Ljj + 72;                  // 2 x 6
@@ -291,23 +292,29 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
     asm volatile("cp.async.commit_group;" ::: "memory");
     if (!diag) {
       if (ok >= 1 && oi <= nbelow) {
-        const double* Li = Pn + ri * kPnS + half * 18;
-        const double* Lk = Pn + rk * kPnS;
+        // C -= L_I L_K^T for this thread's three rows: 27 two-double loads feed 108 fused multiply-adds
+        const double2* Li = reinterpret_cast<const double2*>(Pn + ri * kPnS + half * 18);
+        const double2* Lk = reinterpret_cast<const double2*>(Pn + rk * kPnS);
         double li[18];
 #pragma unroll
-        for (int i = 0; i < 18; ++i) li[i] = Li[i];
+        for (int i = 0; i < 9; ++i) {
+          const double2 v = Li[i];
+          li[2 * i] = -v.x;
+          li[2 * i + 1] = -v.y;
+        }
 #pragma unroll
         for (int c = 0; c < 6; ++c) {
           double lk[6];
 #pragma unroll
-          for (int k = 0; k < 6; ++k) lk[k] = Lk[c * 6 + k];
-#pragma unroll
-          for (int r = 0; r < 3; ++r) {
-            double sum = 0.0;
-#pragma unroll
-            for (int k = 0; k < 6; ++k) sum += li[r * 6 + k] * lk[k];
-            C[r * 6 + c] -= sum;
+          for (int k = 0; k < 3; ++k) {
+            const double2 v = Lk[c * 3 + k];
+            lk[2 * k] = v.x;
+            lk[2 * k + 1] = v.y;
           }
+#pragma unroll
+          for (int r = 0; r < 3; ++r)
+#pragma unroll
+            for (int k = 0; k < 6; ++k) C[r * 6 + c] = fma(li[r * 6 + k], lk[k], C[r * 6 + c]);
         }
       }
     } else if (oa >= 1 && oa <= nbelow) {
