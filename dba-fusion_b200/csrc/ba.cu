@@ -843,7 +843,12 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       }
       k_band_sep<<<1, kThreads, ssm, st>>>(P, B, lm, ep, plan, ws);
       DBAF_LAUNCH_CHECK("k_band_sep");
-      k_band_back<<<2, 32, band_back_smem_doubles(B) * sizeof(double), st>>>(P, B, plan, ws);
+      static bool back_attr[64] = {};
+      if (!back_attr[dev_id & 63]) {
+        DBAF_CUDA(cudaFuncSetAttribute(k_band_back, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        back_attr[dev_id & 63] = true;
+      }
+      k_band_back<<<2, 64, band_back_smem_doubles(B) * sizeof(double), st>>>(P, B, plan, ws);
       DBAF_LAUNCH_CHECK("k_band_back");
     }
     if (rezero) DBAF_CUDA(cudaMemsetAsync(ws.H, 0, ((size_t)n * n + n) * 8, st));

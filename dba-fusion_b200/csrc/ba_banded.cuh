@@ -47,23 +47,24 @@ __device__ __forceinline__ double warp_sum_d(double v) {
   return v;
 }
 
-// Back-substitution L^T x = y of one part, bottom up, right-looking, on ONE warp: once x_J is known every
+// Back-substitution L^T x = y of one part, bottom up, right-looking, on TWO warps: once x_J is known every
 // pending right-hand side above it is updated, y_I -= L_{J,I}^T x_J (I = J-B .. J-1).  A step is a short serial
-// 6x6 solve on lane 0 plus 6B dot products of length 6 spread over the lanes, so a second warp would only add
-// barriers.  Everything a step reads (the B blocks of block row J of L, L_JJ, 1/diag, the y row entering the
-// window) is brought into a kBackDepth-deep shared-memory ring with 16-byte asynchronous copies issued
-// kBackDepth-1 steps ahead: the L2 latency of the band store never shows.  Rows J >= n_elim are not solved:
-// their x comes from `xsep` (the separator solution, physical order, separator-local) and only the update
-// is applied.
-constexpr int kBackDepth = 4;
+// 6x6 solve on lane 0 of the consumer warp plus 6B dot products of length 6 spread over its lanes.  Everything
+// a step reads (block row J of L, 1/diag, the y row entering the window) is brought into a kBackDepth-deep
+// shared-memory ring by the producer warp with 16-byte asynchronous copies that signal a per-slot mbarrier when
+// they land; the consumer frees a slot with a second mbarrier.  The copies (~750 cycles of issue per block row)
+// and the latency of the band store are thus off the serial chain.  Rows J >= n_elim are not solved: their x
+// comes from `xsep` (the separator solution, physical order, separator-local) and only the update is applied.
+// Call with the first 64 threads of the CTA; `sm` needs band_back_smem_doubles(B) doubles.
+constexpr int kBackDepth = 8;
 __host__ __device__ inline int band_back_stage_doubles(int B) { return (B + 1) * 36 + 12; }   // L row (d = 0..B) | dinv | y_in
 __host__ __device__ inline int band_back_smem_doubles(int B) {
-  return kBackDepth * band_back_stage_doubles(B) + (B + 2) * 6 + 6 * B + 8;            // ring | yw | xsep | xs
+  return kBackDepth * band_back_stage_doubles(B) + (B + 2) * 6 + 6 * B + 8 + 2 * kBackDepth;   // ring | yw | xsep | xs | barriers
 }
 
-__device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, const double* __restrict__ xsep_g,
-                                  double* sm, Ws ws) {
-  const int lane = threadIdx.x & 31;
+__device__ void band_backsub(int Pphys, int B, const BandPart& pt, int m, const double* __restrict__ xsep_g,
+                             double* sm, Ws ws) {
+  const int lane = threadIdx.x & 31, role = (threadIdx.x >> 5) & 1;      // role 0: consumer, 1: producer
   const int P = pt.Plog, NB = B + 2, SD = band_back_stage_doubles(B), RD = (B + 1) * 36;
   const double* Lband = ws.Lfac + pt.store;
   const double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
@@ -72,42 +73,58 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
   double* yw = ring + kBackDepth * SD;
   double* xsep = yw + NB * 6;
   double* xs = xsep + 6 * B;
+  uint64_t* full = reinterpret_cast<uint64_t*>(xs + 8);
+  uint64_t* empty = full + kBackDepth;
   auto phys = [&](int I) { return pt.rev ? Pphys - 1 - I : I; };
-  auto cp16 = [&](double* dst, const double* src, int bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"((unsigned)__cvta_generic_to_shared(dst)), "l"(src),
-                 "r"(bytes)
-                 : "memory");
-  };
-  // stage for step J: block row J of the band store (L_JJ, L_{J,J-1}, .. L_{J,J-B}; entries whose column was
-  // never eliminated hold garbage and are skipped below), then 1/diag(J) and y of row J-B
-  const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring) + lane * 16;
-  const int npiece = RD / 2;                         // 16-byte pieces of a block row of L
-  auto issue = [&](int J) {
-    if (J >= 0) {
-      const unsigned dst = ring_s + (unsigned)((J % kBackDepth) * SD * 8);
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kBackDepth; ++i) {
+      mbar_init(smem_u32(&full[i]), 32);             // every producer lane arrives when its copies have landed
+      mbar_init(smem_u32(&empty[i]), 1);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  // consumer set-up: window rows P-1 .. P-B (row P-1-B arrives with the first stage), separator solution
+  if (role == 0) {
+    for (int e = lane; e < B * 6; e += 32) {
+      const int I = P - 1 - e / 6;
+      if (I >= 0) yw[(I % NB) * 6 + e % 6] = I < pt.n_elim ? y_g[6 * I + e % 6] : 0.0;
+    }
+    if (xsep_g != nullptr)
+      for (int e = lane; e < 6 * B; e += 32) xsep[e] = xsep_g[e];
+  }
+  asm volatile("bar.sync 1, 64;" ::: "memory");      // the two warps only (the rest of the CTA may be gone)
+
+  if (role == 1) {
+    // ---------------------------------------------------------------- producer
+    // stage for step J: block row J of the band store (L_JJ, L_{J,J-1}, .. L_{J,J-B}; entries whose column was
+    // never eliminated hold garbage and are skipped by the consumer), then 1/diag(J) and y of row J-B
+    const unsigned ring_s = (unsigned)__cvta_generic_to_shared(ring) + lane * 16;
+    const int npiece = RD / 2;                       // 16-byte pieces of a block row of L
+    int slot = 0, use = 0;
+    for (int J = P - 1; J >= 0; --J) {
+      mbar_wait(smem_u32(&empty[slot]), (use + 1) & 1);
+      const unsigned dst = ring_s + (unsigned)(slot * SD * 8);
       const double* src = Lband + (size_t)J * RD + 2 * lane;
       for (int q = 0; q * 32 + lane < npiece; ++q)
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + q * 512), "l"(src + q * 64) : "memory");
-      double* dtail = ring + (J % kBackDepth) * SD + RD;
-      if (lane < 3) cp16(dtail + 2 * lane, dinv_g + 6 * (J < pt.n_elim ? J : 0) + 2 * lane, 16);
+      const unsigned dtail = (unsigned)__cvta_generic_to_shared(ring + slot * SD + RD);
+      if (lane < 3)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dtail + 16 * lane),
+                     "l"(dinv_g + 6 * (J < pt.n_elim ? J : 0) + 2 * lane) : "memory");
       if (lane >= 3 && lane < 6) {
         const int I = J - B, ok = I >= 0 && I < pt.n_elim;
-        cp16(dtail + 2 * lane, y_g + 6 * (ok ? I : 0) + 2 * (lane - 3), ok ? 16 : 0);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dtail + 16 * lane),
+                     "l"(y_g + 6 * (ok ? I : 0) + 2 * (lane - 3)), "r"(ok ? 16 : 0) : "memory");
       }
+      asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" ::"r"(smem_u32(&full[slot])) : "memory");
+      if (++slot == kBackDepth) { slot = 0; ++use; }
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
-  };
-
-  for (int J = P - 1; J > P - kBackDepth; --J) issue(J);
-  // window rows P-1 .. P-B (row P-1-B arrives with the first stage)
-  for (int e = lane; e < B * 6; e += 32) {
-    const int I = P - 1 - e / 6;
-    if (I >= 0) yw[(I % NB) * 6 + e % 6] = I < pt.n_elim ? y_g[6 * I + e % 6] : 0.0;
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    return;
   }
-  if (xsep_g != nullptr)
-    for (int e = lane; e < 6 * B; e += 32) xsep[e] = xsep_g[e];
-  __syncwarp();
 
+  // ------------------------------------------------------------------ consumer
   // per-lane constants of the update: item u is (block offset o, component c) = divmod(lane + 32 u, 6)
   int it_o[5], it_c[5];
 #pragma unroll
@@ -117,7 +134,7 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
   }
   int jr = (P - 1) % NB;                             // J mod NB, kept incrementally
   int jb = ((P - 1 - B) % NB + NB) % NB;             // (J - B) mod NB
-  int slot = (P - 1) % kBackDepth;                   // J mod kBackDepth
+  int slot = 0, use = 0;
 #ifdef DBAF_BAND_PROFILE
   long long bt[4] = {0, 0, 0, 0}, b0, b1;
 #define BK_TICK(i) do { b1 = clock64(); bt[i] += b1 - b0; b0 = b1; } while (0)
@@ -128,10 +145,8 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
 #ifdef DBAF_BAND_PROFILE
     b0 = clock64();
 #endif
-    issue(J - (kBackDepth - 1));
-    BK_TICK(0);
-    asm volatile("cp.async.wait_group %0;" ::"n"(kBackDepth - 1) : "memory");
-    __syncwarp();
+    mbar_wait(smem_u32(&full[slot]), use & 1);
+    __syncwarp();                                    // also orders the previous step's yw updates before lane 0 reads
     BK_TICK(1);
     const double* st = ring + slot * SD;
     if (lane < 6 && J - B >= 0) yw[jb * 6 + lane] = st[RD + 6 + lane];
@@ -168,34 +183,40 @@ __device__ void band_backsub_warp(int Pphys, int B, const BandPart& pt, int m, c
     for (int r = 0; r < 6; ++r) xv[r] = xs[r];
     const int nab = min(B, J);                       // rows above J inside the band
     const int first_elim = J - pt.n_elim;            // items with o < first_elim belong to separator x separator blocks
-    // fixed trip count (6B <= 150 items over 32 lanes) so that the five dot products overlap
+    // fixed trip count (6B <= 150 items over 32 lanes) so that the five dot products overlap; the panel blocks are
+    // stored transposed (see the sweeps), so a dot product reads six contiguous doubles
 #pragma unroll
     for (int u = 0; u < 5; ++u) {
       const int o = it_o[u], c = it_c[u];
       if (o < nab && o >= first_elim) {
-        const double* q = st + (o + 1) * 36 + c;
-        double sum = 0.0;
-#pragma unroll
-        for (int r = 0; r < 6; ++r) sum += q[r * 6] * xv[r];
+        const double2* q = reinterpret_cast<const double2*>(st + (o + 1) * 36 + c * 6);
+        const double2 q0 = q[0], q1 = q[1], q2 = q[2];
+        double sum = q0.x * xv[0];
+        sum = fma(q0.y, xv[1], sum);
+        sum = fma(q1.x, xv[2], sum);
+        sum = fma(q1.y, xv[3], sum);
+        sum = fma(q2.x, xv[4], sum);
+        sum = fma(q2.y, xv[5], sum);
         int row = jr - 1 - o;
         if (row < 0) row += NB;
         yw[row * 6 + c] -= sum;
       }
     }
-    // no barrier here: the one after the next wait_group orders these updates before lane 0 reads them
+    __syncwarp();
+    if (lane == 0) mbar_arrive(smem_u32(&empty[slot]));      // the producer may refill this slot
     jr = jr == 0 ? NB - 1 : jr - 1;
     jb = jb == 0 ? NB - 1 : jb - 1;
-    slot = slot == 0 ? kBackDepth - 1 : slot - 1;
+    if (++slot == kBackDepth) { slot = 0; ++use; }
     BK_TICK(3);
   }
 #ifdef DBAF_BAND_PROFILE
   if (lane == 0 && pt.rev == 0) for (int i = 0; i < 4; ++i) ws.info[6 + i] = (int)(bt[i] >> 10);
 #endif
-  asm volatile("cp.async.wait_group 0;" ::: "memory");
 }
 
 // Band store of a part: [Plog][B+1][36] (entry (I, d) = L_{I, I-d}, row-major 6x6: a block row of L is one
-// contiguous run, which is what the back-substitution streams), then dinv [6 Plog],
+// contiguous run, which is what the back-substitution streams; off-diagonal blocks are stored TRANSPOSED so that
+// its dot products read contiguous doubles), then dinv [6 Plog],
 // then y [6 Plog].
 __global__ void __launch_bounds__(kBandThreads)
 k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, Ws ws) {
@@ -405,7 +426,7 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
         A[c] = x[c];
-        Lband[((size_t)I * (B + 1) + (I - J)) * 36 + r * 6 + c] = x[c];
+        Lband[((size_t)I * (B + 1) + (I - J)) * 36 + c * 6 + r] = x[c];     // transposed: see band_backsub
         yy -= x[c] * yw[(J % NB) * 6 + c];
       }
       yw[(I % NB) * 6 + r] = yy;
@@ -501,7 +522,7 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
   }
   if (ok) {
     // the window is no longer needed: its shared memory becomes the back-substitution's staging ring
-    if (tid < 32) band_backsub_warp(Pphys, B, pt, 0, nullptr, smb, ws);
+    if (tid < 64) band_backsub(Pphys, B, pt, 0, nullptr, smb, ws);
   } else {
     for (int i = tid; i < n; i += nt) ws.dx[i] = 0.0f;
     if (tid == 0) atomicAdd(&ws.info[1], 1);
@@ -557,7 +578,7 @@ k_band_sep(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   }
 }
 
-__global__ void __launch_bounds__(32)
+__global__ void __launch_bounds__(64)
 k_band_back(int Pphys, int B, BandPlan plan, Ws ws) {
   extern __shared__ double smk[];
   const BandPart pt = plan.part[blockIdx.x];
@@ -571,5 +592,5 @@ k_band_back(int Pphys, int B, BandPlan plan, Ws ws) {
     }
     return;
   }
-  band_backsub_warp(Pphys, B, pt, plan.m, xsep, smk, ws);
+  band_backsub(Pphys, B, pt, plan.m, xsep, smk, ws);
 }

@@ -259,7 +259,7 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
         Pn[rs * kPnS + r * 6 + c] = x[c];
-        Lband[((size_t)I * (B + 1) + (I - J)) * 36 + r * 6 + c] = x[c];
+        Lband[((size_t)I * (B + 1) + (I - J)) * 36 + c * 6 + r] = x[c];     // transposed: see band_backsub
         yy += x[c] * yw[jm * 6 + c];
       }
       yw[rs * 6 + r] -= yy;
@@ -368,7 +368,7 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
     return;
   }
   if (ok_all) {
-    if (tid < 32) band_backsub_warp(Pphys, B, pt, 0, nullptr, smr, ws);
+    if (tid < 64) band_backsub(Pphys, B, pt, 0, nullptr, smr, ws);
   } else {
     for (int i = tid; i < n; i += nt) ws.dx[i] = 0.0f;
     if (tid == 0) atomicAdd(&ws.info[1], 1);
