@@ -160,10 +160,12 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
   if (levels > 1) {
     const size_t smem = ((size_t)((HW + 15) & ~7) + (size_t)(ht / 2) * (wd / 2) + (size_t)(ht / 4) * (wd / 4)) * 2 + 16;
     DBAF_REQUIRE(smem <= 200 * 1024, "feature map too large for the pyramid kernel");
-    static bool attr = false;
-    if (!attr) {
+    static bool attr[64] = {};                        // per device
+    int dev_id = 0;
+    DBAF_CUDA(cudaGetDevice(&dev_id));
+    if (!attr[dev_id & 63]) {
       DBAF_CUDA(cudaFuncSetAttribute(k_pyramid, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-      attr = true;
+      attr[dev_id & 63] = true;
     }
     const long long slabs = (long long)n * HW;
     const int blocks = (int)std::min<long long>(slabs, 148LL * 16);

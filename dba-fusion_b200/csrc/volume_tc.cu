@@ -411,11 +411,13 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
   Pyr pyr;
   for (int l = 0; l < 4; ++l) pyr.l[l] = (fuse && l < levels) ? out[l] : nullptr;
   pyr.l[0] = out[0];
-  static bool attr[2] = {false, false};
-  if (!attr[fuse]) {
+  static bool attr[64][2] = {};                       // per device: the attribute belongs to the device's copy of the kernel
+  int dev_id = 0;
+  DBAF_CUDA(cudaGetDevice(&dev_id));
+  if (!attr[dev_id & 63][fuse]) {
     if (fuse) DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
-    attr[fuse] = true;
+    attr[dev_id & 63][fuse] = true;
   }
   if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2);
   else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2);
