@@ -73,20 +73,29 @@ __device__ __forceinline__ __half pool4(const __half* s, int w, int y, int x) {
   return __float2half_rn((((a + b) + c) + d) * 0.25f);
 }
 
-// One CTA walks slabs (source pixels); the slab and every pooled level live in shared memory.
+// Slabs (source pixels) are pooled by groups of `gthreads` threads that never meet the rest of the CTA: a whole
+// 128-thread CTA per slab when the slab is a level-0 map (thousands of values), one warp per slab when it is a
+// level-1 map of a few hundred values (then four slabs are in flight per CTA and the barriers are warp barriers).
+// The slab and every pooled level live in the group's part of shared memory.
+__device__ __forceinline__ void group_sync(int gthreads) {
+  if (gthreads == 32) __syncwarp();
+  else __syncthreads();
+}
+
 __global__ void __launch_bounds__(128)
 k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int levels,
-          __half* __restrict__ L1, __half* __restrict__ L2, __half* __restrict__ L3) {
+          __half* __restrict__ L1, __half* __restrict__ L2, __half* __restrict__ L3, int gthreads, int group_halves) {
   extern __shared__ __half sm[];
   const int s0 = h2 * w2;
   const int h1 = h2 >> 1, w1 = w2 >> 1, hq = h2 >> 2, wq = w2 >> 2, he = h2 >> 3, we = w2 >> 3;
+  const int groups = 128 / gthreads, grp = threadIdx.x / gthreads, gt = threadIdx.x - grp * gthreads;
   // the slab is fetched with aligned 16-byte loads whatever its own alignment (h2*w2 is odd for 55 x 55): the
   // raw copy starts up to 7 halves before the slab, `a0` points at the slab inside it
-  __half* raw = sm;
+  __half* raw = sm + (size_t)grp * group_halves;
   __half* a1 = raw + ((s0 + 15) & ~7);
   __half* a2 = a1 + h1 * w1;
   const bool vec = (reinterpret_cast<size_t>(L0) & 15) == 0;
-  for (long long s = blockIdx.x; s < slabs; s += gridDim.x) {
+  for (long long s = (long long)blockIdx.x * groups + grp; s < slabs; s += (long long)gridDim.x * groups) {
     const long long first = s * s0;
     const int off = vec ? (int)(first & 7) : 0;
     const __half* a0 = raw + off;
@@ -95,30 +104,30 @@ k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int le
       const int nvec = (off + s0 + 7) >> 3;
       // the last vector may reach past the end of the whole volume: it is then read element-wise
       const bool tail_ok = first - off + (long long)nvec * 8 <= slabs * (long long)s0;
-      for (int t = threadIdx.x; t < nvec - (tail_ok ? 0 : 1); t += 128) reinterpret_cast<uint4*>(raw)[t] = __ldg(src + t);
+      for (int t = gt; t < nvec - (tail_ok ? 0 : 1); t += gthreads) reinterpret_cast<uint4*>(raw)[t] = __ldg(src + t);
       if (!tail_ok)
-        for (int t = (nvec - 1) * 8 + threadIdx.x; t < off + s0; t += 128) raw[t] = L0[first - off + t];
+        for (int t = (nvec - 1) * 8 + gt; t < off + s0; t += gthreads) raw[t] = L0[first - off + t];
     } else {
-      for (int t = threadIdx.x; t < s0; t += 128) raw[t] = L0[first + t];
+      for (int t = gt; t < s0; t += gthreads) raw[t] = L0[first + t];
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < h1 * w1; t += 128) {
+    group_sync(gthreads);
+    for (int t = gt; t < h1 * w1; t += gthreads) {
       const __half v = pool4(a0, w2, t / w1, t % w1);
       a1[t] = v;
       L1[s * (h1 * w1) + t] = v;
     }
-    __syncthreads();
+    group_sync(gthreads);
     if (levels > 2) {
-      for (int t = threadIdx.x; t < hq * wq; t += 128) {
+      for (int t = gt; t < hq * wq; t += gthreads) {
         const __half v = pool4(a1, w1, t / wq, t % wq);
         a2[t] = v;
         L2[s * (hq * wq) + t] = v;
       }
-      __syncthreads();
+      group_sync(gthreads);
       if (levels > 3)
-        for (int t = threadIdx.x; t < he * we; t += 128) L3[s * (he * we) + t] = pool4(a2, wq, t / we, t % we);
+        for (int t = gt; t < he * we; t += gthreads) L3[s * (he * we) + t] = pool4(a2, wq, t / we, t % we);
     }
-    __syncthreads();
+    group_sync(gthreads);
   }
 }
 
@@ -157,8 +166,13 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
     k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, idx1, idx2, C, HW, outs[0]);
     DBAF_LAUNCH_CHECK("k_volume_simt");
   }
-  if (levels > 1) {
-    const size_t smem = ((size_t)((HW + 15) & ~7) + (size_t)(ht / 2) * (wd / 2) + (size_t)(ht / 4) * (wd / 4)) * 2 + 16;
+  if (levels > std::max(done, 1)) {
+    // remaining levels from the deepest one already written: level 0 (SIMT / 256-pixel chunks) or level 1
+    const int src = std::max(done, 1) - 1;
+    const int hs = ht >> src, wsz = wd >> src, HWs = hs * wsz;
+    const int gthreads = HWs <= 1024 ? 32 : 128;      // small (level-1) slabs: one warp each
+    const int group_halves = ((((HWs + 15) & ~7) + (hs / 2) * (wsz / 2) + (hs / 4) * (wsz / 4)) + 7) & ~7;   // 16-byte multiple
+    const size_t smem = (size_t)group_halves * (128 / gthreads) * 2 + 16;
     DBAF_REQUIRE(smem <= 200 * 1024, "feature map too large for the pyramid kernel");
     static bool attr[64] = {};                        // per device
     int dev_id = 0;
@@ -168,8 +182,9 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
       attr[dev_id & 63] = true;
     }
     const long long slabs = (long long)n * HW;
-    const int blocks = (int)std::min<long long>(slabs, 148LL * 16);
-    k_pyramid<<<blocks, 128, smem, st>>>(outs[0], slabs, ht, wd, levels, outs[1], outs[2], outs[3]);
+    const int blocks = (int)std::min<long long>((slabs + 128 / gthreads - 1) / (128 / gthreads), 148LL * 16);
+    k_pyramid<<<blocks, 128, smem, st>>>(outs[src], slabs, hs, wsz, levels - src, outs[src + 1], src + 2 < 4 ? outs[src + 2] : nullptr,
+                                         src + 3 < 4 ? outs[src + 3] : nullptr, gthreads, group_halves);
     DBAF_LAUNCH_CHECK("k_pyramid");
   }
   return DBAF_OK;

@@ -40,8 +40,7 @@ constexpr int kSmemStage = 4 * kStageWarp;           // 80 KB
 constexpr int kSmemBytes = kSmemA + kSmemB + kSmemStage + 1024 /*alignment slack*/ + 256 /*barriers*/;
 constexpr int kThreadsTc = 256;   // warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7: epilogue
 
-// kind::f16: D = F32, A = B = F16, both K-major, N = 256, M = 128
-constexpr uint32_t kInstrDesc = (1u << 4) | ((uint32_t)(kBN >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+// instruction descriptor, kind::f16: D = F32 (bit 4), A = B = F16, both K-major, N >> 3 at bit 17, M >> 4 at bit 24
 
 __device__ __forceinline__ uint32_t pack_h2(__half a, __half b) {
   return (uint32_t)__half_as_ushort(a) | ((uint32_t)__half_as_ushort(b) << 16);
@@ -83,9 +82,14 @@ template <bool FUSE>
 __global__ void __launch_bounds__(kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
-            int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2) {
+            int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2,
+            int chunk_px, int n_mma, int kr, int wd) {
+  // chunk_px: target pixels a chunk advances by; n_mma: UMMA N (chunk_px rounded up to 16, <= 256);
+  // kr > 0 (generic shapes only): a chunk is 2*kr whole image rows of width wd, and level 1 is pooled from it here
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  // 1 KB alignment as an offset into the array (not through an integer cast), so that the compiler keeps
+  // treating everything below as shared memory and emits LDS/STS rather than generic accesses
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   uint8_t* sA = smem;
   uint8_t* sB = smem + kSmemA;
   uint8_t* sStage = smem + kSmemA + kSmemB;
@@ -97,7 +101,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int e = blockIdx.x / m_tiles;
   const int m0 = (blockIdx.x - e * m_tiles) * kBM;
-  const int n_chunks = (HW + kBN - 1) / kBN;
+  const int n_chunks = (HW + chunk_px - 1) / chunk_px;
   // operand rows: the edge's own maps, or frames picked by index (video.fmaps[ii] / [jj], covisible_graph.py:129-130)
   const int ea = idx1 ? idx1[e] : e, eb = idx2 ? idx2[e] : e;
 
@@ -132,9 +136,9 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     tma_load_2d(smem_u32(sA) + kBM * 128, &mapA, barA, kKBlock, ea * HW + m0);
     for (int c = 0; c < n_chunks; ++c) {
       mbar_wait(barFree, (c + 1) & 1);
-      mbar_expect_tx(barB, kSmemB);
-      tma_load_2d(smem_u32(sB), &mapB, barB, 0, eb * HW + c * kBN);
-      tma_load_2d(smem_u32(sB) + kBN * 128, &mapB, barB, kKBlock, eb * HW + c * kBN);
+      mbar_expect_tx(barB, (uint32_t)n_mma * 256u);
+      tma_load_2d(smem_u32(sB), &mapB, barB, 0, eb * HW + c * chunk_px);
+      tma_load_2d(smem_u32(sB) + n_mma * 128, &mapB, barB, kKBlock, eb * HW + c * chunk_px);
     }
     }
     __syncwarp();
@@ -143,6 +147,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     // ---------------------------------------------------------------- MMA issuer
     const uint32_t barA = smem_u32(&bars[0]), barB = smem_u32(&bars[1]), barFree = smem_u32(&bars[2]);
     mbar_wait(barA, 0);
+    const uint32_t idesc = (1u << 4) | ((uint32_t)(n_mma >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
     for (int c = 0; c < n_chunks; ++c) {
       const int s = c & 1, u = c >> 1;
       mbar_wait(smem_u32(&bars[5 + s]), (u + 1) & 1);      // epilogue has drained this accumulator stage
@@ -154,8 +159,8 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
           const uint64_t ad = umma_desc_k128(smem_u32(sA) + kb * (kBM * 128) + k4 * 32);
-          const uint64_t bd = umma_desc_k128(smem_u32(sB) + kb * (kBN * 128) + k4 * 32);
-          tc_mma_f16(d_tmem, ad, bd, kInstrDesc, (kb | k4) ? 1u : 0u);
+          const uint64_t bd = umma_desc_k128(smem_u32(sB) + kb * (n_mma * 128) + k4 * 32);
+          tc_mma_f16(d_tmem, ad, bd, idesc, (kb | k4) ? 1u : 0u);
         }
       }
       tc_commit(barFree);                 // B buffer may be overwritten once these MMAs are done
@@ -275,12 +280,13 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
               make_uint4(l3[0], l3[1], l3[2], l3[3]);
         }
       } else {
-        // generic shapes: level 0 only, 256 consecutive target pixels per chunk.  A row of the volume is
+        // generic shapes: a chunk is 2*kr whole target-image rows (or 256 consecutive pixels when a row pair does
+        // not fit); level 0 is written here, level 1 is pooled from the staged tile.  A row of the volume is
         // HW halves, in general neither 16- nor 4-byte aligned (55 x 55, 28 x 107), so the lane-per-row
         // accumulator layout is turned around through shared memory: the warp's 32 x 256 tile is staged with a
         // 129-word row pitch (conflict-free both ways) and written out row by row, every store instruction
         // covering 64 contiguous bytes of one row.
-        const int n0 = c * kBN;
+        const int n0 = c * chunk_px;
         uint32_t* tile = reinterpret_cast<uint32_t*>(sStage + q * kStageWarp);      // [32][129] words
         __syncwarp();                                    // the previous chunk's rows have been read out
 #pragma unroll 1
@@ -295,22 +301,53 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(smem_u32(&bars[5 + s]));
-        const int ncol = min(kBN, HW - n0);
+        const int ncol = min(chunk_px, HW - n0);
         const int mrow0 = m0 + q * 32;
-        // (explicit shared-space loads, all eight issued before the first store: as generic loads with a store
-        //  behind each one this loop cost 20 k cycles per chunk)
-        const uint32_t tbase = smem_u32(tile) + (uint32_t)lane * 2u;
+        // (all eight loads issued before the first store, and plain shared-memory loads: as generic loads with a
+        //  store behind each one this loop cost 20 k cycles per chunk)
         const int nrow = min(32, HW - mrow0);
 #pragma unroll 2
         for (int r = 0; r < nrow; ++r) {
           unsigned short* dst = reinterpret_cast<unsigned short*>(out.l[0]) + ((size_t)e * HW + mrow0 + r) * (size_t)HW + n0 + lane;
           unsigned short v[kBN / 32];
+          const unsigned short* src = reinterpret_cast<const unsigned short*>(tile) + r * 258 + lane;
 #pragma unroll
-          for (int k = 0; k < kBN / 32; ++k)
-            asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v[k]) : "r"(tbase + (uint32_t)(r * 516 + k * 64)));
+          for (int k = 0; k < kBN / 32; ++k) v[k] = src[k * 32];
 #pragma unroll
           for (int k = 0; k < kBN / 32; ++k)
             if (k * 32 + lane < ncol) dst[k * 32] = v[k];
+        }
+        if (kr > 0 && out.l[1] != nullptr) {
+          // level 1 (dbaf/modules/corr.py:35-38: avg_pool2d 2x2, floor sizes) from the fp16 tile: the chunk holds
+          // ncol / wd whole image rows starting at an even row, so every 2x2 window it touches is complete.
+          // ((a+b)+c)+d, *0.25, one rounding, like the pooling kernel and the fused 64-wide path.
+          // A chunk yields at most kr * (wd/2) <= 64 outputs per source pixel: two per lane, decoded once.
+          const int w1 = wd >> 1, hw1 = ((HW / wd) >> 1) * w1;
+          const int nout = ((ncol / wd) >> 1) * w1;
+          int colA[2], offA[2];
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            const int j = lane + 32 * t;
+            const int y1 = j / w1, x1 = j - y1 * w1;
+            colA[t] = j < nout ? 2 * y1 * wd + 2 * x1 : 0;      // even: the upper pair is one aligned word
+            offA[t] = j < nout ? j : -1;
+          }
+          const unsigned short* t16 = reinterpret_cast<const unsigned short*>(tile);
+          unsigned short* l1base = reinterpret_cast<unsigned short*>(out.l[1]) + ((size_t)e * HW + mrow0) * (size_t)hw1 +
+                                   (size_t)c * kr * w1;
+#pragma unroll 4
+          for (int r = 0; r < nrow; ++r) {
+            const unsigned short* row16 = t16 + r * 258;
+            const uint32_t* row32 = tile + r * 129;
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+              const uint32_t ab = row32[colA[t] >> 1];
+              const unsigned short cc = row16[colA[t] + wd], dd = row16[colA[t] + wd + 1];
+              const __half pooled = pool_h(__ushort_as_half((unsigned short)(ab & 0xffffu)), __ushort_as_half((unsigned short)(ab >> 16)),
+                                           __ushort_as_half(cc), __ushort_as_half(dd));
+              if (offA[t] >= 0) l1base[(size_t)r * hw1 + offA[t]] = __half_as_ushort(pooled);
+            }
+          }
         }
       }
     }
@@ -398,8 +435,16 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
   DBAF_LAUNCH_CHECK("k_to_pixel_major");
   CUtensorMap mapA, mapB;
   if (int rc = make_map(&mapA, a_t, (size_t)n1 * HW, kBM)) return rc;
-  if (int rc = make_map(&mapB, b_t, (size_t)n2 * HW, kBN)) return rc;
   const bool fuse = wd == 64 && ht % 8 == 0;
+  // generic shapes: a chunk of 2*kr whole image rows (so that level 1 can be pooled from it) when a row pair fits
+  // into one UMMA (N <= 256), else 256 consecutive pixels and level 0 only
+  int kr = 0, chunk_px = kBN, n_mma = kBN;
+  if (!fuse && 2 * wd <= kBN && levels > 1) {
+    kr = kBN / (2 * wd);
+    chunk_px = 2 * wd * kr;
+    n_mma = (chunk_px + 15) & ~15;
+  }
+  if (int rc = make_map(&mapB, b_t, (size_t)n2 * HW, n_mma)) return rc;
   const int m_tiles = (HW + kBM - 1) / kBM;
   CUtensorMap mapO0 = mapA, mapO1 = mapA;     // only the fused kernel stores through tensor maps
   if (fuse) {
@@ -411,6 +456,7 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
   Pyr pyr;
   for (int l = 0; l < 4; ++l) pyr.l[l] = (fuse && l < levels) ? out[l] : nullptr;
   pyr.l[0] = out[0];
+  if (kr > 0) pyr.l[1] = out[1];
   static bool attr[64][2] = {};                       // per device: the attribute belongs to the device's copy of the kernel
   int dev_id = 0;
   DBAF_CUDA(cudaGetDevice(&dev_id));
@@ -419,11 +465,12 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[dev_id & 63][fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2);
-  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2);
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd);
   DBAF_LAUNCH_CHECK("k_volume_tc");
-  // fused: all requested levels are written; otherwise only level 0 and the caller pools
-  *levels_done = fuse ? levels : 1;
+  // fused: all requested levels are written; generic with row-pair chunks: levels 0 and 1; otherwise level 0 only.
+  // The caller pools the rest.
+  *levels_done = fuse ? levels : (kr > 0 ? 2 : 1);
   return DBAF_OK;
 }
 
