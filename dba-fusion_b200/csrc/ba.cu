@@ -281,194 +281,7 @@ __device__ __forceinline__ void tri_unpack(int l, int& n, int& m) {
   m = l - n * (n + 1) / 2;
 }
 
-// One CTA = one depth frame k x one pixel tile.  It walks the frame's out-edges, so the
-// source disparity is read once, C/w/Ei accumulate in registers across edges (the reference
-// writes per-edge Cii/bz/Eii and re-reads them in accum_cuda), and each edge's 90 pose
-// terms are reduced with a transposed warp shuffle + one shared-memory stage.
-template <int PXT, bool MOTION_ONLY>
-__global__ void __launch_bounds__(kThreads)
-k_linearize(const float* __restrict__ poses, const float* __restrict__ disps,
-            const float* __restrict__ intr, const float* __restrict__ sens,
-            const float* __restrict__ targets, const float* __restrict__ weights,
-            const float* __restrict__ eta, int eta_rows, const int64_t* __restrict__ jj,
-            int t0, int P, int HW, int wd, float alpha, int k_lo, int k_hi, Ws ws) {
-  const int k = k_lo + blockIdx.y;
-  const int K = ws.info[0];
-  if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
-  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  const int ix = ws.kx[k];
-  const float fx = __ldg(intr), fy = __ldg(intr + 1), cx = __ldg(intr + 2), cy = __ldg(intr + 3);
-  const int n6 = 6 * P;
-
-  __shared__ float red[2][kWarps][96];
-
-  int px[PXT];
-  bool ok[PXT];
-  float X0[PXT], X1[PXT], d0[PXT];
-  float accC[PXT], accW[PXT], accE[PXT][6];
-#pragma unroll
-  for (int s = 0; s < PXT; ++s) {
-    px[s] = (blockIdx.x * PXT + s) * kThreads + tid;
-    ok[s] = px[s] < HW;
-    const int p = ok[s] ? px[s] : 0;
-    const int i = p / wd, j = p - i * wd;
-    X0[s] = ((float)j - cx) / fx;
-    X1[s] = ((float)i - cy) / fy;
-    d0[s] = ok[s] ? __ldg(disps + (size_t)ix * HW + p) : 0.f;
-    accC[s] = 0.f; accW[s] = 0.f;
-#pragma unroll
-    for (int c = 0; c < 6; ++c) accE[s][c] = 0.f;
-  }
-
-  const int e_lo = ws.csr_ptr[k], e_hi = ws.csr_ptr[k + 1];
-  int buf = 0;
-  for (int a = e_lo; a < e_hi; ++a, buf ^= 1) {
-    const int e = ws.csr_idx[a];
-    const int jx = (int)jj[e];
-    const bool stereo = ix == jx;
-    const Se3 G = stereo ? stereo_baseline() : load_relative(poses, ix, jx);
-
-    float h[96];
-#pragma unroll
-    for (int l = 0; l < 96; ++l) h[l] = 0.f;
-
-#pragma unroll
-    for (int s = 0; s < PXT; ++s) {
-      if (!ok[s]) continue;
-      const int p = px[s];
-      const float Xi[4] = {X0[s], X1[s], 1.0f, d0[s]};
-      float Xj[4];
-      act(G, Xi, Xj);
-      const float x = Xj[0], y = Xj[1], hh = Xj[3];
-      const bool near = Xj[2] < kMinDepth;
-      const float d = near ? 0.0f : 1.0f / Xj[2];
-      const float d2 = d * d;
-      const size_t tw = ((size_t)e * 2) * HW + p;
-      float wu = near ? 0.0f : (float)(0.001 * (double)__ldg(weights + tw));
-      float wv = near ? 0.0f : (float)(0.001 * (double)__ldg(weights + tw + HW));
-      const float ru = __ldg(targets + tw) - (fx * d * x + cx);
-      const float rv = __ldg(targets + tw + HW) - (fy * d * y + cy);
-
-      float J[12];           // [0,6) wrt pose i, [6,12) wrt pose j
-      float* Jj = J + 6;
-      // ---- u row
-      Jj[0] = fx * (hh * d);
-      Jj[1] = fx * 0.f;
-      Jj[2] = fx * (-x * hh * d2);
-      Jj[3] = fx * (-x * y * d2);
-      Jj[4] = fx * (1.0f + x * x * d2);
-      Jj[5] = fx * (-y * d);
-      float Jz = fx * (G.t[0] * d - G.t[2] * (x * d2));
-      float Cp = wu * Jz * Jz;
-      float Wp = wu * ru * Jz;
-      if (stereo) wu = 0.f;
-      adjoint_T(G, Jj, J);
-#pragma unroll
-      for (int n = 0; n < 6; ++n) J[n] = -J[n];
-      {
-        int l = 0;
-#pragma unroll
-        for (int n = 0; n < 12; ++n)
-#pragma unroll
-          for (int m = 0; m <= n; ++m) { h[l] += wu * J[n] * J[m]; ++l; }
-        const float wr = wu * ru;
-#pragma unroll
-        for (int n = 0; n < 12; ++n) h[78 + n] += wr * J[n];
-      }
-      float Ej[6];
-      if (!MOTION_ONLY) {
-        const float wz = wu * Jz;
-#pragma unroll
-        for (int n = 0; n < 6; ++n) { accE[s][n] += wz * J[n]; Ej[n] = wz * Jj[n]; }
-      }
-      // ---- v row
-      Jj[0] = fy * 0.f;
-      Jj[1] = fy * (hh * d);
-      Jj[2] = fy * (-y * hh * d2);
-      Jj[3] = fy * (-1.0f - y * y * d2);
-      Jj[4] = fy * (x * y * d2);
-      Jj[5] = fy * (x * d);
-      Jz = fy * (G.t[1] * d - G.t[2] * (y * d2));
-      Cp += wv * Jz * Jz;
-      Wp += wv * rv * Jz;
-      if (stereo) wv = 0.f;
-      adjoint_T(G, Jj, J);
-#pragma unroll
-      for (int n = 0; n < 6; ++n) J[n] = -J[n];
-      {
-        int l = 0;
-#pragma unroll
-        for (int n = 0; n < 12; ++n)
-#pragma unroll
-          for (int m = 0; m <= n; ++m) { h[l] += wv * J[n] * J[m]; ++l; }
-        const float wr = wv * rv;
-#pragma unroll
-        for (int n = 0; n < 12; ++n) h[78 + n] += wr * J[n];
-      }
-      if (!MOTION_ONLY) {
-        const float wz = wv * Jz;
-        float* Eo = ws.Eij + (size_t)e * 6 * HW + p;
-#pragma unroll
-        for (int n = 0; n < 6; ++n) {
-          accE[s][n] += wz * J[n];
-          Eo[(size_t)n * HW] = Ej[n] + wz * Jj[n];
-        }
-        accC[s] += Cp;
-        accW[s] += Wp;
-      }
-    }
-
-    // block reduction of the 90 pose terms of this edge, then float64 atomics into H, v
-    warp_reduce32(h, lane);
-    warp_reduce32(h + 32, lane);
-    warp_reduce32(h + 64, lane);
-    red[buf][wid][lane] = h[0];
-    red[buf][wid][32 + lane] = h[32];
-    red[buf][wid][64 + lane] = h[64];
-    __syncthreads();
-    if (tid < 90) {
-      float sum = 0.f;
-#pragma unroll
-      for (int w = 0; w < kWarps; ++w) sum += red[buf][w][tid];
-      const int pi = ix - t0, pj = jx - t0;
-      if (tid < 78) {
-        int n, m;
-        tri_unpack(tid, n, m);
-        const int rn = n < 6 ? pi : pj, cn = m < 6 ? pi : pj;
-        if (rn >= 0 && cn >= 0 && rn < P && cn < P) {
-          const int row = 6 * rn + (n % 6), col = 6 * cn + (m % 6);
-          atomicAdd(ws.H + (size_t)row * n6 + col, (double)sum);
-          if (n != m) atomicAdd(ws.H + (size_t)col * n6 + row, (double)sum);
-        }
-      } else {
-        const int n = tid - 78;
-        const int rn = n < 6 ? pi : pj;
-        if (rn >= 0 && rn < P) atomicAdd(ws.v + 6 * rn + (n % 6), (double)sum);
-      }
-    }
-  }
-
-  if (!MOTION_ONLY) {
-    const int er = eta_rows == 1 ? 0 : min(k, eta_rows - 1);
-    const int self = ix - t0;
-#pragma unroll
-    for (int s = 0; s < PXT; ++s) {
-      if (!ok[s]) continue;
-      const int p = px[s];
-      const float sd = __ldg(sens + (size_t)ix * HW + p);
-      const float m = sd > 0.f ? 1.0f : 0.0f;
-      const float C = accC[s] + m * alpha + (1.0f - m) * __ldg(eta + (size_t)er * HW + p);
-      const float wk = accW[s] - m * alpha * (d0[s] - sd);
-      ws.Q[(size_t)k * HW + p] = 1.0f / C;
-      ws.w[(size_t)k * HW + p] = wk;
-      if (self >= 0 && self < P) {
-#pragma unroll
-        for (int n = 0; n < 6; ++n) ws.Ei[((size_t)self * 6 + n) * HW + p] = accE[s][n];
-      }
-    }
-    if (eta_rows != 1 && eta_rows != K && blockIdx.x == 0 && tid == 0) ws.info[3] = 1;
-  }
-}
+// (the linearisation kernel lives in ba_lin2.cuh)
 
 // ------------------------------------------------------------------ Schur ----
 
@@ -718,12 +531,12 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
                                                  weights, eta, eta_rows, jj, t0, P, HW, wd,    \
                                                  alpha, k_lo, k_hi, ws)
   if (motion_only == 1) {
-    if (pxt == 4) DBAF_LIN(4, true); else if (pxt == 2) DBAF_LIN(2, true); else DBAF_LIN(1, true);
+    if (pxt == 2) DBAF_LIN(2, true); else DBAF_LIN(1, true);
   } else {
-    if (pxt == 4) DBAF_LIN(4, false); else if (pxt == 2) DBAF_LIN(2, false); else DBAF_LIN(1, false);
+    if (pxt == 2) DBAF_LIN(2, false); else DBAF_LIN(1, false);
   }
 #undef DBAF_LIN
-  DBAF_LAUNCH_CHECK("k_linearize");
+  DBAF_LAUNCH_CHECK("k_linearize2");
   if (motion_only == 0 && P > 0) {
     static bool schur_attr[64] = {};
     int dev_id = 0;
