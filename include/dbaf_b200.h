@@ -207,6 +207,8 @@ int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep,
  * satisfies |I-J| <= band_blocks (a temporal graph with edges reaching `reach` frames gives 2*reach).
  * Windows up to 6P = 160 ignore the hint and use the dense shared-memory solver; beyond that a band of
  * 1..25 blocks selects the sliding-window factorisation, anything else the slow dense fallback.
+ * Chains of 64 or more poses are factorised from both ends at once (two thread blocks meeting at a separator).
+ * The workspace must have gone through dbaf_ba_prepare (it zeroes the failure counter info[1]).
  * Replaces Eigen::SimplicialLLT on the host (src/droid_kernels.cu:1248-1269). */
 int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, int band_blocks, void* stream);
 
