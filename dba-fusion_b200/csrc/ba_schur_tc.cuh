@@ -2,17 +2,18 @@
 //
 // For a depth frame k with m row blocks (6m scalar rows e_a of E that touch its depths) the Schur term is
 //     S[a][b] = sum_px (e_a[px] q[px]) e_b[px],      sv[a] = sum_px (e_a[px] q[px]) w[px]
+// (computed as X X^T with X = E sqrt(q), w sqrt(q) riding along as one more row: q = 1/C > 0)
 // i.e. one (6m x HW) x (HW x 6m) product per frame: GEMM-shaped, K = HW.  The reference forms it block by
 // block (EEt6x6_kernel / Ev6x1_kernel, src/droid_kernels.cu:1046-1138) in fp32.  Here one CTA owns a frame
 // (x a pixel range) and runs it as a 128 x 128 x K TF32 product with fp32 accumulation in TMEM:
 //   * rows of E are contiguous in pixels, so both operands are K-major as they lie in HBM;
 //   * w rides along as row 126 of the B operand, so sv falls out as column 126 of the same product;
 //   * fp32 accuracy is kept with the usual three-product split  x = hi + lo  (hi = x rounded to TF32,
-//     lo = x - hi exactly):  A B^T ~ Ahi Bhi + Ahi Blo + Alo Bhi,  error ~2^-22 per product (tests compare
+//     lo = x - hi exactly):  X X^T ~ Xhi Xhi^T + Xhi Xlo^T + Xlo Xhi^T,  error ~2^-22 per product (tests compare
 //     against the fp32 SIMT kernel and the reference to 1e-4 normwise like every other path).
 // One warp streams 32-pixel slices of the 128 rows from HBM with 16-byte asynchronous copies (four slices =
-// 64 KB in flight per SM); eight transform warps scale them by q, split them and store the four operand tiles
-// (Ahi, Alo, Bhi, Blo; 16 KB each, 128-byte swizzled) of a 2-stage ring; one thread issues
+// 64 KB in flight per SM); eight transform warps scale them by sqrt(q), split them and store the two operand tiles
+// (Xhi, Xlo; 16 KB each, 128-byte swizzled; both are A and B operand) of a 2-stage ring; one thread issues
 // 12 tcgen05.mma.kind::tf32 (M = N = 128, K = 8) per slice into one of two TMEM accumulators.  The tensor core
 // accumulates with truncation, so each slice starts a fresh accumulator and the producer warps add the
 // finished slices into fp32 registers (round to nearest) while the next loads are in flight.  At the end
@@ -21,10 +22,10 @@
 #pragma once   // needs tc_ptx.cuh, included by ba.cu at file scope
 
 constexpr int kStcMaxM = 21;                 // 6 * 21 = 126 rows + w + q = 128
-constexpr int kStcOpStages = 2;
+constexpr int kStcOpStages = 4;             // operand stages = TMEM accumulators (4 x 128 columns): slice c uses slot c & 3
 constexpr int kStcRawStages = 4;
 constexpr int kStcTile = 128 * 128;          // bytes of one tile: 128 rows x 32 floats
-constexpr int kStcStageBytes = 4 * kStcTile; // Ahi, Alo, Bhi, Blo
+constexpr int kStcStageBytes = 2 * kStcTile; // Xhi, Xlo of X = E sqrt(q): both operands of the product
 constexpr int kStcXformWarps = 8;
 constexpr int kStcThreads = (kStcXformWarps + 2) * 32;   // + MMA issuer warp + loader warp
 constexpr size_t kStcSmemBytes = (size_t)kStcOpStages * kStcStageBytes + (size_t)kStcRawStages * kStcTile +
@@ -38,7 +39,7 @@ __device__ __forceinline__ float tf32_rna(float x) {
   return __uint_as_float(r);
 }
 // barrier slots
-constexpr int kBarRawFull = 0, kBarRawEmpty = 4, kBarOpFull = 8, kBarOpEmpty = 10, kBarAccFull = 12, kBarAccRead = 14;
+constexpr int kBarRawFull = 0, kBarRawEmpty = 4, kBarOpFull = 8, kBarOpEmpty = 12, kBarAccFull = 16, kBarAccRead = 20;
 
 __global__ void __launch_bounds__(kStcThreads, 1)
 k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min_m, int k_lo, int k_hi, Ws ws) {
@@ -57,7 +58,7 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
   const float** rowsrc = reinterpret_cast<const float**>(raw + kStcRawStages * kStcTile);   // [128]
   int* rowp = reinterpret_cast<int*>(rowsrc + 128);                        // [32]
   uint64_t* bars = reinterpret_cast<uint64_t*>(rowp + 32);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rows6 = 6 * m;
@@ -84,7 +85,7 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
       mbar_init(smem_u32(&bars[kBarRawFull + i]), 32);     // every lane of the loader warp
       mbar_init(smem_u32(&bars[kBarRawEmpty + i]), kStcXformWarps);
     }
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < kStcOpStages; ++i) {
       mbar_init(smem_u32(&bars[kBarOpFull + i]), kStcXformWarps);
       mbar_init(smem_u32(&bars[kBarOpEmpty + i]), 1);
       mbar_init(smem_u32(&bars[kBarAccFull + i]), 1);
@@ -92,7 +93,7 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kStcXformWarps) tc_alloc(smem_u32(tmem_slot), 256);
+  if (warp == kStcXformWarps) tc_alloc(smem_u32(tmem_slot), 512);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -131,23 +132,22 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
     if (lane == 0) {
       // ---------------------------------------------------------- MMA issuer
       for (int c = 0; c < n_chunks; ++c) {
-        const int st = c & 1;
-        if (c >= 2) mbar_wait(smem_u32(&bars[kBarAccRead + st]), ((c - 2) >> 1) & 1);   // accumulator st has been read
-        mbar_wait(smem_u32(&bars[kBarOpFull + st]), (c >> 1) & 1);
+        const int st = c & 3;
+        if (c >= 4) mbar_wait(smem_u32(&bars[kBarAccRead + st]), ((c - 4) >> 2) & 1);   // accumulator st has been read
+        mbar_wait(smem_u32(&bars[kBarOpFull + st]), (c >> 2) & 1);
         tc_fence_after();
         const uint32_t base = smem_u32(smem + st * kStcStageBytes);
         const uint32_t acc = tmem_base + (uint32_t)(st * 128);
         // the small cross terms first, while the accumulator is still small, then the four hi x hi products
 #pragma unroll
         for (int k8 = 0; k8 < 4; ++k8) {
-          const uint64_t ahi = umma_desc_k128(base + k8 * 32), alo = umma_desc_k128(base + kStcTile + k8 * 32);
-          const uint64_t bhi = umma_desc_k128(base + 2 * kStcTile + k8 * 32), blo = umma_desc_k128(base + 3 * kStcTile + k8 * 32);
-          tc_mma_tf32(acc, alo, bhi, kStcInstr, k8 ? 1u : 0u);
-          tc_mma_tf32(acc, ahi, blo, kStcInstr, 1u);
+          const uint64_t hi = umma_desc_k128(base + k8 * 32), lo = umma_desc_k128(base + kStcTile + k8 * 32);
+          tc_mma_tf32(acc, lo, hi, kStcInstr, k8 ? 1u : 0u);
+          tc_mma_tf32(acc, hi, lo, kStcInstr, 1u);
         }
 #pragma unroll
         for (int k8 = 0; k8 < 4; ++k8)
-          tc_mma_tf32(acc, umma_desc_k128(base + k8 * 32), umma_desc_k128(base + 2 * kStcTile + k8 * 32), kStcInstr, 1u);
+          tc_mma_tf32(acc, umma_desc_k128(base + k8 * 32), umma_desc_k128(base + k8 * 32), kStcInstr, 1u);
         tc_commit(smem_u32(&bars[kBarOpEmpty + st]));      // operand stage free
         tc_commit(smem_u32(&bars[kBarAccFull + st]));      // accumulator complete
       }
@@ -168,9 +168,9 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
     // each on average, always toward zero: -1.2e-7 relative on this data); the factor 1 + 2^-23 folded into the
     // FMA gives that expected loss back, leaving a zero-mean error below that of a sequential fp32 chain.
     auto drain = [&](int c) {
-      mbar_wait(smem_u32(&bars[kBarAccFull + (c & 1)]), (c >> 1) & 1);
+      mbar_wait(smem_u32(&bars[kBarAccFull + (c & 3)]), (c >> 2) & 1);
       tc_fence_after();
-      const uint32_t t = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)((c & 1) * 128 + half * 64);
+      const uint32_t t = tmem_base + ((uint32_t)(qd * 32) << 16) + (uint32_t)((c & 3) * 128 + half * 64);
       uint32_t d0[32], d1[32];
       tc_ld32x2(t, t + 32, d0, d1);
 #pragma unroll
@@ -180,22 +180,37 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bars[kBarAccRead + (c & 1)]));
+      if (lane == 0) mbar_arrive(smem_u32(&bars[kBarAccRead + (c & 3)]));
     };
+#ifdef DBAF_STC_PROFILE
+    long long sp[6] = {0, 0, 0, 0, 0, 0}, p0, p1;
+#define SP_TICK(i) do { p1 = clock64(); sp[i] += p1 - p0; p0 = p1; } while (0)
+#else
+#define SP_TICK(i) do {} while (0)
+#endif
     for (int c = 0; c < n_chunks; ++c) {
-      const int rs = c % kStcRawStages, st = c & 1;
+      const int rs = c % kStcRawStages, st = c & 3;
+#ifdef DBAF_STC_PROFILE
+      p0 = clock64();
+#endif
       mbar_wait(smem_u32(&bars[kBarRawFull + rs]), (c / kStcRawStages) & 1);
+      SP_TICK(0);
       // thread = (row group, 16-byte piece): 4 pixels of rows rg, rg+32, rg+64, rg+96.  A warp reads and writes
       // 4 whole rows per instruction (512 contiguous bytes in, 4 x 128 swizzled bytes out): no bank conflicts
       const uint8_t* rw = raw + rs * kStcTile;
-      const float4 q4 = *reinterpret_cast<const float4*>(rw + 127 * 128 + piece * 16);
+      const float4 q4r = *reinterpret_cast<const float4*>(rw + 127 * 128 + piece * 16);
+      // S = (E sqrt(q)) (E sqrt(q))^T: one scaled matrix serves as both operands (and S is symmetric by construction)
+      const float4 q4 = make_float4(sqrtf(q4r.x), sqrtf(q4r.y), sqrtf(q4r.z), sqrtf(q4r.w));
       float4 e4[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) e4[i] = *reinterpret_cast<const float4*>(rw + (rg + 32 * i) * 128 + piece * 16);
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bars[kBarRawEmpty + rs]));
-      if (c >= 2) drain(c - 2);
-      mbar_wait(smem_u32(&bars[kBarOpEmpty + st]), ((c >> 1) + 1) & 1);   // the MMAs that read this stage have retired
+      SP_TICK(1);
+      if (c >= 3) drain(c - 3);                                // three slices behind: its MMAs have long retired
+      SP_TICK(2);
+      mbar_wait(smem_u32(&bars[kBarOpEmpty + st]), ((c >> 2) + 1) & 1);   // the MMAs that read this stage have retired
+      SP_TICK(3);
       uint8_t* base = smem + st * kStcStageBytes;
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
@@ -205,18 +220,19 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
         if (r == 127) ev = make_float4(0.f, 0.f, 0.f, 0.f);             // row 127 only transports q
         const float4 aq = make_float4(ev.x * q4.x, ev.y * q4.y, ev.z * q4.z, ev.w * q4.w);
         const float4 ahi = make_float4(tf32_rna(aq.x), tf32_rna(aq.y), tf32_rna(aq.z), tf32_rna(aq.w));
-        const float4 bhi = make_float4(tf32_rna(ev.x), tf32_rna(ev.y), tf32_rna(ev.z), tf32_rna(ev.w));
         *reinterpret_cast<float4*>(base + off) = ahi;
         *reinterpret_cast<float4*>(base + kStcTile + off) = make_float4(aq.x - ahi.x, aq.y - ahi.y, aq.z - ahi.z, aq.w - ahi.w);
-        *reinterpret_cast<float4*>(base + 2 * kStcTile + off) = bhi;
-        *reinterpret_cast<float4*>(base + 3 * kStcTile + off) = make_float4(ev.x - bhi.x, ev.y - bhi.y, ev.z - bhi.z, ev.w - bhi.w);
       }
+      SP_TICK(4);
       fence_async_smem();                                      // generic-proxy stores -> visible to the MMA unit
       __syncwarp();
       if (lane == 0) mbar_arrive(smem_u32(&bars[kBarOpFull + st]));
+      SP_TICK(5);
     }
-    if (n_chunks >= 2) drain(n_chunks - 2);
-    drain(n_chunks - 1);
+#ifdef DBAF_STC_PROFILE
+    if (tid == 0 && blockIdx.x == 0 && blockIdx.y == 500) for (int i = 0; i < 6; ++i) ws.info[10 + i] = (int)(sp[i] / n_chunks);
+#endif
+    for (int c = max(0, n_chunks - 3); c < n_chunks; ++c) drain(c);
 
     // ------------------------------------------------------------ epilogue: H -= S, v -= sv
     const int a = qd * 32 + lane;                  // accumulator row = scalar row of E q
@@ -245,6 +261,6 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
   __syncthreads();
   if (warp == kStcXformWarps) {
     tc_fence_after();
-    tc_dealloc(tmem_base, 256);
+    tc_dealloc(tmem_base, 512);
   }
 }
