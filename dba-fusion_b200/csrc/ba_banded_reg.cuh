@@ -246,21 +246,33 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
       int rs = jm + 1 + o;
       if (rs >= NB) rs -= NB;
       const double* A = Praw + rs * kPnS + r * 6;
-      double x[6];
+      // column sweep: as soon as x[c] is final the later entries are corrected, so the serial chain per unknown
+      // is one multiply and one fused multiply-add (12 dependent operations instead of 21)
+      double x[6], lj[15], yj[6];
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
-        double sum = A[c];
+        x[c] = A[c];
+        yj[c] = yw[jm * 6 + c];
+      }
+      {
+        int l = 0;
 #pragma unroll
-        for (int k = 0; k < 6; ++k)
-          if (k < c) sum -= x[k] * Lj[c * 6 + k];
-        x[c] = sum * dd[c];
+        for (int c = 1; c < 6; ++c)
+#pragma unroll
+          for (int k = 0; k < c; ++k) lj[l++] = Lj[c * 6 + k];
       }
       double yy = 0.0;
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
+        x[c] *= dd[c];
+#pragma unroll
+        for (int k = c + 1; k < 6; ++k) x[k] = fma(-x[c], lj[k * (k - 1) / 2 + c], x[k]);
+        yy = fma(x[c], yj[c], yy);
+      }
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
         Pn[rs * kPnS + r * 6 + c] = x[c];
         Lband[((size_t)I * (B + 1) + (I - J)) * 36 + c * 6 + r] = x[c];     // transposed: see band_backsub
-        yy += x[c] * yw[jm * 6 + c];
       }
       yw[rs * 6 + r] -= yy;
     } else if (tid >= nt - 32) {
