@@ -131,23 +131,25 @@ k_schur_tc(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int min
   } else if (warp == kStcXformWarps) {
     if (lane == 0) {
       // ---------------------------------------------------------- MMA issuer
+      const uint64_t desc0 = umma_desc_k128(smem_u32(smem));
       for (int c = 0; c < n_chunks; ++c) {
         const int st = c & 3;
         if (c >= 4) mbar_wait(smem_u32(&bars[kBarAccRead + st]), ((c - 4) >> 2) & 1);   // accumulator st has been read
         mbar_wait(smem_u32(&bars[kBarOpFull + st]), (c >> 2) & 1);
         tc_fence_after();
-        const uint32_t base = smem_u32(smem + st * kStcStageBytes);
+        // shared-memory descriptors are linear in the address (start field = address >> 4): one is built before the
+        // loop, the other 31 are integer adds, so that the issuing thread keeps the tensor pipe fed
+        const uint64_t dhi = desc0 + (uint64_t)((st * kStcStageBytes) >> 4);
+        const uint64_t dlo = dhi + (uint64_t)(kStcTile >> 4);
         const uint32_t acc = tmem_base + (uint32_t)(st * 128);
         // the small cross terms first, while the accumulator is still small, then the four hi x hi products
 #pragma unroll
         for (int k8 = 0; k8 < 4; ++k8) {
-          const uint64_t hi = umma_desc_k128(base + k8 * 32), lo = umma_desc_k128(base + kStcTile + k8 * 32);
-          tc_mma_tf32(acc, lo, hi, kStcInstr, k8 ? 1u : 0u);
-          tc_mma_tf32(acc, hi, lo, kStcInstr, 1u);
+          tc_mma_tf32(acc, dlo + 2 * k8, dhi + 2 * k8, kStcInstr, k8 ? 1u : 0u);
+          tc_mma_tf32(acc, dhi + 2 * k8, dlo + 2 * k8, kStcInstr, 1u);
         }
 #pragma unroll
-        for (int k8 = 0; k8 < 4; ++k8)
-          tc_mma_tf32(acc, umma_desc_k128(base + k8 * 32), umma_desc_k128(base + k8 * 32), kStcInstr, 1u);
+        for (int k8 = 0; k8 < 4; ++k8) tc_mma_tf32(acc, dhi + 2 * k8, dhi + 2 * k8, kStcInstr, 1u);
         tc_commit(smem_u32(&bars[kBarOpEmpty + st]));      // operand stage free
         tc_commit(smem_u32(&bars[kBarAccFull + st]));      // accumulator complete
       }
