@@ -739,6 +739,63 @@ extern "C" int dbaf_ba(void* workspace, float* poses, float* disps, const float*
   return DBAF_OK;
 }
 
+// ------------------------------------------------------- H/v hand-off to the factor graph ----
+// BA2GTSAM, dbaf/depth_video.py:20-29: H' = J^T H J, v' = J^T v with J = blockdiag(A), A a 6x6 matrix (the
+// row-swapped -Ad(Tbc^-1) that carries camera-frame tangents to the body frame).  The reference does this with
+// two dense 6P x 6P host matmuls per iteration; per 6x6 block it is A^T H_IK A, done here on the device on the
+// way out, so that one copy delivers the system in the form the factor graph wants.
+namespace dbaf {
+namespace {
+__global__ void __launch_bounds__(64)
+k_congruence(const double* __restrict__ H, const double* __restrict__ v, const double* __restrict__ A, int P,
+             double* __restrict__ Ho, double* __restrict__ vo) {
+  __shared__ double As[36], Hb[36], Tb[36];
+  const int I = blockIdx.y, K = blockIdx.x, t = threadIdx.x;
+  const int n = 6 * P;
+  if (t < 36) {
+    As[t] = A[t];
+    Hb[t] = H[(size_t)(6 * I + t / 6) * n + 6 * K + t % 6];
+  }
+  __syncthreads();
+  if (t < 36) {                        // T = H_IK A
+    const int r = t / 6, c = t % 6;
+    double s = 0.0;
+#pragma unroll
+    for (int b = 0; b < 6; ++b) s += Hb[r * 6 + b] * As[b * 6 + c];
+    Tb[t] = s;
+  }
+  __syncthreads();
+  if (t < 36) {                        // A^T T
+    const int r = t / 6, c = t % 6;
+    double s = 0.0;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) s += As[a * 6 + r] * Tb[a * 6 + c];
+    Ho[(size_t)(6 * I + r) * n + 6 * K + c] = s;
+  } else if (K == 0 && t < 42) {
+    const int r = t - 36;
+    double s = 0.0;
+#pragma unroll
+    for (int a = 0; a < 6; ++a) s += As[a * 6 + r] * v[6 * I + a];
+    vo[6 * I + r] = s;
+  }
+}
+}  // namespace
+}  // namespace dbaf
+
+extern "C" int dbaf_ba_congruence(void* workspace, int t0, int t1, const double* A, double* H_out, double* v_out,
+                                  void* stream) {
+  DBAF_REQUIRE(workspace != nullptr && A != nullptr && H_out != nullptr && v_out != nullptr, "null pointer");
+  DBAF_REQUIRE(t1 >= t0, "t1 < t0");
+  const int P = t1 - t0;
+  if (P == 0) return DBAF_OK;
+  dbaf_ba_layout L;
+  fill_layout(1, 0, 0, P, 1, 1, &L);          // H and v offsets depend on P alone
+  Ws ws = view(workspace, L);
+  k_congruence<<<dim3(P, P), 64, 0, (cudaStream_t)stream>>>(ws.H, ws.v, A, P, H_out, v_out);
+  DBAF_LAUNCH_CHECK("k_congruence");
+  return DBAF_OK;
+}
+
 // ------------------------------------------------------- host-buffer entry point ----
 namespace {
 struct HostStage {

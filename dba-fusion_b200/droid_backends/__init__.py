@@ -307,6 +307,25 @@ class BACore:
         w.linearize(0.001)                 # alpha = 0.001, src/droid_kernels.cu:1872
         _export(w, H, v)
 
+    def hessian_gtsam(self, H, v, A):
+        """`hessian` followed by gtsam.BA2GTSAM (dbaf/depth_video.py:20-29, call site :527-530) in one go:
+        H <- J^T H J, v <- J^T v with J = blockdiag(A), computed on the device before the copy to the caller's
+        float64 CPU tensors.  A: [6,6] float64 (the row-swapped -Ad(Tbc^-1) of the reference)."""
+        w = self._w
+        if H.dtype != torch.float64 or v.dtype != torch.float64 or H.is_cuda or v.is_cuda:
+            raise RuntimeError("H and v must be float64 CPU tensors")
+        if tuple(H.shape) != (w.n, w.n) or v.numel() != w.n:
+            raise RuntimeError("hessian_gtsam expects the full reduced system")
+        w.linearize(0.001)                 # alpha = 0.001, src/droid_kernels.cu:1872
+        dev = w.ws.device
+        Ad = torch.as_tensor(A, dtype=torch.float64).reshape(6, 6).contiguous().to(dev)
+        out = torch.empty(w.n * w.n + w.n, dtype=torch.float64, device=dev)
+        check(lib.dbaf_ba_congruence(_p(w.ws), w.t0, w.t1, _p(Ad), _p(out), c_void_p(out.data_ptr() + 8 * w.n * w.n),
+                                     _stream()), "dbaf_ba_congruence")
+        host = out.cpu()                   # one D2H copy, synchronises the stream
+        H.copy_(host[:w.n * w.n].view(w.n, w.n))
+        v.reshape(-1).copy_(host[w.n * w.n:])
+
     def optimize(self, H, v):
         w = self._w
         if H.shape != (w.n, w.n) or v.numel() != w.n:

@@ -47,6 +47,7 @@ SIGNATURES = {
                                                  ctypes.POINTER(c_void_p), P, c_size_t, P]),
     "dbaf_ba_workspace_layout": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(BaLayout)]),
     "dbaf_ba_prepare": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P]),
+    "dbaf_ba_congruence": (c_int, [P, c_int, c_int, P, P, P, P]),
     "dbaf_ba_host_staging_bytes": (c_size_t, [c_int] * 7),
     "dbaf_ba_host": (c_int, [P, P, c_size_t] + [P] * 7 + [c_int, P, P] + [c_int] * 7 + [c_float, c_float, c_int, P, P]),
     "dbaf_ba_tables_noalloc": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P, P, P]),

@@ -229,6 +229,13 @@ int dbaf_ba(void* workspace, float* poses, float* disps, const float* intrinsics
             int n_edges, int n_frames, int t0, int t1, int ht, int wd, int iterations,
             float lm, float ep, int motion_only, float* dx_out, float* dz_out, void* stream);
 
+/* BA2GTSAM, dbaf/depth_video.py:20-29 (a "next" row of the scope table): the reduced camera system left in the
+ * workspace by dbaf_ba_linearize, transformed block by block, H_out = J^T H J, v_out = J^T v with J = blockdiag(A).
+ * A: float64 [6,6] row-major on the device (the reference passes the row-swapped -Ad(Tbc^-1));
+ * H_out float64 [(6P),(6P)], v_out float64 [6P] on the device (they must not alias the workspace). */
+int dbaf_ba_congruence(void* workspace, int t0, int t1, const double* A, double* H_out, double* v_out,
+                       void* stream);
+
 /* The same call for callers whose window lives in HOST memory (a frontend that assembles targets/weights on the
  * CPU, a process that receives them over IPC): every input is copied to `staging` (device scratch of
  * dbaf_ba_host_staging_bytes() bytes) with cudaMemcpyAsync on `stream`, dbaf_ba runs on the copies, and the updated

@@ -492,6 +492,18 @@ def projmap(poses, disps, intr, ii, jj, dtype=np.float32):
     return coords.reshape(n, ht, wd, 3), valid.reshape(n, ht, wd, 1)
 
 
+def ba2gtsam(H, v, A):
+    """BA2GTSAM, dbaf/depth_video.py:20-29 with the 6x6 matrix A given (the reference builds it from
+    gtsam.Pose3: the rows of -Tbc.inverse().AdjointMap() swapped, :21-23): J = blockdiag(A),
+    returns J^T H J and J^T v."""
+    H, v, A = np.asarray(H, np.float64), np.asarray(v, np.float64), np.asarray(A, np.float64)
+    ss = H.shape[0] // 6
+    J = np.zeros_like(H)
+    for i in range(ss):
+        J[i * 6:i * 6 + 6, i * 6:i * 6 + 6] = A
+    return J.T @ H @ J, J.T @ v
+
+
 def reproject(poses, disps, intr, ii, jj, dtype=np.float32):
     """DepthVideo.reproject, dbaf/depth_video.py:221-229 -> projective_transform without Jacobians,
     dbaf/geom/projective_ops.py:96-125: iproj with the intrinsics of frame ii (:18-31), Gij = Tj * Ti^-1 with

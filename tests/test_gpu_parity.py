@@ -466,3 +466,22 @@ def test_lookup_at_integer_coordinates_returns_volume_entries_c2_full_size(dev, 
                 want = torch.gather(vol.reshape(E, ht, wd, h2 * w2), 3, flat).squeeze(-1)
                 want = torch.where(inb, want, torch.zeros_like(want))
                 assert torch.equal(out[:, l, a, b].view(torch.int16), want.view(torch.int16)), (l, a, b)
+
+
+def test_bacore_hessian_gtsam_matches_ba2gtsam(dev, db, oracle, synth):
+    """BACore.hessian_gtsam = BACore.hessian followed by BA2GTSAM (dbaf/depth_video.py:20-29,527-530)."""
+    w = synth.make_window("tiny", seed=9, sensor_frac=0.2)
+    t = to_torch(w, dev)
+    args = (t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], t["eta"],
+            t["ii"], t["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, False)
+    n = 6 * (w["t1"] - w["t0"])
+    core = db.BACore()
+    core.init(*args)
+    H, v = torch.zeros(n, n, dtype=torch.float64), torch.zeros(n, dtype=torch.float64)
+    core.hessian(H, v)
+    rng = np.random.default_rng(0)
+    A = rng.normal(0, 1, (6, 6))
+    Hg, vg = torch.zeros(n, n, dtype=torch.float64), torch.zeros(n, dtype=torch.float64)
+    core.hessian_gtsam(Hg, vg, A)
+    wantH, wantv = oracle.ba2gtsam(H.numpy(), v.numpy(), A)
+    assert relerr(Hg.numpy(), wantH) < 1e-12 and relerr(vg.numpy(), wantv) < 1e-12
