@@ -97,7 +97,8 @@ __device__ __forceinline__ void load_row8_h(const __half* __restrict__ vol, long
 template <typename T, int R>
 __global__ void __launch_bounds__(kThreads)
 k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, int h2_0, int w2_0,
-              int ch_total, T* __restrict__ out) {
+              int ch_total, T* __restrict__ out, const int* __restrict__ slot, int n_vol) {
+  // slot != null: edge e reads volume slot[e] of a pool of n_vol volumes (CorrPool); else its own, n_vol == n
   constexpr int RD = 2 * R + 1;
   const int level = blockIdx.z / n;
   const int e = blockIdx.z - level * n;
@@ -111,8 +112,8 @@ k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, in
   const float dx = x0 - fx0, dy = y0 - fy0;
   const int bx = window_base(fx0, R), by = window_base(fy0, R);
 
-  const long long slab = ((long long)e * HW1 + p) * (long long)(h2 * w2);
-  const long long total = (long long)n * HW1 * (long long)(h2 * w2);
+  const long long slab = ((long long)(slot ? slot[e] : e) * HW1 + p) * (long long)(h2 * w2);
+  const long long total = (long long)n_vol * HW1 * (long long)(h2 * w2);
   // selected with compares so that the pointer table stays in the parameter bank (no local copy)
   const void* volp = lv.vol[0];
 #pragma unroll
@@ -280,10 +281,11 @@ k_corr_lookup_bwd(const float* __restrict__ coords, const T* __restrict__ cg, in
 
 template <typename T>
 int launch_lookup(const LevelPtrs& lv, int levels, const float* coords, int n, int HW1, int h2, int w2,
-                  int radius, T* out, cudaStream_t st) {
+                  int radius, T* out, cudaStream_t st, const int* slot = nullptr, int n_vol = -1) {
+  if (n_vol < 0) n_vol = n;
   dim3 grid((HW1 + kThreads - 1) / kThreads, 1, n * levels);
   if (radius == 3) {
-    k_corr_lookup<T, 3><<<grid, kThreads, 0, st>>>(lv, coords, n, HW1, h2, w2, levels * 49, out);
+    k_corr_lookup<T, 3><<<grid, kThreads, 0, st>>>(lv, coords, n, HW1, h2, w2, levels * 49, out, slot, n_vol);
   } else {
     // generic radius: one level per launch
     const int rd = 2 * radius + 1;
@@ -328,6 +330,25 @@ extern "C" int dbaf_corr_lookup_pyramid(const void* const* volumes_host, int lev
   if (dtype == DBAF_F16)
     return launch_lookup<__half>(lv, levels, coords, n, h1 * w1, h2, w2, radius, static_cast<__half*>(out), (cudaStream_t)stream);
   return launch_lookup<float>(lv, levels, coords, n, h1 * w1, h2, w2, radius, static_cast<float*>(out), (cudaStream_t)stream);
+}
+
+// The same lookup over a slot pool: edge e reads volume slots[e] of pools holding `capacity` volumes per level
+// (slots are not range-checked here: dbaf_corr_volume_pyramid_pool checked them when it filled the pool).
+extern "C" int dbaf_corr_lookup_pyramid_pool(const void* const* pool_host, int levels, int dtype, const float* coords,
+                                             const int32_t* slots, int n, int capacity, int h1, int w1, int h2, int w2,
+                                             int radius, void* out, void* stream) {
+  DBAF_REQUIRE(dtype == DBAF_F16 || dtype == DBAF_F32, "dtype must be DBAF_F16 or DBAF_F32");
+  DBAF_REQUIRE(levels >= 1 && levels <= kMaxLevels, "levels out of range");
+  DBAF_REQUIRE(radius == 3, "pyramid lookup supports radius 3 only");
+  DBAF_REQUIRE(n >= 0 && capacity > 0 && h1 > 0 && w1 > 0 && h2 >= 0 && w2 >= 0 && slots != nullptr, "bad sizes");
+  if (n == 0) return DBAF_OK;
+  LevelPtrs lv{};
+  for (int l = 0; l < levels; ++l) lv.vol[l] = pool_host[l];
+  if (dtype == DBAF_F16)
+    return launch_lookup<__half>(lv, levels, coords, n, h1 * w1, h2, w2, radius, static_cast<__half*>(out), (cudaStream_t)stream,
+                                 slots, capacity);
+  return launch_lookup<float>(lv, levels, coords, n, h1 * w1, h2, w2, radius, static_cast<float*>(out), (cudaStream_t)stream, slots,
+                              capacity);
 }
 
 extern "C" int dbaf_corr_index_backward(const float* coords, const void* corr_grad, int dtype, int n,

@@ -16,7 +16,7 @@ namespace dbaf {
 // volume_tc.cu
 int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
                    int ht, int wd, int levels, __half* const* out, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st, int* levels_done);
+                   cudaStream_t st, int* levels_done, const int* out_slot, int n_out);
 size_t corr_volume_tc_workspace(int n1, int n2, int C, int ht, int wd);
 
 namespace {
@@ -26,7 +26,7 @@ constexpr int kTile = 64;
 // 64x64 output tile per CTA, 256 threads x (4x4), K staged 32 channels at a time.
 __global__ void __launch_bounds__(256)
 k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, const int* __restrict__ idx1,
-              const int* __restrict__ idx2, int C, int HW, __half* __restrict__ out) {
+              const int* __restrict__ idx2, int C, int HW, __half* __restrict__ out, const int* __restrict__ out_slot) {
   __shared__ float As[32][kTile + 1];
   __shared__ float Bs[32][kTile + 1];
   const int e = blockIdx.z;
@@ -62,7 +62,7 @@ k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, cons
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       const int nn = n0 + tx * 4 + j;
-      if (nn < HW) out[((size_t)e * HW + m) * HW + nn] = __float2half_rn(acc[i][j]);   // operands were divided by 4 in fp16, corr.py:67-68
+      if (nn < HW) out[((size_t)(out_slot ? out_slot[e] : e) * HW + m) * HW + nn] = __float2half_rn(acc[i][j]);   // operands were divided by 4 in fp16, corr.py:67-68
     }
   }
 }
@@ -84,7 +84,10 @@ __device__ __forceinline__ void group_sync(int gthreads) {
 
 __global__ void __launch_bounds__(128)
 k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int levels,
-          __half* __restrict__ L1, __half* __restrict__ L2, __half* __restrict__ L3, int gthreads, int group_halves) {
+          __half* __restrict__ L1, __half* __restrict__ L2, __half* __restrict__ L3, int gthreads, int group_halves,
+          const int* __restrict__ slot, int hw_src, long long total_slabs) {
+  // slot != null: logical slab s = (edge, source pixel) lives at physical slab slot[edge] * hw_src + pixel of buffers
+  // that hold total_slabs slabs
   extern __shared__ __half sm[];
   const int s0 = h2 * w2;
   const int h1 = h2 >> 1, w1 = w2 >> 1, hq = h2 >> 2, wq = w2 >> 2, he = h2 >> 3, we = w2 >> 3;
@@ -95,7 +98,8 @@ k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int le
   __half* a1 = raw + ((s0 + 15) & ~7);
   __half* a2 = a1 + h1 * w1;
   const bool vec = (reinterpret_cast<size_t>(L0) & 15) == 0;
-  for (long long s = (long long)blockIdx.x * groups + grp; s < slabs; s += (long long)gridDim.x * groups) {
+  for (long long sl = (long long)blockIdx.x * groups + grp; sl < slabs; sl += (long long)gridDim.x * groups) {
+    const long long s = slot ? (long long)slot[sl / hw_src] * hw_src + sl % hw_src : sl;
     const long long first = s * s0;
     const int off = vec ? (int)(first & 7) : 0;
     const __half* a0 = raw + off;
@@ -103,7 +107,7 @@ k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int le
       const uint4* src = reinterpret_cast<const uint4*>(L0 + (first - off));
       const int nvec = (off + s0 + 7) >> 3;
       // the last vector may reach past the end of the whole volume: it is then read element-wise
-      const bool tail_ok = first - off + (long long)nvec * 8 <= slabs * (long long)s0;
+      const bool tail_ok = first - off + (long long)nvec * 8 <= total_slabs * (long long)s0;
       for (int t = gt; t < nvec - (tail_ok ? 0 : 1); t += gthreads) reinterpret_cast<uint4*>(raw)[t] = __ldg(src + t);
       if (!tail_ok)
         for (int t = (nvec - 1) * 8 + gt; t < off + s0; t += gthreads) raw[t] = L0[first - off + t];
@@ -146,8 +150,9 @@ __global__ void k_check_index(const int* __restrict__ idx, int n, int limit, int
 
 int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
                    int ht, int wd, int levels, void* const* out_host, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st) {
+                   cudaStream_t st, const int* out_slot = nullptr, int n_out = -1) {
   const int HW = ht * wd;
+  if (n_out < 0) n_out = n;
   __half* outs[4] = {nullptr, nullptr, nullptr, nullptr};
   for (int l = 0; l < levels; ++l) outs[l] = static_cast<__half*>(out_host[l]);
   // DBAF_VOLUME_IMPL=simt forces the cross-check kernels (tests use it to validate the
@@ -157,13 +162,13 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
   int done = 0;
   if (!force_simt) {
     const int rc = corr_volume_tc(f1, n1, f2, n2, idx1, idx2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st,
-                                  &done);
+                                  &done, out_slot, n_out);
     if (rc != DBAF_OK) return rc;
     if (done >= levels) return DBAF_OK;
   }
   if (done == 0) {
     dim3 grid((HW + kTile - 1) / kTile, (HW + kTile - 1) / kTile, n);
-    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, idx1, idx2, C, HW, outs[0]);
+    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, idx1, idx2, C, HW, outs[0], out_slot);
     DBAF_LAUNCH_CHECK("k_volume_simt");
   }
   if (levels > std::max(done, 1)) {
@@ -184,7 +189,8 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
     const long long slabs = (long long)n * HW;
     const int blocks = (int)std::min<long long>((slabs + 128 / gthreads - 1) / (128 / gthreads), 148LL * 16);
     k_pyramid<<<blocks, 128, smem, st>>>(outs[src], slabs, hs, wsz, levels - src, outs[src + 1], src + 2 < 4 ? outs[src + 2] : nullptr,
-                                         src + 3 < 4 ? outs[src + 3] : nullptr, gthreads, group_halves);
+                                         src + 3 < 4 ? outs[src + 3] : nullptr, gthreads, group_halves, out_slot, HW,
+                                         (long long)n_out * HW);
     DBAF_LAUNCH_CHECK("k_pyramid");
   }
   return DBAF_OK;
@@ -238,4 +244,29 @@ extern "C" int dbaf_corr_volume_pyramid_indexed(const void* fmaps1, int n1, cons
   }
   return volume_pyramid(static_cast<const __half*>(fmaps1), n1, static_cast<const __half*>(fmaps2), n2, ii, jj, n_edges,
                         C, ht, wd, levels, out_host, workspace, ws_bytes, st);
+}
+
+// ---------------------------------------------------------------- slot pool (CorrBlock bookkeeping) ----
+extern "C" int dbaf_corr_volume_pyramid_pool(const void* fmaps1, int n1, const void* fmaps2, int n2,
+                                             const int32_t* ii, const int32_t* jj, const int32_t* slots, int n_edges,
+                                             int capacity, int C, int ht, int wd, int levels, void* const* pool_host,
+                                             void* workspace, size_t workspace_bytes, void* stream) {
+  DBAF_REQUIRE(n1 > 0 && n2 > 0 && n_edges >= 0 && capacity > 0 && C > 0 && ht > 0 && wd > 0, "bad sizes");
+  DBAF_REQUIRE(levels >= 1 && levels <= 4, "levels must be 1..4");
+  DBAF_REQUIRE(pool_host != nullptr && ii != nullptr && jj != nullptr && slots != nullptr, "null pointer");
+  if (n_edges == 0) return DBAF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  DBAF_REQUIRE(workspace != nullptr && workspace_bytes >= 256, "workspace too small");
+  int* flag = reinterpret_cast<int*>((reinterpret_cast<uintptr_t>(workspace) + workspace_bytes - 64) & ~(uintptr_t)63);
+  DBAF_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), st));
+  k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(ii, n_edges, n1, flag);
+  k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(jj, n_edges, n2, flag);
+  k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(slots, n_edges, capacity, flag);
+  DBAF_LAUNCH_CHECK("k_check_index");
+  int bad = 0;
+  DBAF_CUDA(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
+  DBAF_CUDA(cudaStreamSynchronize(st));
+  DBAF_REQUIRE(bad == 0, "frame index or slot out of range");
+  return volume_pyramid(static_cast<const __half*>(fmaps1), n1, static_cast<const __half*>(fmaps2), n2, ii, jj, n_edges,
+                        C, ht, wd, levels, pool_host, workspace, workspace_bytes - 256, st, slots, capacity);
 }

@@ -83,7 +83,7 @@ __global__ void __launch_bounds__(kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
             int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2,
-            int chunk_px, int n_mma, int kr, int wd) {
+            int chunk_px, int n_mma, int kr, int wd, const int* __restrict__ out_slot) {
   // chunk_px: target pixels a chunk advances by; n_mma: UMMA N (chunk_px rounded up to 16, <= 256);
   // kr > 0 (generic shapes only): a chunk is 2*kr whole image rows of width wd, and level 1 is pooled from it here
   extern __shared__ uint8_t smem_raw[];
@@ -104,6 +104,8 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
   const int n_chunks = (HW + chunk_px - 1) / chunk_px;
   // operand rows: the edge's own maps, or frames picked by index (video.fmaps[ii] / [jj], covisible_graph.py:129-130)
   const int ea = idx1 ? idx1[e] : e, eb = idx2 ? idx2[e] : e;
+  // where the edge's volume goes: its own position, or a slot of a larger pool (CorrPool)
+  const int eo = out_slot ? out_slot[e] : e;
 
   if (threadIdx.x == 0) {
     mbar_init(smem_u32(&bars[0]), 1);
@@ -173,7 +175,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     const int q = warp - 4;                           // TMEM lane quarter == warp % 4
     const int m = m0 + q * 32 + lane;                 // this thread's source pixel
     const bool mok = m < HW;
-    const size_t row = (size_t)e * HW + (mok ? m : 0);
+    const size_t row = (size_t)eo * HW + (mok ? m : 0);
     uint32_t carry2[8];                               // level-2 row of the even chunk (FUSE)
 #pragma unroll
     for (int i = 0; i < 8; ++i) carry2[i] = 0;
@@ -234,7 +236,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         fence_async_smem();
         __syncwarp();
         if (lane == 0) {
-          const int r0 = e * HW + m0 + q * 32;
+          const int r0 = eo * HW + m0 + q * 32;
 #pragma unroll
           for (int rr = 0; rr < 4; ++rr) tma_store_2d(&mapO0, smem_u32(stage + rr * 4096), c * kBN + rr * 64, r0);
           if (out.l[1]) tma_store_2d(&mapO1, smem_u32(stage + 4 * 4096), c * 64, r0);
@@ -308,7 +310,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         const int nrow = min(32, HW - mrow0);
 #pragma unroll 2
         for (int r = 0; r < nrow; ++r) {
-          unsigned short* dst = reinterpret_cast<unsigned short*>(out.l[0]) + ((size_t)e * HW + mrow0 + r) * (size_t)HW + n0 + lane;
+          unsigned short* dst = reinterpret_cast<unsigned short*>(out.l[0]) + ((size_t)eo * HW + mrow0 + r) * (size_t)HW + n0 + lane;
           unsigned short v[kBN / 32];
           const unsigned short* src = reinterpret_cast<const unsigned short*>(tile) + r * 258 + lane;
 #pragma unroll
@@ -333,7 +335,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
             offA[t] = j < nout ? j : -1;
           }
           const unsigned short* t16 = reinterpret_cast<const unsigned short*>(tile);
-          unsigned short* l1base = reinterpret_cast<unsigned short*>(out.l[1]) + ((size_t)e * HW + mrow0) * (size_t)hw1 +
+          unsigned short* l1base = reinterpret_cast<unsigned short*>(out.l[1]) + ((size_t)eo * HW + mrow0) * (size_t)hw1 +
                                    (size_t)c * kr * w1;
 #pragma unroll 4
           for (int r = 0; r < nrow; ++r) {
@@ -420,12 +422,13 @@ size_t corr_volume_tc_workspace(int n1, int n2, int C, int ht, int wd) {
 // f1 [n1,C,ht,wd], f2 [n2,C,ht,wd]; edge e correlates f1[idx1[e]] with f2[idx2[e]] (idx null: e itself).
 int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
                    int ht, int wd, int levels, __half* const* out, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st, int* levels_done) {
+                   cudaStream_t st, int* levels_done, const int* out_slot, int n_out) {
+  // out_slot / n_out: edge e is written to slot out_slot[e] of outputs that hold n_out volumes (null: e itself, n)
   *levels_done = 0;
   const int HW = ht * wd;
   if (C != kC) return DBAF_OK;                              // the SIMT kernel takes other channel counts
   if (workspace == nullptr || workspace_bytes < corr_volume_tc_workspace(n1, n2, C, ht, wd)) return DBAF_OK;
-  if ((size_t)n * HW >= (size_t)1 << 31 || (size_t)std::max(n1, n2) * HW >= (size_t)1 << 31) return DBAF_OK;
+  if ((size_t)std::max(n, n_out) * HW >= (size_t)1 << 31 || (size_t)std::max(n1, n2) * HW >= (size_t)1 << 31) return DBAF_OK;
   __half* a_t = reinterpret_cast<__half*>((reinterpret_cast<uintptr_t>(workspace) + 255) & ~(uintptr_t)255);
   __half* b_t = a_t + (size_t)n1 * HW * C;
   const bool shared_src = f1 == f2 && n1 == n2;             // one set of frames on both sides: transpose it once
@@ -448,10 +451,10 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
   const int m_tiles = (HW + kBM - 1) / kBM;
   CUtensorMap mapO0 = mapA, mapO1 = mapA;     // only the fused kernel stores through tensor maps
   if (fuse) {
-    if (int rc = make_map2(&mapO0, out[0], (size_t)n * HW, (size_t)HW, 32)) return rc;
+    if (int rc = make_map2(&mapO0, out[0], (size_t)n_out * HW, (size_t)HW, 32)) return rc;
     mapO1 = mapO0;
     if (levels > 1)
-      if (int rc = make_map2(&mapO1, out[1], (size_t)n * HW, (size_t)HW / 4, 32)) return rc;
+      if (int rc = make_map2(&mapO1, out[1], (size_t)n_out * HW, (size_t)HW / 4, 32)) return rc;
   }
   Pyr pyr;
   for (int l = 0; l < 4; ++l) pyr.l[l] = (fuse && l < levels) ? out[l] : nullptr;
@@ -465,8 +468,8 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[dev_id & 63][fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd);
-  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd);
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
   DBAF_LAUNCH_CHECK("k_volume_tc");
   // fused: all requested levels are written; generic with row-pair chunks: levels 0 and 1; otherwise level 0 only.
   // The caller pools the rest.

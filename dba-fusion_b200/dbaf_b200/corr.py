@@ -142,3 +142,58 @@ class AltCorrBlock:
         if single:
             corr = corr.squeeze(-1)
         return corr.contiguous()
+
+
+class CorrPool:
+    """CorrBlock whose pyramids live in a fixed pool of `capacity` slots, so that adding and removing edges
+    never copies a volume.  The reference re-creates its pyramid tensors on every edge change
+    (`CorrBlock.cat`, `CorrBlock.__getitem__` with a boolean mask, dbaf/modules/corr.py:52-60, called from
+    dbaf/covisible_graph.py:131-132 and :166-167): adding one keyframe's edges to a 48-edge graph copies the whole
+    2 GB pyramid.  Here `append` builds the new edges' volumes straight into free slots and `keep` only edits the
+    edge -> slot table; the lookup reads through that table.  Edge order is the order of the calls, as in the
+    reference (new edges at the end, removal keeps the order of the survivors), and the lookup result is
+    bit-identical to a CorrBlock built from scratch on the surviving edge list."""
+
+    def __init__(self, capacity, ht, wd, num_levels=4, radius=3, device="cuda", dtype=torch.float16):
+        if radius != 3:
+            raise RuntimeError("CorrPool supports radius 3 (the only one the pipeline uses)")
+        self.capacity, self.ht, self.wd = int(capacity), int(ht), int(wd)
+        self.num_levels, self.radius = int(num_levels), int(radius)
+        self.pool = [torch.empty(self.capacity, ht, wd, ht >> l, wd >> l, dtype=dtype, device=device)
+                     for l in range(self.num_levels)]
+        self.slots = torch.empty(0, dtype=torch.int32, device=device)      # slot of every live edge, in edge order
+        self._free = list(range(self.capacity - 1, -1, -1))               # host-side free list (pop from the end)
+
+    def __len__(self):
+        return int(self.slots.numel())
+
+    def append(self, fmaps1, fmaps2, ii, jj):
+        """Add the edges (ii[e], jj[e]): correlate fmaps1[ii[e]] with fmaps2[jj[e]] (per-frame stacks [n,C,ht,wd])."""
+        n_new = int(ii.numel())
+        if n_new == 0:
+            return
+        if n_new > len(self._free):
+            raise RuntimeError(f"CorrPool is full: {n_new} new edges, {len(self._free)} free slots")
+        new = [self._free.pop() for _ in range(n_new)]
+        dev = self.slots.device
+        new_t = torch.tensor(new, dtype=torch.int32, device=dev)
+        f1 = fmaps1 if fmaps1.dtype == torch.float16 else fmaps1.half()
+        f2 = f1 if fmaps2 is fmaps1 else (fmaps2 if fmaps2.dtype == torch.float16 else fmaps2.half())
+        droid_backends.corr_volume_pyramid_pool(f1.contiguous(), f2.contiguous(), ii, jj, new_t, self.pool)
+        self.slots = torch.cat([self.slots, new_t])
+
+    def keep(self, mask):
+        """Drop the edges where `mask` is False (the reference's `corr = corr[~remove_mask]`)."""
+        mask = mask.to(self.slots.device)
+        gone = self.slots[~mask].tolist()
+        self._free.extend(reversed(gone))
+        self.slots = self.slots[mask].contiguous()
+
+    def __call__(self, coords):
+        """coords [batch=1, num, ht, wd, 2] as for CorrBlock.__call__ -> [1, num, levels*49, ht, wd]."""
+        batch, num, ht, wd, _ = coords.shape
+        if batch != 1 or num != len(self):
+            raise RuntimeError("coords must be [1, number of live edges, ht, wd, 2]")
+        c = coords.permute(0, 1, 4, 2, 3).contiguous().view(num, 2, ht, wd)
+        out = droid_backends.corr_lookup_pyramid_pool(self.pool, c.float(), self.slots, self.radius)
+        return out.view(1, num, -1, ht, wd)

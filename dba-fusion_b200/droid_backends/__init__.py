@@ -548,6 +548,51 @@ def corr_volume_pyramid_indexed(fmaps1, fmaps2, ii, jj, num_levels=4):
     return outs
 
 
+def corr_volume_pyramid_pool(fmaps1, fmaps2, ii, jj, slots, pool):
+    """Build the pyramids of the edges (ii[e], jj[e]) straight into slots `slots[e]` of `pool` (a list of
+    [capacity, ht, wd, ht>>l, wd>>l] float16 tensors): C entry point dbaf_corr_volume_pyramid_pool, see
+    dbaf_b200.corr.CorrPool."""
+    _contig(fmaps1=fmaps1, fmaps2=fmaps2, **{f"pool[{l}]": t for l, t in enumerate(pool)})
+    _cuda(torch.float16, fmaps1=fmaps1, fmaps2=fmaps2, **{f"pool[{l}]": t for l, t in enumerate(pool)})
+    n1, C, ht, wd = fmaps1.shape
+    n2 = fmaps2.shape[0]
+    cap = pool[0].shape[0]
+    for l, t in enumerate(pool):
+        if tuple(t.shape) != (cap, ht, wd, ht >> l, wd >> l):
+            raise RuntimeError(f"pool level {l} has the wrong shape")
+    dev = fmaps1.device
+    ii32 = ii.to(device=dev, dtype=torch.int32).contiguous()
+    jj32 = jj.to(device=dev, dtype=torch.int32).contiguous()
+    sl32 = slots.to(device=dev, dtype=torch.int32).contiguous()
+    E = ii32.numel()
+    if jj32.numel() != E or sl32.numel() != E:
+        raise RuntimeError("ii, jj and slots must have the same length")
+    nbytes = lib.dbaf_corr_volume_indexed_workspace_bytes(n1, n2, C, ht, wd)
+    ws = torch.empty(max(1, nbytes), dtype=torch.uint8, device=dev)
+    arr = (c_void_p * len(pool))(*[t.data_ptr() for t in pool])
+    check(lib.dbaf_corr_volume_pyramid_pool(_p(fmaps1), n1, _p(fmaps2), n2, _p(ii32), _p(jj32), _p(sl32), E, cap, C, ht,
+                                            wd, len(pool), arr, _p(ws), nbytes, _stream()),
+          "dbaf_corr_volume_pyramid_pool")
+
+
+def corr_lookup_pyramid_pool(pool, coords, slots, radius=3):
+    """corr_lookup_pyramid over a slot pool: edge e (coords [n,2,h1,w1]) reads volume slots[e] of every level."""
+    _contig(coords=coords, slots=slots, **{f"pool[{i}]": t for i, t in enumerate(pool)})
+    _cuda(torch.float32, coords=coords)
+    _cuda(torch.int32, slots=slots)
+    dt = _corr_dtype(pool[0], "pool")
+    cap, h1, w1, h2, w2 = pool[0].shape
+    n = coords.shape[0]
+    if slots.numel() != n or tuple(coords.shape) != (n, 2, h1, w1):
+        raise RuntimeError("coords must be [n,2,h1,w1] with one slot per edge")
+    rd = 2 * radius + 1
+    out = torch.empty(n, len(pool) * rd * rd, h1, w1, dtype=pool[0].dtype, device=coords.device)
+    arr = (c_void_p * len(pool))(*[t.data_ptr() for t in pool])
+    check(lib.dbaf_corr_lookup_pyramid_pool(arr, len(pool), dt, _p(coords), _p(slots), n, cap, h1, w1, h2, w2,
+                                            int(radius), _p(out), _stream()), "dbaf_corr_lookup_pyramid_pool")
+    return out
+
+
 def corr_lookup_pyramid(pyramid, coords, radius=3):
     """All levels of CorrBlock.__call__ (dbaf/modules/corr.py:40-50) in one launch.
     pyramid[l] [n,h1,w1,h2>>l,w2>>l]; coords [n,2,h1,w1] (level-0 pixels) ->

@@ -128,6 +128,23 @@ int dbaf_corr_volume_pyramid_indexed(const void* fmaps1, int n1, const void* fma
                                      int wd, int levels, void* const* out_host, void* workspace,
                                      size_t workspace_bytes, void* stream);
 
+/* CorrBlock bookkeeping without copies (a "next" row of the scope table).  The reference keeps the pyramids of the
+ * live edges in tensors that it re-creates on every edge change: `cat` on add, boolean-mask indexing on removal
+ * (dbaf/modules/corr.py:52-60, dbaf/covisible_graph.py:131-132,166-167), i.e. the whole multi-GB pyramid is
+ * copied each time.  Here the pyramids live in caller-owned pools of `capacity` volumes per level,
+ * pool_host[l] = [capacity, ht, wd, ht>>l, wd>>l] fp16, and an int32 device array maps edge -> slot:
+ * adding edges fills free slots in place, removing edges only edits the slot array.
+ * dbaf_corr_volume_pyramid_pool: as dbaf_corr_volume_pyramid_indexed, edge e written to slot slots[e] (checked
+ *   against capacity; workspace: dbaf_corr_volume_indexed_workspace_bytes).
+ * dbaf_corr_lookup_pyramid_pool: as dbaf_corr_lookup_pyramid, edge e (coords [n,2,h1,w1]) reads slot slots[e]. */
+int dbaf_corr_volume_pyramid_pool(const void* fmaps1, int n1, const void* fmaps2, int n2, const int32_t* ii,
+                                  const int32_t* jj, const int32_t* slots, int n_edges, int capacity, int C,
+                                  int ht, int wd, int levels, void* const* pool_host, void* workspace,
+                                  size_t workspace_bytes, void* stream);
+int dbaf_corr_lookup_pyramid_pool(const void* const* pool_host, int levels, int dtype, const float* coords,
+                                  const int32_t* slots, int n, int capacity, int h1, int w1, int h2, int w2,
+                                  int radius, void* out, void* stream);
+
 /* ------------------------------------------------------- bundle adjustment ---- */
 
 /* Workspace layout (byte offsets into one caller-allocated device buffer).  The caller owns

@@ -485,3 +485,41 @@ def test_bacore_hessian_gtsam_matches_ba2gtsam(dev, db, oracle, synth):
     core.hessian_gtsam(Hg, vg, A)
     wantH, wantv = oracle.ba2gtsam(H.numpy(), v.numpy(), A)
     assert relerr(Hg.numpy(), wantH) < 1e-12 and relerr(vg.numpy(), wantv) < 1e-12
+
+
+@pytest.mark.parametrize("cfg", ["tiny", "c3", "c4"])
+def test_corr_pool_matches_rebuilt_corrblock(dev, db, synth, cfg):
+    """CorrPool (slot pool + edge->slot table, no copies on edge changes) against a CorrBlock rebuilt from scratch
+    on the surviving edge list after every append / keep: lookups identical bit for bit (the reference's
+    cat / boolean-mask bookkeeping, dbaf/modules/corr.py:52-60)."""
+    from dbaf_b200.corr import CorrBlock, CorrPool
+    w = synth.make_window(cfg, seed=4)
+    N = w["poses"].shape[0]
+    f = torch.from_numpy(synth.make_features(cfg, seed=8, n_frames=N)).to(dev)
+    ht, wd = w["ht"], w["wd"]
+    rng = np.random.default_rng(1)
+    pool = CorrPool(24, ht, wd, device=dev)
+    ii = torch.empty(0, dtype=torch.long, device=dev)
+    jj = torch.empty(0, dtype=torch.long, device=dev)
+    for step in range(6):
+        if step % 2 == 0 or len(pool) == 0:
+            k = int(rng.integers(3, 9))
+            k = min(k, pool.capacity - len(pool))
+            ni = torch.from_numpy(rng.integers(0, N, k)).to(dev)
+            nj = torch.from_numpy(rng.integers(0, N, k)).to(dev)
+            pool.append(f, f, ni, nj)
+            ii, jj = torch.cat([ii, ni]), torch.cat([jj, nj])
+        else:
+            mask = torch.from_numpy(rng.random(len(pool)) > 0.4).to(dev)
+            pool.keep(mask)
+            ii, jj = ii[mask], jj[mask]
+        assert len(pool) == ii.numel()
+        if len(pool) == 0:
+            continue
+        coords = torch.from_numpy(rng.uniform(-4, max(ht, wd) + 4, (1, len(pool), ht, wd, 2)).astype(np.float32)).to(dev)
+        want = CorrBlock.from_frames(f, f, ii, jj)(coords)
+        got = pool(coords)
+        assert got.shape == want.shape
+        assert torch.equal(got.view(torch.int16), want.view(torch.int16)), (cfg, step)
+    with pytest.raises(RuntimeError, match="full"):
+        pool.append(f, f, torch.zeros(30, dtype=torch.long, device=dev), torch.zeros(30, dtype=torch.long, device=dev))
