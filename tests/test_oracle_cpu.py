@@ -328,3 +328,20 @@ def test_projmap_frame_distance_iproj(oracle, synth):
     cnt = oracle.depth_filter(w["poses_gt"], w["disps_gt"], w["intrinsics"], np.array([1, 3]),
                               np.array([0.05, 0.05], np.float32))
     assert cnt.shape == (2, w["ht"], w["wd"]) and cnt.max() <= 6 and cnt.mean() > 0.5
+
+
+def test_ba2gtsam_blockwise(oracle):
+    """oracle.ba2gtsam (BA2GTSAM, dbaf/depth_video.py:20-29) against the block-wise form A^T H_IK A, A^T v_I that the
+    device kernel uses, and its invariants: symmetry is preserved, A = -I leaves H and flips v."""
+    rng = np.random.default_rng(3)
+    P = 5
+    G = rng.normal(0, 1, (6 * P, 6 * P))
+    H, v, A = G @ G.T, rng.normal(0, 1, 6 * P), rng.normal(0, 1, (6, 6))
+    Hg, vg = oracle.ba2gtsam(H, v, A)
+    for I in range(P):
+        assert np.allclose(vg[6 * I:6 * I + 6], A.T @ v[6 * I:6 * I + 6])
+        for K in range(P):
+            assert np.allclose(Hg[6 * I:6 * I + 6, 6 * K:6 * K + 6], A.T @ H[6 * I:6 * I + 6, 6 * K:6 * K + 6] @ A)
+    assert np.allclose(Hg, Hg.T)
+    H2, v2 = oracle.ba2gtsam(H, v, -np.eye(6))
+    assert np.allclose(H2, H) and np.allclose(v2, -v)
