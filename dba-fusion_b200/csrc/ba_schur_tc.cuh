@@ -13,8 +13,8 @@
 //     against the fp32 SIMT kernel and the reference to 1e-4 normwise like every other path).
 // One warp streams 32-pixel slices of the 128 rows from HBM with 16-byte asynchronous copies (four slices =
 // 64 KB in flight per SM); eight transform warps scale them by sqrt(q), split them and store the two operand tiles
-// (Xhi, Xlo; 16 KB each, 128-byte swizzled; both are A and B operand) of a 2-stage ring; one thread issues
-// 12 tcgen05.mma.kind::tf32 (M = N = 128, K = 8) per slice into one of two TMEM accumulators.  The tensor core
+// (Xhi, Xlo; 16 KB each, 128-byte swizzled; both are A and B operand) of a 4-stage ring; one thread issues
+// 12 tcgen05.mma.kind::tf32 (M = N = 128, K = 8) per slice into one of four TMEM accumulators.  The tensor core
 // accumulates with truncation, so each slice starts a fresh accumulator and the producer warps add the
 // finished slices into fp32 registers (round to nearest) while the next loads are in flight.  At the end
 // the sums are subtracted from the dense fp64 H, v with atomics (same addresses as k_schur_smem).
