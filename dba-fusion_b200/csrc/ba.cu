@@ -502,6 +502,51 @@ int pick_pxt(int Kcap, int HW) {
 }
 }  // namespace
 
+namespace {
+// Schur complement of the depth frames [k_lo, k_lo + k_cap): H -= E Q E^T, v -= E Q w from the E, Q, w in the workspace.
+int launch_schur(Ws ws, const int64_t* jj, int E, int t0, int P, int HW, int k_lo, int k_hi, int k_cap, cudaStream_t st) {
+  static bool schur_attr[64] = {};
+  int dev_id = 0;
+  DBAF_CUDA(cudaGetDevice(&dev_id));
+  if (!schur_attr[dev_id & 63]) {   // once per device: the attribute call costs ~10 us of host time
+    DBAF_CUDA(cudaFuncSetAttribute(k_schur_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
+    schur_attr[dev_id & 63] = true;
+  }
+  // dense graphs (global BA: ~20 out-edges per frame) go to the tensor-core kernel, whose cost does not grow
+  // with the square of the row count; dbaf_set_option("schur_impl", "simt") keeps everything on the fp32 SIMT kernels
+  const bool simt_only = options().schur_simt != 0;
+  // mean out-degree >= 7, i.e. frames with >= 8 row blocks exist; whole 32-pixel slices for the 16-byte copies
+  const bool use_tc = !simt_only && E >= 7 * k_cap && HW % 32 == 0;
+  const int tc_min_m = 8;
+  if (use_tc) {
+    static bool tc_attr[64] = {};
+    if (!tc_attr[dev_id & 63]) {
+      DBAF_CUDA(cudaFuncSetAttribute(k_schur_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStcSmemBytes));
+      tc_attr[dev_id & 63] = true;
+    }
+    // one CTA per frame when there are enough frames to fill the machine, else split the pixels
+    int splits = std::max(1, std::min((2 * 148 + k_cap - 1) / k_cap, (HW + 255) / 256));
+    const int St = (((HW + splits - 1) / splits) + 31) & ~31;
+    splits = (HW + St - 1) / St;
+    k_schur_tc<<<dim3(splits, k_cap), kStcThreads, kStcSmemBytes, st>>>(jj, t0, P, HW, St, tc_min_m, k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_schur_tc");
+  }
+  const int S = 256;
+  dim3 sgrid((HW + S - 1) / S, k_cap);
+  k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, use_tc ? tc_min_m : 1,
+                                                         use_tc ? kStcMaxM : 0, ws);
+  DBAF_LAUNCH_CHECK("k_schur_smem");
+  if (E + 1 > kSchurMaxRows) {
+    // a depth frame can only have more than kSchurMaxRows rows if the graph has that many edges
+    const int tile_px = 1024;
+    dim3 ogrid((HW + tile_px - 1) / tile_px, k_cap);
+    k_schur<<<ogrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, kSchurMaxRows + 1, k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_schur");
+  }
+  return DBAF_OK;
+}
+}  // namespace
+
 extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
                                  const float* intrinsics, const float* disps_sens,
                                  const float* targets, const float* weights, const float* eta,
@@ -538,47 +583,24 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
 #undef DBAF_LIN
   DBAF_LAUNCH_CHECK("k_linearize2");
   if (motion_only == 0 && P > 0) {
-    static bool schur_attr[64] = {};
-    int dev_id = 0;
-    DBAF_CUDA(cudaGetDevice(&dev_id));
-    if (!schur_attr[dev_id & 63]) {   // once per device: the attribute call costs ~10 us of host time
-      DBAF_CUDA(cudaFuncSetAttribute(k_schur_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSchurSmemBytes));
-      schur_attr[dev_id & 63] = true;
-    }
-    // dense graphs (global BA: ~20 out-edges per frame) go to the tensor-core kernel, whose cost does not grow
-    // with the square of the row count; DBAF_SCHUR_IMPL=simt keeps everything on the fp32 SIMT kernels
-    const char* schur_impl = std::getenv("DBAF_SCHUR_IMPL");
-    const bool simt_only = schur_impl != nullptr && std::strcmp(schur_impl, "simt") == 0;
-    // mean out-degree >= 7, i.e. frames with >= 8 row blocks exist; whole 32-pixel slices for the 16-byte copies
-    const bool use_tc = !simt_only && E >= 7 * k_cap && HW % 32 == 0;
-    const int tc_min_m = 8;
-    if (use_tc) {
-      static bool tc_attr[64] = {};
-      if (!tc_attr[dev_id & 63]) {
-        DBAF_CUDA(cudaFuncSetAttribute(k_schur_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStcSmemBytes));
-        tc_attr[dev_id & 63] = true;
-      }
-      // one CTA per frame when there are enough frames to fill the machine, else split the pixels
-      int splits = std::max(1, std::min((2 * 148 + k_cap - 1) / k_cap, (HW + 255) / 256));
-      const int St = (((HW + splits - 1) / splits) + 31) & ~31;
-      splits = (HW + St - 1) / St;
-      k_schur_tc<<<dim3(splits, k_cap), kStcThreads, kStcSmemBytes, st>>>(jj, t0, P, HW, St, tc_min_m, k_lo, k_hi, ws);
-      DBAF_LAUNCH_CHECK("k_schur_tc");
-    }
-    const int S = 256;
-    dim3 sgrid((HW + S - 1) / S, k_cap);
-    k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, use_tc ? tc_min_m : 1,
-                                                           use_tc ? kStcMaxM : 0, ws);
-    DBAF_LAUNCH_CHECK("k_schur_smem");
-    if (E + 1 > kSchurMaxRows) {
-      // a depth frame can only have more than kSchurMaxRows rows if the graph has that many edges
-      const int tile_px = 1024;
-      dim3 ogrid((HW + tile_px - 1) / tile_px, k_cap);
-      k_schur<<<ogrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, kSchurMaxRows + 1, k_lo, k_hi, ws);
-      DBAF_LAUNCH_CHECK("k_schur");
-    }
+    if (int rc = launch_schur(ws, jj, E, t0, P, HW, k_lo, k_hi, k_cap, st)) return rc;
   }
   return DBAF_OK;
+}
+
+// The Schur stage of dbaf_ba_linearize on its own: H -= E Q E^T, v -= E Q w from whatever E, Q, w the workspace
+// holds (diagnostics and tests: lets a caller feed the Schur kernels with chosen blocks).
+extern "C" int dbaf_ba_schur(void* workspace, const int64_t* jj, int E, int N, int t0, int t1, int ht, int wd,
+                             int k_lo, int k_hi, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
+  dbaf_ba_layout L;
+  fill_layout(N, E, t0, t1, ht, wd, &L);
+  Ws ws = view(workspace, L);
+  if (k_lo < 0) k_lo = 0;
+  const int k_cap = (k_hi >= 0 ? std::min(k_hi, ws.Kcap) : ws.Kcap) - k_lo;
+  if (k_cap <= 0 || t1 == t0) return DBAF_OK;
+  return launch_schur(ws, jj, E, t0, t1 - t0, ht * wd, k_lo, k_hi, k_cap, (cudaStream_t)stream);
 }
 
 namespace {
@@ -615,8 +637,7 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       band_attr[dev_id & 63] = true;
     }
     BandPlan plan{};
-    const char* band_impl = std::getenv("DBAF_BAND_IMPL");       // "single" keeps the one-CTA sweep (tests)
-    const bool single = band_impl != nullptr && std::strcmp(band_impl, "single") == 0;
+    const bool single = options().band_single != 0;              // the one-CTA sweep (tests)
     if (!single && P >= kBandTwistMinP && P >= 3 * B + 2) {
       // two sweeps meeting at the separator [m, m+B)
       const int m = (P - B) / 2;
@@ -629,9 +650,8 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       plan.part[0] = BandPart{0, P, P, 0};
       plan.part[1] = plan.part[0];
     }
-    // B <= 20: the sweep that keeps the window in registers; DBAF_BAND_SWEEP=smem keeps the shared-memory window
-    const char* sweep_impl = std::getenv("DBAF_BAND_SWEEP");
-    const bool smem_sweep = B > kBandRegMaxB || (sweep_impl != nullptr && std::strcmp(sweep_impl, "smem") == 0);
+    // B <= 20: the sweep that keeps the window in registers; option band_sweep=smem keeps the shared-memory window
+    const bool smem_sweep = B > kBandRegMaxB || options().band_smem != 0;
     if (smem_sweep) {
       k_solve_banded<<<plan.twisted ? 2 : 1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
       DBAF_LAUNCH_CHECK("k_solve_banded");
@@ -829,7 +849,7 @@ extern "C" int dbaf_ba_host(void* workspace, void* staging, size_t staging_bytes
                             const float* intrinsics_h, const float* disps_sens_h, const float* targets_h,
                             const float* weights_h, const float* eta_h, int eta_rows, const int64_t* ii_h,
                             const int64_t* jj_h, int E, int N, int t0, int t1, int ht, int wd, int iterations,
-                            float lm, float ep, int motion_only, float* dx_out_h, void* stream) {
+                            float lm, float ep, int motion_only, float* dx_out_h, int32_t* info_out_h, void* stream) {
   DBAF_REQUIRE(workspace != nullptr && staging != nullptr, "null workspace or staging buffer");
   if (int rc = check_dims(N, E, t0, t1, ht, wd)) return rc;
   DBAF_REQUIRE(poses_h && disps_h && intrinsics_h && disps_sens_h && ii_h && jj_h && (E == 0 || (targets_h && weights_h)),
@@ -866,6 +886,8 @@ extern "C" int dbaf_ba_host(void* workspace, void* staging, size_t staging_bytes
     if (P > 0) DBAF_CUDA(cudaMemcpyAsync(poses_h + (size_t)t0 * 7, poses_d + (size_t)t0 * 7, (size_t)P * 7 * 4, cudaMemcpyDeviceToHost, st));
     if (!motion_only) DBAF_CUDA(cudaMemcpyAsync(disps_h, disps_d, (size_t)N * HW * 4, cudaMemcpyDeviceToHost, st));
     if (dx_out_h && P > 0) DBAF_CUDA(cudaMemcpyAsync(dx_out_h, dx_d, (size_t)P * 6 * 4, cudaMemcpyDeviceToHost, st));
+    // the status words sit at the start of the workspace (dbaf_ba_layout.info == 0)
+    if (info_out_h) DBAF_CUDA(cudaMemcpyAsync(info_out_h, workspace, 16 * sizeof(int32_t), cudaMemcpyDeviceToHost, st));
   }
   return DBAF_OK;
 }

@@ -391,7 +391,9 @@ k_backsub_fused(const int64_t* __restrict__ jj, const float* __restrict__ dx, fl
       }
     }
   }
-  if (live) {
+  // eta with a row count that is neither 1 nor K (info[3], raised by the linearisation): the reference fails with
+  // a broadcast error there; here nothing is written, so that dz_out sized from the caller's row count is safe
+  if (live && ws.info[3] == 0) {
     const float dz = qv * (wv - acc);
     if (dz_out) dz_out[(size_t)k * HW + p] = dz;
     if (disps) disps[(size_t)f * HW + p] += dz;

@@ -36,6 +36,21 @@ int cuda_fail(cudaError_t e, const char* what);
     if (e__ != cudaSuccess) return ::dbaf::cuda_fail(e__, #call);            \
   } while (0)
 
+// ---------------------------------------------------------------- options ----
+// Kernel-selection switches (test and profiling aids).  Read once from the environment when the
+// library is first used (DBAF_SCHUR_IMPL, DBAF_BAND_IMPL, DBAF_BAND_SWEEP, DBAF_VOLUME_IMPL,
+// DBAF_BAND_DOMAINS, DBAF_STRICT), changed afterwards only through dbaf_set_option().
+struct Options {
+  int schur_simt;      // 1: keep the Schur complement on the fp32 SIMT kernels
+  int band_single;     // 1: one-CTA banded sweep (no twisted / domain-decomposed factorisation)
+  int band_twisted;    // 1: two-CTA twisted factorisation instead of the domain decomposition
+  int band_smem;       // 1: banded sweep with the window in shared memory
+  int band_domains;    // > 0: number of domains of the decomposed banded solve
+  int volume_simt;     // 1: SIMT cross-check kernels for the correlation volume
+  int eij_recompute;   // -1: automatic, 0: always materialise Eij, 1: always recompute it
+};
+Options& options();
+
 constexpr float kMinDepth = 0.25f;   // MIN_DEPTH, src/droid_kernels.cu:29
 
 // ------------------------------------------------------------------ SE3 ----

@@ -3,6 +3,9 @@
 // pixel index fastest, one thread per pixel, so every global access is a coalesced 128 B line.
 #include "common.cuh"
 
+#include <cstdlib>
+#include <cstring>
+
 namespace dbaf {
 
 static thread_local std::string g_error;
@@ -12,6 +15,30 @@ void set_error(const std::string& msg) { g_error = msg; }
 int cuda_fail(cudaError_t e, const char* what) {
   g_error = std::string(what) + ": " + cudaGetErrorString(e);
   return DBAF_ECUDA;
+}
+
+namespace {
+bool env_is(const char* name, const char* value) {
+  const char* v = std::getenv(name);
+  return v != nullptr && std::strcmp(v, value) == 0;
+}
+}  // namespace
+
+Options& options() {
+  static Options o = [] {
+    Options x{};
+    x.schur_simt = env_is("DBAF_SCHUR_IMPL", "simt");
+    x.band_single = env_is("DBAF_BAND_IMPL", "single");
+    x.band_twisted = env_is("DBAF_BAND_IMPL", "twisted");
+    x.band_smem = env_is("DBAF_BAND_SWEEP", "smem");
+    x.volume_simt = env_is("DBAF_VOLUME_IMPL", "simt");
+    const char* d = std::getenv("DBAF_BAND_DOMAINS");
+    x.band_domains = d ? std::atoi(d) : 0;
+    const char* r = std::getenv("DBAF_EIJ_RECOMPUTE");
+    x.eij_recompute = r ? std::atoi(r) : -1;
+    return x;
+  }();
+  return o;
 }
 
 namespace {
@@ -257,5 +284,34 @@ extern "C" int dbaf_depth_filter(const float* poses, const float* disps, const f
   dim3 grid((HW + kThreads - 1) / kThreads, M);
   k_depth_filter<<<grid, kThreads, 0, (cudaStream_t)stream>>>(poses, disps, intrinsics, ix, thresh, N, ht, wd, counter);
   DBAF_LAUNCH_CHECK("k_depth_filter");
+  return DBAF_OK;
+}
+
+// ------------------------------------------------------------------ options ----
+extern "C" int dbaf_set_option(const char* key, const char* value) {
+  DBAF_REQUIRE(key != nullptr && value != nullptr, "null key or value");
+  Options& o = options();
+  const std::string k(key), v(value);
+  if (k == "schur_impl") {
+    DBAF_REQUIRE(v == "auto" || v == "simt", "schur_impl: auto | simt");
+    o.schur_simt = v == "simt";
+  } else if (k == "band_impl") {
+    DBAF_REQUIRE(v == "auto" || v == "single" || v == "twisted", "band_impl: auto | single | twisted");
+    o.band_single = v == "single";
+    o.band_twisted = v == "twisted";
+  } else if (k == "band_sweep") {
+    DBAF_REQUIRE(v == "auto" || v == "smem", "band_sweep: auto | smem");
+    o.band_smem = v == "smem";
+  } else if (k == "band_domains") {
+    o.band_domains = std::atoi(value);
+  } else if (k == "volume_impl") {
+    DBAF_REQUIRE(v == "auto" || v == "simt", "volume_impl: auto | simt");
+    o.volume_simt = v == "simt";
+  } else if (k == "eij") {
+    DBAF_REQUIRE(v == "auto" || v == "store" || v == "recompute", "eij: auto | store | recompute");
+    o.eij_recompute = v == "auto" ? -1 : v == "recompute";
+  } else {
+    DBAF_REQUIRE(false, "unknown option '" + k + "'");
+  }
   return DBAF_OK;
 }

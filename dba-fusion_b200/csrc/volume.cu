@@ -155,10 +155,9 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
   if (n_out < 0) n_out = n;
   __half* outs[4] = {nullptr, nullptr, nullptr, nullptr};
   for (int l = 0; l < levels; ++l) outs[l] = static_cast<__half*>(out_host[l]);
-  // DBAF_VOLUME_IMPL=simt forces the cross-check kernels (tests use it to validate the
+  // option volume_impl=simt forces the cross-check kernels (tests use it to validate the
   // tensor-core path against an independent implementation inside the same library).
-  const char* impl = std::getenv("DBAF_VOLUME_IMPL");
-  const bool force_simt = impl && std::strcmp(impl, "simt") == 0;
+  const bool force_simt = options().volume_simt != 0;
   int done = 0;
   if (!force_simt) {
     const int rc = corr_volume_tc(f1, n1, f2, n2, idx1, idx2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st,

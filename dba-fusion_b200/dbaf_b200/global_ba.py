@@ -135,6 +135,13 @@ class GlobalBA:
         dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=self.group)
         sys_flat.index_copy_(0, idx, packed)
 
+    def launches_per_iteration(self):
+        """Kernels of this library enqueued by one `iterate` (k_linearize2, k_schur_tc, k_schur_smem, k_schur when a
+        frame has > 96 rows, the banded solve's kernels, k_backsub_fused)."""
+        import droid_backends as db
+        n_solve = db.banded_solve_launches(self.P, self.band) if hasattr(db, "banded_solve_launches") else 3
+        return 3 + n_solve + 1
+
     def run(self, iterations, lm=1e-4, ep=0.1):
         for _ in range(iterations):
             self.iterate(lm, ep)
@@ -153,9 +160,117 @@ class GlobalBA:
         disps.copy_(torch.where(touched[:, None, None] > 0, contrib, disps))
 
 
+# --------------------------------------------------------------------------- host-resident windows
+def _runs(ids):
+    """Sorted integer ids -> list of (first, count) runs of consecutive values."""
+    ids = np.asarray(ids, np.int64)
+    if ids.size == 0:
+        return []
+    cut = np.nonzero(np.diff(ids) != 1)[0] + 1
+    return [(int(r[0]), int(len(r))) for r in np.split(ids, cut)]
+
+
+class HostWindow:
+    """A window that lives in pinned HOST memory (a backend thread that assembles targets / weights on the CPU or
+    receives them over IPC), iterated on this rank's GPU: `GlobalBA.iterate_host` uploads what this rank needs
+    (all poses and the edge lists, its own depth frames' disparities / eta / sensor depths, its own edges' targets
+    and weights), runs one Gauss-Newton iteration, and reads back the pose update, the window poses and its own
+    disparities.  The uploads of targets / weights run on a copy stream in `chunks` pieces of depth frames and the
+    linearisation of a piece starts as soon as it has landed."""
+
+    KEYS = ("poses", "disps", "disps_sens", "targets", "weights", "eta", "ii", "jj", "intrinsics")
+
+    def __init__(self, win):
+        self.h = {k: torch.from_numpy(np.ascontiguousarray(win[k])).pin_memory() for k in self.KEYS}
+        self.t0, self.t1 = int(win["t0"]), int(win["t1"])
+        P = self.t1 - self.t0
+        self.dx = torch.zeros(max(P, 1), 6, dtype=torch.float32).pin_memory()
+
+
+def plan_host_chunks(ii, kx, k_lo, k_hi, chunks):
+    """Split the depth-frame positions [k_lo,k_hi) into `chunks` pieces; for each piece the runs of consecutive
+    frame ids (disps / sens rows), of eta rows, and of edge ids whose source frame lies in the piece."""
+    ii = np.asarray(ii, np.int64)
+    bounds = np.linspace(k_lo, k_hi, max(1, chunks) + 1).round().astype(int)
+    out = []
+    for a, b in zip(bounds[:-1], bounds[1:]):
+        if b <= a:
+            continue
+        frames = kx[a:b]
+        edges = np.nonzero(np.isin(ii, frames))[0]
+        out.append(dict(k=(int(a), int(b)), frame_runs=_runs(frames), eta_run=(int(a), int(b - a)),
+                        edge_runs=_runs(edges), n_edges=int(len(edges))))
+    return out
+
+
+def iterate_host(gba, host, dev, plan, copy_stream, lm=1e-4, ep=0.1, alpha=0.05):
+    """One global-BA iteration from / to pinned host memory on this rank (see HostWindow).  `dev` is the dict of
+    device tensors the engine was built on.  Returns (h2d_bytes, d2h_bytes) of this rank."""
+    eng, h = gba.engine, host.h
+    main = torch.cuda.current_stream()
+    h2d = d2h = 0
+    ev_small = torch.cuda.Event()
+    copy_stream.wait_stream(main)
+    with torch.cuda.stream(copy_stream):
+        for k in ("poses", "intrinsics", "ii", "jj"):
+            dev[k].copy_(h[k], non_blocking=True)
+            h2d += h[k].numel() * h[k].element_size()
+        ev_small.record(copy_stream)
+        events = []
+        for ch in plan:
+            for f0, cnt in ch["frame_runs"]:
+                for k in ("disps", "disps_sens"):
+                    dev[k][f0:f0 + cnt].copy_(h[k][f0:f0 + cnt], non_blocking=True)
+                    h2d += cnt * h[k][0].numel() * 4
+            a, cnt = ch["eta_run"]
+            if h["eta"].shape[0] > 1:
+                dev["eta"][a:a + cnt].copy_(h["eta"][a:a + cnt], non_blocking=True)
+                h2d += cnt * h["eta"][0].numel() * 4
+            for e0, cnt in ch["edge_runs"]:
+                for k in ("targets", "weights"):
+                    dev[k][e0:e0 + cnt].copy_(h[k][e0:e0 + cnt], non_blocking=True)
+                    h2d += cnt * h[k][0].numel() * 4
+            ev = torch.cuda.Event()
+            ev.record(copy_stream)
+            events.append(ev)
+    main.wait_event(ev_small)
+    eng.w.prepare()                                    # the edge lists were just uploaded: rebuild the tables
+    for n, (ch, ev) in enumerate(zip(plan, events)):
+        main.wait_event(ev)
+        eng.w.linearize(alpha, zero_first=(n == 0), k_lo=ch["k"][0], k_hi=ch["k"][1])
+    if not plan:
+        eng.w.Hv().zero_()
+    if gba.world > 1:
+        gba.reduce_system(eng.system())
+    eng.solve(lm, ep, gba.band)
+    eng.w.retract(update_poses=True, update_disps=True, k_lo=gba.k_lo, k_hi=gba.k_hi, want_dx=False, want_dz=False)
+    P = host.t1 - host.t0
+    h["poses"][host.t0:host.t1].copy_(dev["poses"][host.t0:host.t1], non_blocking=True)
+    host.dx[:P].copy_(eng.w.dx(), non_blocking=True)
+    d2h += P * 7 * 4 + P * 6 * 4
+    for ch in plan:
+        for f0, cnt in ch["frame_runs"]:
+            h["disps"][f0:f0 + cnt].copy_(dev["disps"][f0:f0 + cnt], non_blocking=True)
+            d2h += cnt * h["disps"][0].numel() * 4
+    main.synchronize()
+    return h2d, d2h
+
+
 # --------------------------------------------------------------------------- benchmark arm
+C5_WORKLOAD = ("c5 global BA: 1000-frame banded keyframe graph (999 window poses, 19890 edges, +-10 neighbours), "
+               "64x64 disparity maps, 1 GN iteration per step")
+C5_L2 = "512 MB read+write between steps (the 1.4 GB of inputs are also larger than the 126 MB L2)"
+
+
+def c5_config():
+    """`config` of the bench line; the reference arm prints the identical dict."""
+    return dict(workload=C5_WORKLOAD, l2=C5_L2)
+
+
 def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
-    """bench.py arm for N > 1 (and --workload c5): configs[4], 1000 keyframes, +-10 neighbours."""
+    """The bench line of record at every N: BASELINE.json configs[4] (1000 keyframes, +-10 neighbours), the depth
+    frames sharded over the `world` ranks.  `value` = device time of one Gauss-Newton iteration with all inputs
+    resident in HBM; `e2e` = the same iteration from / to pinned host memory (HostWindow)."""
     from . import synth
     cfg = "c5"
     ht, wd, P, E, _ = synth.CONFIGS[cfg]
@@ -197,14 +312,16 @@ def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
     step_ms = statistics.mean(ms)
     # stage breakdown on this rank
     stages = {}
-    for name, fn in (("linearize+schur", lambda: eng.linearize(0.05, gba.k_lo, gba.k_hi)),
+    for name, fn in (("linearize", lambda: eng.w.linearize(0.05, motion_only=2, zero_first=True, k_lo=gba.k_lo, k_hi=gba.k_hi)),
+                     ("linearize+schur", lambda: eng.linearize(0.05, gba.k_lo, gba.k_hi)),
                      ("allreduce", (lambda: gba.reduce_system(eng.system())) if world > 1 else (lambda: None)),
                      ("solve", lambda: eng.solve(1e-4, 0.1, gba.band)),
                      ("retract", lambda: eng.retract(gba.k_lo, gba.k_hi))):
         ts = []
         for _ in range(3):
             reset()
-            torch.cuda.synchronize()
+            flush()
+            barrier()
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()
@@ -212,22 +329,64 @@ def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
             b.synchronize()
             ts.append(a.elapsed_time(b))
         stages[name] = min(ts)
+
+    # ---- N ranks == 1 rank: one iteration from the initial state, sharded, against the same iteration done by
+    #      this rank alone over all depth frames (every rank holds the whole window in this benchmark)
+    reset()
+    gba.iterate()
+    dx_n = eng.w.dx().clone()
+    poses_n, disps_n = t["poses"].clone(), t["disps"].clone()
+    gba.gather_disps(disps_n)
+    reset()
+    eng.linearize(0.05, 0, -1)
+    eng.solve(1e-4, 0.1, gba.band)
+    eng.retract(0, -1)
+    rel = lambda a, b: float((a.double() - b.double()).abs().max() / b.double().abs().max().clamp(min=1e-300))
+    par = torch.tensor([rel(dx_n, eng.w.dx()), rel(poses_n, t["poses"]), rel(disps_n, t["disps"])],
+                       dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(par, op=dist.ReduceOp.MAX)
+    parity = dict(dx_rel=float(par[0]), poses_rel=float(par[1]), disps_rel=float(par[2]), bound=1e-6,
+                  what="one iteration sharded over the ranks vs the same iteration on one rank, max over ranks")
+
+    # ---- end to end from pinned host memory
+    host = HostWindow(win)
+    plan = plan_host_chunks(win["ii"], gba.kx, gba.k_lo, gba.k_hi, 6)
+    cs = torch.cuda.Stream(device=dev)
+    hp0, hd0 = host.h["poses"].clone(), host.h["disps"].clone()
+    e2e_ms, h2d, d2h = [], 0, 0
+    for it in range(3 + max(3, min(args.steps, 10))):
+        host.h["poses"].copy_(hp0)
+        host.h["disps"].copy_(hd0)
+        flush()
+        barrier()
+        a = time.perf_counter()
+        h2d, d2h = iterate_host(gba, host, t, plan, cs)
+        if it >= 3:
+            e2e_ms.append((time.perf_counter() - a) * 1e3)
+    e2e = torch.tensor([statistics.mean(e2e_ms), float(h2d), float(d2h)], dtype=torch.float64, device=dev)
+    if world > 1:
+        e2e_max = e2e.clone()
+        dist.all_reduce(e2e_max, op=dist.ReduceOp.MAX)
+        dist.all_reduce(e2e, op=dist.ReduceOp.SUM)
+        e2e[0] = e2e_max[0]
     HW = ht * wd
     K = len(gba.kx)
     lin_bytes = n_edges * HW * 20 + K * HW * 12
-    roof = dict(bound="hbm", kernel="k_linearize2 + k_schur_tc (rank 0 shard)", unit="GB/s", peak=peaks["hbm"],
+    roof = dict(bound="hbm", kernel="k_linearize2 + Schur kernels (this rank's shard)", unit="GB/s", peak=peaks["hbm"],
                 achieved=lin_bytes / world / (stages["linearize+schur"] * 1e-3) / 1e9, traffic=None,
                 peak_source=peaks["src"], algorithmic_bytes=lin_bytes // world, ms=stages["linearize+schur"])
     roof["frac"] = roof["achieved"] / roof["peak"]
     line = dict(metric="dense-BA ms/iter", value=step_ms, unit="ms/iter", n_gpus=world, steps=args.steps,
                 warmup=max(3, args.warmup), ms_per_step=step_ms, higher_is_better=False, scaling="strong",
-                vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=f"c5 global BA: {P} keyframes, {n_edges} edges (+-10 neighbours), {ht}x{wd} "
-                                     f"disparity maps, 1 GN iteration per step, depth frames sharded over {world} GPU(s)",
-                            l2="512 MB read+write between steps", band_blocks=gba.band,
-                            shard=[list(r) for r in gba.ranges]),
-                roofline=roof, stages_ms=stages,
-                e2e=dict(value=step_ms, unit="ms/iter", h2d_bytes_per_step=0, d2h_bytes_per_step=0,
-                         note="global BA state lives on the GPUs between iterations; no host traffic per step"),
-                gpu_launches=args.steps * 9)   # linearize2, schur_tc, schur_smem, schur, 3 x banded solve, memset-free retract
+                vs_baseline=None, dtype="f32", data="synthetic", config=c5_config(),
+                shard=dict(depth_frame_ranges=[list(r) for r in gba.ranges], band_blocks=gba.band,
+                           solve=eng.solve_kind() if hasattr(eng, "solve_kind") else None),
+                roofline=roof, stages_ms=stages, parity_vs_1gpu=parity,
+                e2e=dict(value=float(e2e[0]), unit="ms/iter", h2d_bytes_per_step=int(e2e[1]),
+                         d2h_bytes_per_step=int(e2e[2]), ms_per_step=float(e2e[0]),
+                         note="one iteration from / to pinned host memory (global_ba.iterate_host): every rank uploads "
+                              "the poses, the edge lists and its own depth frames' inputs, 6 chunks overlapped with "
+                              "the linearisation; bytes are summed over the ranks, time is the max"),
+                gpu_launches=args.steps * gba.launches_per_iteration())
     return line, clk

@@ -8,21 +8,48 @@ dbaf/ needs to change (callers: dbaf/modules/corr.py:12,19,79,87, dbaf/depth_vid
 Tensors are torch CUDA tensors; torch only provides memory, the current stream and
 (for global BA) the process group.  All kernels are enqueued on the current stream.
 Extras beyond the reference surface: corr_volume_pyramid, corr_lookup_pyramid, ba_tables,
-ba_info.
+ba_info, set_option, set_strict.
+
+Status words.  The kernels never fault on a bad edge index or an `eta` whose row count does not match the
+number of depth frames; they raise a flag on the device instead (int32 info[2], info[3]) and skip the work
+that depends on it.  Calls that synchronise with the device anyway (BACore.hessian / hessian_gtsam, ba_extend,
+ba_host) read the flags and raise RuntimeError like the reference would; the asynchronous `ba` does so only in
+strict mode (set_strict(True) or DBAF_STRICT=1), otherwise poll ba_info().
 """
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
 from ._lib import BaLayout, c_void_p, check, lib
 
-__all__ = ["ba", "ba_extend", "frame_distance", "projmap", "depth_filter", "iproj",
+__all__ = ["set_option", "set_strict", "ba", "ba_extend", "frame_distance", "projmap", "depth_filter", "iproj",
            "altcorr_forward", "altcorr_backward", "corr_index_forward", "corr_index_backward",
            "BACore", "corr_volume_pyramid", "corr_lookup_pyramid", "ba_tables", "ba_info"]
 
 DBAF_F16, DBAF_F32 = 0, 1
+_strict = os.environ.get("DBAF_STRICT", "0") not in ("", "0")
+
+
+def set_option(key, value):
+    """dbaf_set_option: kernel-selection switches for tests and profiling (see include/dbaf_b200.h)."""
+    check(lib.dbaf_set_option(str(key).encode(), str(value).encode()), "dbaf_set_option")
+
+
+def set_strict(on=True):
+    """In strict mode `ba` synchronises after the call and raises on a bad edge index or an eta/K mismatch."""
+    global _strict
+    _strict = bool(on)
+
+
+def _raise_on_flags(info, what):
+    if int(info[2]):
+        raise RuntimeError(f"{what}: an edge index in ii/jj lies outside [0, n_frames)")
+    if int(info[3]):
+        raise RuntimeError(f"{what}: eta has a row count that is neither 1 nor the number of depth frames "
+                           f"K = {int(info[0])} (len(unique(cat(arange(t0,t1), ii))))")
 
 
 def _contig(**named):
@@ -80,8 +107,31 @@ def _eta_rows(eta, ii, t0, t1, HW):
         # a single row broadcasts over all K depth frames; K then has to be counted
         K = int(torch.unique(torch.cat([torch.arange(t0, t1, device=ii.device), ii])).numel())
     else:
+        # the reference demands rows == K (broadcast error otherwise, src/droid_kernels.cu:1475); the device
+        # verifies it (info[3]).  dz is always allocated with Kcap rows, so a wrong count cannot write out of bounds
         K = rows
     return eta, rows, K
+
+
+# Workspaces are recycled between calls: `ba` is called many times per keyframe on windows of the same shape.  A
+# workspace is only handed out again for the same device, stream and size, and at most two are kept.
+_ws_pool = {}
+
+
+def _take_ws(nbytes, device):
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream, int(nbytes))
+    lst = _ws_pool.get(key)
+    if lst:
+        return lst.pop(), key
+    return torch.empty(nbytes, dtype=torch.uint8, device=device), key
+
+
+def _give_ws(key, t):
+    if key not in _ws_pool:
+        _ws_pool.clear()                   # a new window shape: drop the old one's workspaces
+    lst = _ws_pool.setdefault(key, [])
+    if len(lst) < 2 and all(x is not t for x in lst):
+        lst.append(t)
 
 
 class _Window:
@@ -98,8 +148,16 @@ class _Window:
         else:
             self.eta, self.eta_rows, self.K = eta, max(1, eta.numel() // self.HW), 0
         self.L = _layout(self.N, self.E, self.t0, self.t1, self.ht, self.wd)
-        self.ws = torch.empty(self.L.total_bytes, dtype=torch.uint8, device=poses.device)
+        self.ws, self._ws_key = _take_ws(self.L.total_bytes, poses.device)
         self.n = 6 * self.P
+        self._pin = None
+
+    def release(self):
+        """Return the workspace to the pool (the tensor stays referenced here, so ba_info() keeps working until
+        the next call of the same shape overwrites it)."""
+        if self._ws_key is not None:
+            _give_ws(self._ws_key, self.ws)
+            self._ws_key = None
 
     # views into the workspace ------------------------------------------------
     def _view(self, off, count, dtype):
@@ -122,6 +180,18 @@ class _Window:
     def info(self):
         return self._view(self.L.info, 16, torch.int32)
 
+    def export_host(self, src=None):
+        """H|v (or `src`, a float64 device tensor of the same size) and the status words -> pinned host memory
+        with one stream synchronisation.  Returns the float64 host tensor; info lands in self._info_host."""
+        n2 = self.n * self.n + self.n
+        if getattr(self, "_pin", None) is None:
+            self._pin = torch.empty(n2, dtype=torch.float64).pin_memory()
+            self._info_host = torch.zeros(16, dtype=torch.int32).pin_memory()
+        self._pin.copy_(self.Hv() if src is None else src, non_blocking=True)
+        self._info_host.copy_(self.info(), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return self._pin
+
     # stages ------------------------------------------------------------------
     def prepare(self):
         poses, disps, intr, sens, tg, wt, ii, jj = self.args
@@ -135,12 +205,12 @@ class _Window:
                                     self.t1, self.ht, self.wd, float(alpha), int(motion_only),
                                     int(zero_first), int(k_lo), int(k_hi), _stream()), "dbaf_ba_linearize")
 
-    def solve(self, lm, ep, prior=None, band=0):
+    def solve(self, lm, ep, prior=None, band=0, prior_shape=None):
         if band and prior is None:
             check(lib.dbaf_ba_solve_banded(_p(self.ws), self.t0, self.t1, float(lm), float(ep), int(band),
                                            _stream()), "dbaf_ba_solve_banded")
             return
-        pr, pc = (prior.shape if prior is not None else (0, 0))
+        pr, pc = (0, 0) if prior is None else (prior_shape if prior_shape is not None else prior.shape)
         check(lib.dbaf_ba_solve(_p(self.ws), self.t0, self.t1, float(lm), float(ep), _p(prior),
                                 int(pr), int(pc), _stream()), "dbaf_ba_solve")
 
@@ -148,13 +218,22 @@ class _Window:
                 want_dx=True, want_dz=True):
         poses, disps, intr, sens, tg, wt, ii, jj = self.args
         dx_out = torch.empty(self.P, 6, dtype=torch.float32, device=poses.device) if want_dx else None
-        dz_out = (torch.empty(self.K, self.HW, dtype=torch.float32, device=poses.device)
+        dz_out = (torch.empty(max(self.K, int(self.L.Kcap)), self.HW, dtype=torch.float32, device=poses.device)
                   if (want_dz and update_disps) else None)
         check(lib.dbaf_ba_retract(_p(self.ws), _p(poses), _p(disps), _p(dx_in), _p(ii), _p(jj), self.E,
                                   self.N, self.t0, self.t1, self.ht, self.wd, int(update_poses),
                                   int(update_disps), int(k_lo), int(k_hi), _p(dx_out), _p(dz_out),
                                   _stream()), "dbaf_ba_retract")
-        return dx_out, dz_out
+        return dx_out, (dz_out[:self.K] if dz_out is not None else None)
+
+    def schur(self, k_lo=0, k_hi=-1):
+        """dbaf_ba_schur: the Schur stage alone, on the E, Q, w the workspace holds."""
+        jj = self.args[7]
+        check(lib.dbaf_ba_schur(_p(self.ws), _p(jj), self.E, self.N, self.t0, self.t1, self.ht, self.wd,
+                                int(k_lo), int(k_hi), _stream()), "dbaf_ba_schur")
+
+    def check_flags(self, what, synced=False):
+        _raise_on_flags(self._info_host if synced else self.info().cpu(), what)
 
 
 _last_window = None
@@ -181,12 +260,16 @@ def ba(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj,
     if iterations <= 0:
         return [None, None]
     dx = torch.empty(w.P, 6, dtype=torch.float32, device=poses.device)
-    dz = None if motion_only else torch.empty(w.K, w.HW, dtype=torch.float32, device=poses.device)
+    dz = None if motion_only else torch.empty(max(w.K, int(w.L.Kcap)), w.HW, dtype=torch.float32,
+                                              device=poses.device)
     poses_, disps_, intr, sens, tg, wt, ii_, jj_ = w.args
     check(lib.dbaf_ba(_p(w.ws), _p(poses_), _p(disps_), _p(intr), _p(sens), _p(tg), _p(wt), _p(w.eta),
                       w.eta_rows, _p(ii_), _p(jj_), w.E, w.N, w.t0, w.t1, w.ht, w.wd, int(iterations),
                       float(lm), float(ep), int(bool(motion_only)), _p(dx), _p(dz), _stream()), "dbaf_ba")
-    return [dx, dz]
+    if _strict:
+        w.check_flags("ba")
+    w.release()
+    return [dx, None if dz is None else dz[:w.K]]
 
 
 _host_cache = {}
@@ -224,17 +307,20 @@ def ba_host(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj,
         nstage = lib.dbaf_ba_host_staging_bytes(N, E, int(t0), int(t1), ht, wd, rows)
         ent = (torch.empty(L.total_bytes, dtype=torch.uint8, device=dev),
                torch.empty(nstage, dtype=torch.uint8, device=dev), nstage,
-               torch.empty(max(int(t1 - t0), 1), 6, dtype=torch.float32).pin_memory())
+               torch.empty(max(int(t1 - t0), 1), 6, dtype=torch.float32).pin_memory(),
+               torch.zeros(16, dtype=torch.int32).pin_memory())
         _host_cache.clear()            # one window shape at a time is the common case; do not hoard device memory
         _host_cache[key] = ent
-    ws, stage, nstage, dx = ent
+    ws, stage, nstage, dx, info = ent
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream()
         check(lib.dbaf_ba_host(_p(ws), _p(stage), nstage, _p(poses), _p(disps), _p(intrinsics), _p(disps_sens),
                                _p(targets), _p(weights), _p(eta), rows, _p(ii), _p(jj), E, N, int(t0), int(t1), ht,
                                wd, int(iterations), float(lm), float(ep), int(bool(motion_only)), _p(dx),
-                               c_void_p(stream.cuda_stream)), "dbaf_ba_host")
+                               _p(info), c_void_p(stream.cuda_stream)), "dbaf_ba_host")
         stream.synchronize()
+    if iterations > 0:
+        _raise_on_flags(info, "ba_host")
     return dx[:int(t1 - t0)]
 
 
@@ -246,7 +332,8 @@ def _export(w, H, v):
     r, c = H.shape
     if r > w.n or c > w.n:
         raise RuntimeError(f"H is larger than the {w.n}x{w.n} reduced camera system")
-    hv = w.Hv().cpu()                      # one D2H copy, synchronises the stream
+    hv = w.export_host()                   # one D2H copy into pinned memory, synchronises the stream
+    w.check_flags("hessian export", synced=True)
     H.copy_(hv[:w.n * w.n].view(w.n, w.n)[:r, :c])
     v[:r].copy_(hv[w.n * w.n:][:r])
 
@@ -277,8 +364,11 @@ def ba_extend(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, j
         if prior is None:
             if A_prior.dtype != torch.float64 or A_prior.dim() != 2:
                 raise RuntimeError("A_prior must be a 2-D float64 tensor")
-            prior = A_prior.to(poses.device).contiguous()
-        w.solve(lm, ep, prior)
+            prior_shape = tuple(A_prior.shape)
+            # a non-null pointer even for an empty prior: the reference then still solves with Ad + Adprior = 2 Ad
+            prior = (A_prior.to(poses.device).contiguous() if A_prior.numel() > 0
+                     else torch.zeros(1, dtype=torch.float64, device=poses.device))
+        w.solve(lm, ep, prior, prior_shape=prior_shape)
         dx, dz = w.retract()
     return [dx, dz]
 
@@ -322,7 +412,8 @@ class BACore:
         out = torch.empty(w.n * w.n + w.n, dtype=torch.float64, device=dev)
         check(lib.dbaf_ba_congruence(_p(w.ws), w.t0, w.t1, _p(Ad), _p(out), c_void_p(out.data_ptr() + 8 * w.n * w.n),
                                      _stream()), "dbaf_ba_congruence")
-        host = out.cpu()                   # one D2H copy, synchronises the stream
+        host = w.export_host(out)          # one D2H copy into pinned memory, synchronises the stream
+        w.check_flags("hessian_gtsam", synced=True)
         H.copy_(host[:w.n * w.n].view(w.n, w.n))
         v.reshape(-1).copy_(host[w.n * w.n:])
 

@@ -28,6 +28,8 @@ P = c_void_p
 SIGNATURES = {
     "dbaf_version": (c_int, []),
     "dbaf_last_error": (ctypes.c_char_p, []),
+    "dbaf_set_option": (c_int, [ctypes.c_char_p, ctypes.c_char_p]),
+    "dbaf_ba_schur": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "dbaf_projmap": (c_int, [P, P, P, P, P, c_int, c_int, c_int, P, P, P]),
     "dbaf_frame_distance": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_float, P, P]),
     "dbaf_iproj": (c_int, [P, P, P, c_int, c_int, c_int, P, P]),
@@ -52,7 +54,7 @@ SIGNATURES = {
     "dbaf_ba_prepare": (c_int, [P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "dbaf_ba_congruence": (c_int, [P, c_int, c_int, P, P, P, P]),
     "dbaf_ba_host_staging_bytes": (c_size_t, [c_int] * 7),
-    "dbaf_ba_host": (c_int, [P, P, c_size_t] + [P] * 7 + [c_int, P, P] + [c_int] * 7 + [c_float, c_float, c_int, P, P]),
+    "dbaf_ba_host": (c_int, [P, P, c_size_t] + [P] * 7 + [c_int, P, P] + [c_int] * 7 + [c_float, c_float, c_int, P, P, P]),
     "dbaf_ba_tables_noalloc": (c_int, [P, P, c_int, c_int, c_int, c_int, P, P, P, P, P, P]),
     "dbaf_ba_linearize": (c_int, [P, P, P, P, P, P, P, P, c_int, P, P, c_int, c_int, c_int, c_int, c_int,
                                   c_int, c_float, c_int, c_int, c_int, c_int, P]),

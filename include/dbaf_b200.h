@@ -36,6 +36,17 @@ extern "C" {
 int dbaf_version(void);
 const char* dbaf_last_error(void);
 
+/* Kernel-selection switches for tests and profiling (no counterpart in the reference).  Process-wide; the
+ * defaults come from the environment, read once (DBAF_SCHUR_IMPL, DBAF_BAND_IMPL, DBAF_BAND_SWEEP,
+ * DBAF_BAND_DOMAINS, DBAF_VOLUME_IMPL, DBAF_EIJ_RECOMPUTE).  Keys and values:
+ *   "schur_impl"   "auto" | "simt"                 Schur complement on tcgen05 where it pays / fp32 SIMT only
+ *   "band_impl"    "auto" | "single" | "twisted"   domain-decomposed banded solve / one sweep / two sweeps
+ *   "band_sweep"   "auto" | "smem"                 window of the banded sweep in registers / in shared memory
+ *   "band_domains" "<n>"                           number of domains of the decomposed solve (0 = automatic)
+ *   "volume_impl"  "auto" | "simt"                 correlation volume on tcgen05 / SIMT cross-check kernels
+ *   "eij"          "auto" | "store" | "recompute"  pose-depth blocks of the edges kept in HBM / recomputed */
+int dbaf_set_option(const char* key, const char* value);
+
 /* ------------------------------------------------------------------ geometry ---- */
 
 /* droid_backends.projmap, src/droid.cpp:200-215, src/droid_kernels.cu:471-560,1706-1731.
@@ -204,7 +215,8 @@ int dbaf_ba_tables_noalloc(const int64_t* ii, const int64_t* jj, int n_edges, in
  * E, Q, w for the back-substitution.  Only depth frames k in [k_lo,k_hi) (positions in kx) and
  * their out-edges are processed, which is how edge-sharded global BA splits the work
  * (k_hi < 0 means all).  alpha: sensor-depth prior weight (0.05 in `ba`, 0.001 in BACore).
- * eta [eta_rows,ht,wd]; eta_rows must equal K or be 1 (broadcast).
+ * eta [eta_rows,ht,wd]; eta_rows must equal K or be 1 (broadcast); anything else raises info[3] and the
+ * retraction then leaves disps and dz_out untouched (the reference fails with a broadcast error there).
  * motion_only: 0 = full, 1 = pose blocks only (no E/Q/w, no Schur), 2 = full linearisation but
  * the Schur kernel is not launched (profiling aid: times the Jacobian kernel alone). */
 int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
@@ -213,6 +225,12 @@ int dbaf_ba_linearize(void* workspace, const float* poses, const float* disps,
                       const int64_t* ii, const int64_t* jj, int n_edges, int n_frames,
                       int t0, int t1, int ht, int wd, float alpha, int motion_only,
                       int zero_first, int k_lo, int k_hi, void* stream);
+
+/* The Schur stage of dbaf_ba_linearize alone (schur_block + EEt6x6_kernel + Ev6x1_kernel,
+ * src/droid_kernels.cu:1297-1391,1046-1138): H -= E Q E^T, v -= E Q w for the depth frames [k_lo,k_hi) from the
+ * E, Q, w that the workspace holds.  Diagnostics and tests (feeding the Schur kernels with chosen blocks). */
+int dbaf_ba_schur(void* workspace, const int64_t* jj, int n_edges, int n_frames, int t0, int t1, int ht, int wd,
+                  int k_lo, int k_hi, void* stream);
 
 /* SparseBlock::solve / solveDense, src/droid_kernels.cu:1248-1288,180-198: L = H (+ prior);
  * diag += ep + lm*diag; float64 Cholesky; dx -> workspace (float32), zeros if a pivot <= 0.
@@ -231,7 +249,8 @@ int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, in
 
 /* EvT6x1_kernel + dz + pose_retr_kernel + disp_retr_kernel, src/droid_kernels.cu:1140-1160,
  * 1486-1506,943-991.  dx_in: float32 [P,6] (NULL = the workspace's dx).  poses/disps are updated
- * in place.  dz_out [K,HW] (may be NULL), dx_out [P,6] (may be NULL).  update_disps=0 gives the
+ * in place.  dz_out [K,HW] (may be NULL; K is only known on the device, info[0], so size it with Kcap rows
+ * unless K is known), dx_out [P,6] (may be NULL).  update_disps=0 gives the
  * motion-only update.  Depth frames [k_lo,k_hi) only, as in dbaf_ba_linearize. */
 int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,
                     const int64_t* ii, const int64_t* jj, int n_edges, int n_frames,
@@ -256,7 +275,8 @@ int dbaf_ba_congruence(void* workspace, int t0, int t1, const double* A, double*
 /* The same call for callers whose window lives in HOST memory (a frontend that assembles targets/weights on the
  * CPU, a process that receives them over IPC): every input is copied to `staging` (device scratch of
  * dbaf_ba_host_staging_bytes() bytes) with cudaMemcpyAsync on `stream`, dbaf_ba runs on the copies, and the updated
- * poses[t0:t1], disps (unless motion_only) and dx_out_h [P,6] (may be NULL) are copied back.  Everything is enqueued
+ * poses[t0:t1], disps (unless motion_only), dx_out_h [P,6] (may be NULL) and the status words info_out_h int32[16]
+ * (may be NULL; meanings as dbaf_ba_layout.info) are copied back.  Everything is enqueued
  * on `stream`; the host buffers must stay valid, and should be pinned, until the caller has synchronised it.  No
  * reference counterpart: droid_backends.ba only accepts CUDA tensors (src/droid.cpp:16-18 CHECK_INPUT). */
 size_t dbaf_ba_host_staging_bytes(int n_frames, int n_edges, int t0, int t1, int ht, int wd, int eta_rows);
@@ -264,7 +284,8 @@ int dbaf_ba_host(void* workspace, void* staging, size_t staging_bytes, float* po
                  const float* intrinsics_h, const float* disps_sens_h, const float* targets_h,
                  const float* weights_h, const float* eta_h, int eta_rows, const int64_t* ii_h,
                  const int64_t* jj_h, int n_edges, int n_frames, int t0, int t1, int ht, int wd,
-                 int iterations, float lm, float ep, int motion_only, float* dx_out_h, void* stream);
+                 int iterations, float lm, float ep, int motion_only, float* dx_out_h, int32_t* info_out_h,
+                 void* stream);
 
 #ifdef __cplusplus
 }

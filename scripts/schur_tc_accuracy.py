@@ -12,8 +12,7 @@ for cfg, reach in (("g40", 6), ("g24", 10)):
     w = synth.make_window(cfg, seed=3, graph="banded", reach=reach)
     out = {}
     for impl in ("tc", "simt"):
-        if impl == "simt": os.environ["DBAF_SCHUR_IMPL"] = "simt"
-        else: os.environ.pop("DBAF_SCHUR_IMPL", None)
+        db.set_option("schur_impl", "simt" if impl == "simt" else "auto")
         t = {k: (torch.from_numpy(v.copy()).to(dev) if isinstance(v, np.ndarray) else v) for k, v in w.items()}
         win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
         win.prepare(); win.linearize(0.05)

@@ -45,6 +45,18 @@ def db():
     return droid_backends
 
 
+@pytest.fixture(autouse=True)
+def _default_kernel_options():
+    """Kernel-selection switches (droid_backends.set_option) never leak from one test into the next."""
+    yield
+    mod = sys.modules.get("droid_backends")
+    if mod is not None:
+        for key in ("schur_impl", "band_impl", "band_sweep", "volume_impl", "eij"):
+            mod.set_option(key, "auto")
+        mod.set_option("band_domains", "0")
+        mod.set_strict(False)
+
+
 @pytest.fixture(scope="session")
 def ref():
     """The reference CUDA extension rebuilt for sm_100a (oracle/_ref/droid_backends_ref.so)."""

@@ -1,5 +1,22 @@
 """Shared helpers for the parity tests."""
+import json
+import os
+
 import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def record(test, **values):
+    """Append the ACHIEVED error figures of a parity test to gpurun_out/parity_achieved.jsonl (scratch; the
+    table in DESIGN.md section 4 is filled from it)."""
+    out = os.path.join(ROOT, "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_achieved.jsonl"), "a") as f:
+            f.write(json.dumps(dict(test=test, **{k: (float(v) if v is not None else None) for k, v in values.items()})) + "\n")
+    except OSError:
+        pass
 
 
 def relerr(a, b):

@@ -189,6 +189,43 @@ def test_failed_factorisation_leaves_poses_untouched(dev, db, synth):
     assert torch.all(dx == 0) and torch.equal(t["poses"], p0)
 
 
+def test_eta_row_mismatch_is_flagged_and_nothing_is_written(dev, db, synth):
+    """eta must have one row per depth frame (or one row in all): the reference fails with a broadcast error
+    (src/droid_kernels.cu:1475); here the device raises info[3], leaves disps and dz alone, and every call that
+    synchronises anyway -- or `ba` in strict mode -- raises."""
+    w = _window(synth, "tiny", seed=7)
+    K = w["eta"].shape[0]
+    assert K >= 3
+    for rows in (K - 1, K + 2):
+        t = to_torch(w, dev)
+        eta = (t["eta"][:rows] if rows < K else torch.cat([t["eta"], t["eta"][:rows - K]])).contiguous()
+        guard = torch.full((4, w["ht"] * w["wd"]), 7.0, device=dev)     # lives right behind a would-be [rows,HW] dz
+        dx, dz = db.ba(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], eta,
+                       t["ii"], t["jj"], w["t0"], w["t1"], 1, 1e-4, 0.1, False)
+        info = db.ba_info()
+        assert int(info[3]) == 1 and int(info[0]) == K
+        assert dz.shape[0] == rows
+        assert torch.equal(t["disps"].cpu(), torch.from_numpy(w["disps"]))
+        assert float(guard.min()) == 7.0 and float(guard.max()) == 7.0
+        db.set_strict(True)
+        with pytest.raises(RuntimeError, match="eta"):
+            db.ba(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], eta,
+                  t["ii"], t["jj"], w["t0"], w["t1"], 1, 1e-4, 0.1, False)
+        db.set_strict(False)
+        core = db.BACore()
+        core.init(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], eta,
+                  t["ii"], t["jj"], w["t0"], w["t1"], 2, 1e-4, 0.1, False)
+        n = 6 * (w["t1"] - w["t0"])
+        with pytest.raises(RuntimeError, match="eta"):
+            core.hessian(torch.zeros(n, n, dtype=torch.float64), torch.zeros(n, dtype=torch.float64))
+    # a bad edge index is reported the same way
+    t = to_torch(w, dev)
+    t["jj"][0] = w["poses"].shape[0] + 3
+    db.set_strict(True)
+    with pytest.raises(RuntimeError, match="edge index"):
+        db.ba(*ba_args(t), w["t0"], w["t1"], 1, 1e-4, 0.1, False)
+
+
 def test_ba_extend_exports_and_prior(dev, db, oracle, synth):
     w = _window(synth, "tiny", seed=5)
     n = 6 * (w["t1"] - w["t0"])
