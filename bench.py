@@ -1,22 +1,26 @@
 #!/usr/bin/env python
-"""Benchmark of the dense-BA / correlation hot path (BASELINE.json: "dense-BA ms/iter + corr edges/s").
+"""Benchmark of the dense-BA / correlation hot path (BASELINE.json: "dense-BA ms/iter + corr edges/s vs ref CUDA &
+CPU; 1/2/4/8 B200 global-BA scaling").
 
-    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c2|c3|c5]
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload c2|c2_real|c3|c4|c5]
 
-N = 1 (default): the TUM-VI-shaped frontend window (BASELINE.json configs[1]: 64x64 disparity maps,
-12 keyframes, 48 edges).  One step = one `droid_backends.ba(..., iterations=2)` call; `value` is
-milliseconds per Gauss-Newton iteration with every input already resident in HBM, `e2e` is the same
-through the public API with HOST (pinned) inputs, host->device copies and the device->host read of
-the result inside the timed region.  The correlation half of the metric (volume+pyramid build and the
-4-level lookup over the same 48 edges) is timed in the same run and reported under "corr".
+The line of record is the SAME workload at every N, so that the 1/2/4/8 series is one series: global / backend BA
+over a 1000-keyframe banded graph (BASELINE.json configs[4], the largest single-GPU configuration and the only
+one that shards).  One step = one Gauss-Newton iteration; `value` is milliseconds per iteration with all inputs
+resident in HBM (CUDA events, max over ranks, L2 flushed between steps), `e2e` the same iteration from / to pinned
+HOST memory through dbaf_b200.global_ba.iterate_host.  For N > 1 the depth frames are sharded over the ranks
+(strong scaling, NCCL).
 
-N > 1 (torchrun): edge-sharded global BA over a banded keyframe graph (configs[4]); every rank
-linearises the depth frames it owns, the reduced camera system is all-reduced with NCCL, the solve
-is replicated.  `value` is ms per iteration (strong scaling), max over ranks.
+At N = 1 the line also carries the frontend measurements as named sub-records: `frontend_c2` (BASELINE.json
+configs[1]: 64x64, 12 keyframes, 48 edges, `droid_backends.ba` with 2 iterations, device-resident and end to end
+through `ba_host`, the correlation volume / lookup / reproject kernels, the unmodified reference on the same GPU),
+`frontend_c2_real` (55x55, what the TUM-VI demo really produces), `frontend_c3` (28x107, KITTI-360), `bacore` (the
+IMU-mode call sequence BACore.init -> 2 x (hessian -> host -> retract) and the marginalisation call), `c4_altcorr`
+(on-the-fly correlation against the materialised volume), and `cpu_baseline`.
 
 --impl reference runs the unmodified reference extension (oracle/_ref/droid_backends_ref.so, built by
-oracle/build_ref.py from the reference's own sources) on the same workload; if that library is absent
-it times the oracle's CPU port instead.  Prints ONE JSON line on rank 0.
+oracle/build_ref.py from the reference's own sources) on the same workload; if that library is absent it times the
+oracle's CPU port instead.  Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
@@ -44,18 +48,23 @@ NCU_TRAFFIC_BYTES = {("c2", "k_linearize2"): 3.79e6, ("c2", "k_volume_tc"): 2.13
 
 
 def write_only_peak(dev):
-    """HBM write-only bandwidth measured here and now (GB/s): a 2 GiB fill, best of 5.  The copy figure in
-    MEASURED_PEAKS.json counts read + write bytes; a kernel that only writes cannot exceed this one."""
-    x = torch.empty(1 << 30, dtype=torch.int16, device=dev)
-    best = 1e9
-    for _ in range(7):
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        x.fill_(1)
-        b.record()
-        b.synchronize()
-        best = min(best, a.elapsed_time(b))
-    return x.numel() * 2 / (best * 1e-3) / 1e9
+    """HBM write-only bandwidth measured here and now (GB/s): the best of cudaMemsetAsync and the library's
+    hand-written 128-bit-store fill over 2 GiB (dbaf_probe_fill), best of 7 each.  Reported next to -- never instead
+    of -- the fraction of the copy peak in MEASURED_PEAKS.json."""
+    import droid_backends as db
+    x = torch.empty(1 << 31, dtype=torch.uint8, device=dev)
+    out = {}
+    for kind in (0, 1):
+        best = 1e9
+        for _ in range(7):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            db.probe_fill(x, kind)
+            b.record()
+            b.synchronize()
+            best = min(best, a.elapsed_time(b))
+        out["memset" if kind == 0 else "st128"] = x.numel() / (best * 1e-3) / 1e9
+    return max(out.values()), out
 
 
 def measured_peaks():
@@ -145,6 +154,18 @@ def window_tensors(win, dev):
 def ba_call_args(t):
     return (t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"], t["eta"],
             t["ii"], t["jj"])
+
+
+def global_ba_config():
+    from dbaf_b200 import global_ba
+    return global_ba.c5_config()
+
+
+def frontend_config(cfg, n_frames, n_edges, ht, wd, iters):
+    """`config` of a frontend line; both arms print the identical dict."""
+    return dict(workload=f"{cfg}: {ht}x{wd} disparity maps, {n_frames} keyframes, {n_edges} edges, "
+                         f"{iters} GN iterations per step (droid_backends.ba)",
+                l2="512 MB read+write between steps (inputs are smaller than L2)")
 
 
 # --------------------------------------------------------------------- single-GPU arm
@@ -256,10 +277,7 @@ def bench_local(args, dev, rank, world):
     line = dict(metric="dense-BA ms/iter", value=step_ms / iters, unit="ms/iter", n_gpus=world, steps=args.steps,
                 warmup=args.warmup, ms_per_step=step_ms, higher_is_better=False, scaling="weak",
                 vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=f"{cfg}: {ht}x{wd} disparity maps, {win['poses'].shape[0]} keyframes, "
-                                     f"{E} edges, {iters} GN iterations per step (droid_backends.ba)",
-                            l2="512 MB read+write between steps (inputs are smaller than L2)",
-                            replicas=world),
+                config=frontend_config(cfg, win["poses"].shape[0], E, ht, wd, iters), replicas=world,
                 roofline=roof, stages_ms=stage,
                 e2e=dict(value=e2e_val, unit="ms/iter", h2d_bytes_per_step=h2d, d2h_bytes_per_step=d2h,
                          ms_per_step=statistics.mean(e2e_ms)),
@@ -280,7 +298,7 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
     vol_ms = statistics.mean(timed_steps(lambda: db.corr_volume_pyramid(f1, f2, 4), steps, 3, flush))
     # the call the pipeline makes (dbaf/covisible_graph.py:129-131): per-frame maps + edge lists, no gather
     idx_ms = statistics.mean(timed_steps(lambda: db.corr_volume_pyramid_indexed(feats, feats, ii, jj, 4), steps, 3, flush))
-    wpeak = write_only_peak(dev)
+    wpeak, wpeak_kinds = write_only_peak(dev)
     look_ms = statistics.mean(timed_steps(lambda: db.corr_lookup_pyramid(pyr, coords, 3), steps, 3, flush))
     # the reference's own path for the same work, on this GPU, in this run: torch.matmul (cuBLAS) + 3x
     # avg_pool2d (dbaf/modules/corr.py:24-38,63-71) and its corr_index_forward kernel (oracle/_ref)
@@ -328,8 +346,10 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
             roofline=dict(bound="hbm", kernel="k_volume_tc", achieved=idx_bytes / (idx_ms * 1e-3) / 1e9, peak=peaks["hbm"],
                           unit="GB/s", frac=idx_bytes / (idx_ms * 1e-3) / 1e9 / peaks["hbm"],
                           traffic=NCU_TRAFFIC_BYTES.get((cfg, "k_volume_tc")),
-                          write_only_peak=wpeak, frac_of_write_only_peak=idx_bytes / (idx_ms * 1e-3) / 1e9 / wpeak,
-                          note="97 % of the bytes are writes; write_only_peak is a fill measured in this run")),
+                          write_only_peak=wpeak, write_only_peak_by=wpeak_kinds,
+                          frac_of_write_only_peak=idx_bytes / (idx_ms * 1e-3) / 1e9 / wpeak,
+                          note="97 % of the bytes are writes; write_only_peak = best of cudaMemsetAsync and a 128-bit "
+                               "store kernel over 2 GiB, measured in this run")),
         volume_pyramid=dict(edges_per_s=n / (vol_ms * 1e-3), ms=vol_ms,
                             roofline=dict(bound="hbm", achieved=vol_bytes / (vol_ms * 1e-3) / 1e9, peak=peaks["hbm"],
                                           unit="GB/s", frac=vol_bytes / (vol_ms * 1e-3) / 1e9 / peaks["hbm"],
@@ -348,14 +368,24 @@ def bench_corr(db, synth, cfg, win, dev, flush, peaks, args):
 
 
 def cpu_baseline(cfg, budget_s=20.0):
-    """Oracle port (numpy, float32) of `ba` on the same workload, on the host cores of this box."""
+    """Oracle port (numpy, float32, one core) of `ba` on the host cores of this box.  Frontend windows are run whole;
+    the global-BA workload is sampled: the first 48 keyframes of the same banded graph (same +-10 neighbourhood, same
+    frame size), scaled by the edge count -- everything upstream of the solve is linear in the edges, and the
+    sample's dense solve (288 unknowns) is cheaper per pose than the full one, so the scaled figure flatters the CPU."""
     import dbaf_oracle as oracle
     from dbaf_b200 import synth
     try:
         from threadpoolctl import threadpool_limits
     except Exception:
         threadpool_limits = None
-    win = synth.make_window(cfg, seed=0)
+    big = cfg == "c5"
+    if big:
+        full_edges = len(synth.banded_graph(synth.CONFIGS["c5"][2], reach=10)[0])
+        win = synth.make_window("g24", seed=0, graph="banded", reach=10, n_extra_frames=24, pose_noise=0.005)
+        iters, max_runs = 1, 3
+    else:
+        win = synth.make_window(cfg, seed=0)
+        iters, max_runs = 2, 6
     times = []
     t_start = time.perf_counter()
 
@@ -363,7 +393,7 @@ def cpu_baseline(cfg, budget_s=20.0):
         p, d = win["poses"].copy(), win["disps"].copy()
         a = time.perf_counter()
         oracle.ba(p, d, win["intrinsics"], win["disps_sens"], win["targets"], win["weights"], win["eta"],
-                  win["ii"], win["jj"], win["t0"], win["t1"], 2, 1e-4, 0.1, False, dtype=np.float32)
+                  win["ii"], win["jj"], win["t0"], win["t1"], iters, 1e-4, 0.1, False, dtype=np.float32)
         times.append((time.perf_counter() - a) * 1e3)
 
     ctx = threadpool_limits(limits=1) if threadpool_limits else None
@@ -371,14 +401,126 @@ def cpu_baseline(cfg, budget_s=20.0):
         if ctx:
             ctx.__enter__()
         one()
-        while time.perf_counter() - t_start < budget_s and len(times) < 6:
+        while time.perf_counter() - t_start < budget_s and len(times) < max_runs:
             one()
     finally:
         if ctx:
             ctx.__exit__(None, None, None)
-    best = statistics.median(times)
-    return dict(value=best / 2, unit="ms/iter", cores=1, kind="port",
+    best = statistics.median(times) / iters
+    if big:
+        scale = full_edges / len(win["ii"])
+        return dict(value=best * scale, unit="ms/iter", cores=1, kind="port", measured_ms=best, scale=scale,
+                    sample=f"{len(times)} x oracle.ba (numpy float32, 1 iteration) on a {win['poses'].shape[0]}-keyframe, "
+                           f"{len(win['ii'])}-edge window of the same banded graph at 64x64, scaled by "
+                           f"{full_edges}/{len(win['ii'])} edges")
+    return dict(value=best, unit="ms/iter", cores=1, kind="port",
                 sample=f"{len(times)} x oracle.ba (numpy float32, 2 iterations) on the full {cfg} window")
+
+
+# --------------------------------------------------------------------- IMU-mode call sequence
+def bench_bacore(db, synth, cfg, dev, flush, steps):
+    """What DBA-Fusion's IMU mode actually calls (dbaf/depth_video.py:392-399, 524-558): BACore.init, then twice
+    {hessian -> float64 H, v on the host -> (GTSAM) -> retract(dx from the host)}, plus the marginalisation call
+    (a second BACore with zeroed sensor depths, one hessian, H[i,i] += 0.00025).  GTSAM itself is outside the path;
+    dx is a fixed small vector.  Wall clock (every call ends in a host synchronisation), ours and the reference's."""
+    win = synth.make_window(cfg, seed=0, sensor_frac=0.3)
+    t0, t1 = win["t0"], win["t1"]
+    n = 6 * (t1 - t0)
+    dx_host = torch.from_numpy(np.random.default_rng(3).normal(0, 1e-3, n))
+    out = {}
+    mods = [("ours", db)]
+    try:
+        import build_ref
+        rmod = build_ref.load()
+        if rmod is not None:
+            mods.append(("reference", rmod))
+    except Exception:
+        pass
+    for name, mod in mods:
+        t = window_tensors(win, dev)
+        p0, d0 = t["poses"].clone(), t["disps"].clone()
+        zs = torch.zeros_like(t["disps_sens"])
+        H = torch.zeros(n, n, dtype=torch.float64)
+        v = torch.zeros(n, dtype=torch.float64)
+
+        def update():
+            core = mod.BACore()
+            core.init(*ba_call_args(t), t0, t1, 2, 1e-4, 0.1, False)
+            for _ in range(2):
+                core.hessian(H, v)
+                core.retract(dx_host)
+            del core
+
+        def marginalise():
+            core = mod.BACore()
+            core.init(t["poses"], t["disps"], t["intrinsics"], zs, t["targets"], t["weights"], t["eta"], t["ii"],
+                      t["jj"], t0, t1, 2, 1e-4, 0.1, False)
+            core.hessian(H, v)
+            for i in range(6):
+                H[i, i] += 0.00025
+            del core
+
+        rec = {}
+        for key, fn in (("update_ms", update), ("marginalise_ms", marginalise)):
+            ts = []
+            for it in range(3 + steps):
+                t["poses"].copy_(p0)
+                t["disps"].copy_(d0)
+                flush()
+                torch.cuda.synchronize()
+                a = time.perf_counter()
+                fn()
+                torch.cuda.synchronize()
+                if it >= 3:
+                    ts.append((time.perf_counter() - a) * 1e3)
+            rec[key] = statistics.mean(ts)
+        out[name] = rec
+    out["d2h_bytes_per_hessian"] = (n * n + n) * 8
+    out["h2d_bytes_per_retract"] = n * 4
+    out["workload"] = f"{cfg}: BACore.init + 2 x (hessian -> host, retract) / marginalisation hessian, {n}x{n} float64 H"
+    return out
+
+
+def bench_altcorr(db, synth, dev, flush, steps):
+    """BASELINE.json configs[3]: the on-the-fly correlation (altcorr_forward over the 4 feature-pooled levels,
+    dbaf/modules/corr.py:91-139) against the materialised volume + lookup on the same 36-edge window."""
+    cfg = "c4"
+    ht, wd, P, E, _ = synth.CONFIGS[cfg]
+    win = synth.make_window(cfg, seed=0)
+    feats = torch.from_numpy(synth.make_features(cfg, seed=0, n_frames=win["poses"].shape[0])).to(dev)
+    ii, jj = torch.from_numpy(win["ii"]).to(dev), torch.from_numpy(win["jj"]).to(dev)
+    n = len(win["ii"])
+    coords0 = torch.from_numpy(synth.lookup_coords(win, 0.05, 0)).to(dev)          # [E,2,ht,wd]
+    coords = coords0.permute(0, 2, 3, 1)[:, None].contiguous()                     # [E,1,ht,wd,2]
+    f1 = (feats[ii].float() / 4.0).permute(0, 2, 3, 1).contiguous()
+    f2 = feats[jj].float() / 4.0
+    pyr2 = [f2.permute(0, 2, 3, 1).contiguous()]
+    for _ in range(3):
+        f2 = torch.nn.functional.avg_pool2d(f2, 2, stride=2)
+        pyr2.append(f2.permute(0, 2, 3, 1).contiguous())
+
+    def alt(mod):
+        return [mod.altcorr_forward(f1, pyr2[l], (coords / 2 ** l).contiguous(), 3)[0] for l in range(4)]
+
+    ours_ms = statistics.mean(timed_steps(lambda: alt(db), steps, 3, flush))
+    HW = ht * wd
+    flop = n * 2.0 * 128 * 64 * 4 * HW
+    bytes_ = n * (HW * 128 * 4 + sum((ht >> l) * (wd >> l) for l in range(4)) * 128 * 4 + HW * 196 * 4 + HW * 8)
+    out = dict(edges=n, ours_ms=ours_ms, ours_edges_per_s=n / (ours_ms * 1e-3),
+               roofline=dict(bound="hbm", kernel="k_altcorr_fwd", achieved=bytes_ / (ours_ms * 1e-3) / 1e9,
+                             unit="GB/s", algorithmic_bytes=bytes_, fp32_tflops=flop / (ours_ms * 1e-3) / 1e12))
+    pyr = db.corr_volume_pyramid_indexed(feats, feats, ii, jj, 4)
+    vol_ms = statistics.mean(timed_steps(lambda: db.corr_volume_pyramid_indexed(feats, feats, ii, jj, 4), steps, 3, flush))
+    look_ms = statistics.mean(timed_steps(lambda: db.corr_lookup_pyramid(pyr, coords0, 3), steps, 3, flush))
+    out["volume_plus_lookup_ms"] = dict(volume_pyramid=vol_ms, lookup=look_ms)
+    try:
+        import build_ref
+        rmod = build_ref.load()
+        if rmod is not None:
+            out["reference_ms"] = statistics.mean(timed_steps(lambda: alt(rmod), steps, 3, flush))
+    except Exception as ex:
+        out["reference_error"] = str(ex)[:200]
+    return out
 
 
 # --------------------------------------------------------------------- reference arm
@@ -396,7 +538,7 @@ def bench_reference(args, dev):
     ref = build_ref.load() if torch.cuda.is_available() else None
     iters = 1 if big else 2
     if ref is None:
-        cb = cpu_baseline("c2" if big else cfg, budget_s=60.0)
+        cb = cpu_baseline(cfg, budget_s=60.0)
         val, step_ms, kind, n_steps = cb["value"], cb["value"] * iters, cb, 0
     else:
         t = window_tensors(win, dev)
@@ -432,8 +574,7 @@ def bench_reference(args, dev):
     return dict(impl="reference", metric="dense-BA ms/iter", value=val, unit="ms/iter", n_gpus=1, steps=n_steps,
                 warmup=args.warmup, ms_per_step=step_ms, higher_is_better=False,
                 scaling="strong" if big else "weak", vs_baseline=None, dtype="f32", data="synthetic",
-                config=dict(workload=f"{cfg}: {ht}x{wd} disparity maps, {win['poses'].shape[0]} keyframes, {n_edges} edges, "
-                                     f"{iters} GN iteration(s) per step"),
+                config=(global_ba_config() if big else frontend_config(cfg, win["poses"].shape[0], n_edges, ht, wd, iters)),
                 cpu_baseline=kind,
                 e2e=dict(value=val, unit="ms/iter", h2d_bytes_per_step=0, d2h_bytes_per_step=0))
 
@@ -447,7 +588,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-global", action="store_true", help="skip the 1-GPU run of the c5 global-BA workload")
+    ap.add_argument("--no-sub", action="store_true", help="skip the frontend / BACore / altcorr sub-records at N = 1")
     args = ap.parse_args()
     args.warmup = max(3, args.warmup)
     rank = int(os.environ.get("RANK", "0"))
@@ -457,7 +598,7 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        args.workload = args.workload or ("c5" if max(args.gpus, world) > 1 else "c2")
+        args.workload = args.workload or "c5"
         dev = torch.device("cuda:0") if torch.cuda.is_available() else torch.device("cpu")
         print(json.dumps(bench_reference(args, dev)))
         return
@@ -470,22 +611,29 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         torch.distributed.init_process_group("nccl", device_id=dev)
 
-    if world > 1 or (args.workload or "").startswith("c5"):
+    default_run = args.workload is None
+    args.workload = args.workload or "c5"
+    if args.workload.startswith("c5"):
         from dbaf_b200 import global_ba
         line, clk = global_ba.bench(args, dev, rank, world, ClockSampler, L2Flusher, measured_peaks())
-    else:
-        default_run = args.workload is None
-        args.workload = args.workload or "c2"
-        line, clk = bench_local(args, dev, rank, world)
-        if default_run and not args.no_global:
-            # `--gpus N` for N > 1 runs the edge-sharded global BA (BASELINE.json configs[4]); its 1-GPU point is
-            # measured here so that the 1/2/4/8 series has a base on the same workload
-            from dbaf_b200 import global_ba
+        if default_run and world == 1 and not args.no_sub:
+            # the frontend halves of the metric, as named sub-records of the same line
             import copy
-            ga = copy.copy(args)
-            ga.workload, ga.steps = "c5", min(args.steps, 10)
-            gl, _ = global_ba.bench(ga, dev, rank, world, ClockSampler, L2Flusher, measured_peaks())
-            line["global_ba_1gpu"] = {k: gl[k] for k in ("value", "unit", "ms_per_step", "config", "stages_ms", "roofline")}
+            import droid_backends as db
+            from dbaf_b200 import synth
+            fa = copy.copy(args)
+            fa.steps = min(args.steps, 20)
+            for cfg in ("c2", "c2_real", "c3"):
+                fa.workload = cfg
+                fl, _ = bench_local(fa, dev, rank, world)
+                line[f"frontend_{cfg}"] = {k: fl[k] for k in ("value", "unit", "ms_per_step", "config", "stages_ms",
+                                                               "roofline", "e2e", "gpu_launches", "corr",
+                                                               "reference_cuda_same_gpu")}
+            flush = L2Flusher(dev)
+            line["bacore"] = {cfg: bench_bacore(db, synth, cfg, dev, flush, min(args.steps, 10)) for cfg in ("c2_real", "c3")}
+            line["c4_altcorr"] = bench_altcorr(db, synth, dev, flush, max(3, min(args.steps, 10)))
+    else:
+        line, clk = bench_local(args, dev, rank, world)
 
     if world > 1:
         v = torch.tensor([line["ms_per_step"]], device=dev, dtype=torch.float64)
@@ -493,14 +641,21 @@ def main():
         scale = float(v.item()) / line["ms_per_step"]
         line["ms_per_step"] = float(v.item())
         line["value"] *= scale
+    rc = 0
     if rank == 0:
         line["clocks"] = clk.summary()
         if not args.no_cpu_baseline and world == 1:
-            line["cpu_baseline"] = cpu_baseline(args.workload if args.workload in ("c1", "c2", "c2_real", "c3", "tiny") else "c2")
+            line["cpu_baseline"] = cpu_baseline(args.workload)
         print(json.dumps(line))
+        par = line.get("parity_vs_1gpu")
+        if par and max(par["dx_rel"], par["poses_rel"], par["disps_rel"]) > par["bound"]:
+            print(f"bench.py: the sharded iteration differs from the single-rank one: {par}", file=sys.stderr)
+            rc = 3
     if world > 1:
         torch.distributed.barrier()
         torch.distributed.destroy_process_group()
+    if rc:
+        sys.exit(rc)
 
 
 if __name__ == "__main__":

@@ -287,6 +287,30 @@ extern "C" int dbaf_depth_filter(const float* poses, const float* disps, const f
   return DBAF_OK;
 }
 
+// ------------------------------------------------------------------ probes ----
+namespace dbaf {
+namespace {
+// write-only stream of 128-bit stores, one 512-byte line group per warp instruction
+__global__ void __launch_bounds__(256) k_fill128(uint4* __restrict__ dst, size_t n16, uint4 val) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) dst[i] = val;
+}
+}  // namespace
+}  // namespace dbaf
+
+extern "C" int dbaf_probe_fill(void* dst, size_t bytes, int kind, void* stream) {
+  DBAF_REQUIRE(dst != nullptr && (reinterpret_cast<uintptr_t>(dst) & 15) == 0, "dst must be 16-byte aligned");
+  DBAF_REQUIRE(kind == 0 || kind == 1, "kind: 0 = cudaMemsetAsync, 1 = 128-bit store kernel");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (kind == 0) {
+    DBAF_CUDA(cudaMemsetAsync(dst, 1, bytes, st));
+  } else {
+    k_fill128<<<148 * 8, 256, 0, st>>>(static_cast<uint4*>(dst), bytes / 16, make_uint4(1u, 2u, 3u, 4u));
+    DBAF_LAUNCH_CHECK("k_fill128");
+  }
+  return DBAF_OK;
+}
+
 // ------------------------------------------------------------------ options ----
 extern "C" int dbaf_set_option(const char* key, const char* value) {
   DBAF_REQUIRE(key != nullptr && value != nullptr, "null key or value");

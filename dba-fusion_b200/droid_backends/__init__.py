@@ -38,6 +38,11 @@ def set_option(key, value):
     check(lib.dbaf_set_option(str(key).encode(), str(value).encode()), "dbaf_set_option")
 
 
+def probe_fill(buf, kind):
+    """dbaf_probe_fill: overwrite `buf` (a CUDA tensor) with cudaMemsetAsync (kind 0) or 128-bit stores (kind 1)."""
+    check(lib.dbaf_probe_fill(_p(buf), buf.numel() * buf.element_size(), int(kind), _stream()), "dbaf_probe_fill")
+
+
 def set_strict(on=True):
     """In strict mode `ba` synchronises after the call and raises on a bad edge index or an eta/K mismatch."""
     global _strict

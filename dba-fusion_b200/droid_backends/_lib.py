@@ -29,6 +29,7 @@ SIGNATURES = {
     "dbaf_version": (c_int, []),
     "dbaf_last_error": (ctypes.c_char_p, []),
     "dbaf_set_option": (c_int, [ctypes.c_char_p, ctypes.c_char_p]),
+    "dbaf_probe_fill": (c_int, [P, c_size_t, c_int, P]),
     "dbaf_ba_schur": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "dbaf_projmap": (c_int, [P, P, P, P, P, c_int, c_int, c_int, P, P, P]),
     "dbaf_frame_distance": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_float, P, P]),

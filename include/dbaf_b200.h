@@ -47,6 +47,11 @@ const char* dbaf_last_error(void);
  *   "eij"          "auto" | "store" | "recompute"  pose-depth blocks of the edges kept in HBM / recomputed */
 int dbaf_set_option(const char* key, const char* value);
 
+/* Measurement aid (no counterpart in the reference): a write-only stream over `bytes` of device memory, either
+ * cudaMemsetAsync (kind 0) or a kernel of 128-bit stores (kind 1).  bench.py times both to state the HBM write
+ * ceiling next to the copy peak for the kernels whose traffic is almost all stores (the correlation volume). */
+int dbaf_probe_fill(void* dst, size_t bytes, int kind, void* stream);
+
 /* ------------------------------------------------------------------ geometry ---- */
 
 /* droid_backends.projmap, src/droid.cpp:200-215, src/droid_kernels.cu:471-560,1706-1731.

@@ -830,3 +830,83 @@ def altcorr_backward(fmap1, fmap2, coords, corr_grad, r, dtype=np.float32):
                 g1 += g[..., None] * f2g
                 np.add.at(g2, (bb[inb], h2[inb], w2[inb]), g[inb][:, None] * f1[inb])
     return g1, g2, np.zeros(coords.shape, dtype)
+
+
+# --------------------------------------------------------------------------
+# frame-graph edge selection (dbaf/covisible_graph.py)
+# --------------------------------------------------------------------------
+def proximity_candidates(t0, t1, t, skip_edge=(), frontend_window=0):
+    """Candidate pairs of add_proximity_factors, dbaf/covisible_graph.py:360-377: the (t-t0) x (t-t1) grid in
+    row-major order (torch.meshgrid, 'ij'), then -- when skip edges are configured and the grid's source range
+    spans exactly frontend_window frames -- one pair (newest frame, oldest + s) per skip offset s with
+    oldest + s > 0.  Returns ii, jj (int64) and cc, the size of the grid."""
+    ix = np.arange(t0, t, dtype=np.int64)
+    jx = np.arange(t1, t, dtype=np.int64)
+    ii = np.repeat(ix, len(jx))
+    jj = np.tile(jx, len(ix))
+    cc = len(ii)
+    if len(skip_edge) and cc and ii.max() - ii.min() == frontend_window - 1:
+        jj_add = ii.min() + np.asarray(skip_edge, np.int64)
+        jj_add = jj_add[jj_add > 0]
+        ii = np.concatenate([ii, np.full(len(jj_add), ii.max(), np.int64)])
+        jj = np.concatenate([jj, jj_add])
+    return ii, jj, cc
+
+
+def proximity_edges(d, ii, jj, cc, ex_ii, ex_jj, t0, t1, t, rad, nms, thresh, stereo, max_factors):
+    """The edge list add_proximity_factors hands to add_factors, dbaf/covisible_graph.py:379-439, given the
+    candidates (ii, jj, cc of proximity_candidates), their float32 distances d and the existing edges
+    ex_ii/ex_jj (= cat(ii, ii_bad, ii_inac) of the graph, :383-384).  Returns int64 arrays (es_i, es_j)."""
+    d = np.array(d, np.float32, copy=True)
+    W = t - t1
+    d[ii - rad < jj] = np.inf                                   # :380
+    d[d > 100] = np.inf                                         # :381
+
+    def stamp(i, j):                                            # :386-394 and :425-433
+        lim = max(min(abs(i - j) - 2, nms), 0)
+        for di in range(-nms, nms + 1):
+            for dj in range(-nms, nms + 1):
+                if abs(di) + abs(dj) <= lim:
+                    i1, j1 = i + di, j + dj
+                    if t0 <= i1 < t and t1 <= j1 < t:
+                        d[(i1 - t0) * W + (j1 - t1)] = np.inf
+
+    for i, j in zip(np.asarray(ex_ii).tolist(), np.asarray(ex_jj).tolist()):
+        stamp(i, j)
+    es = []
+    for i in range(t0, t):                                      # :396-406
+        if stereo:
+            es.append((i, i))
+            d[(i - t0) * W + (i - t1)] = np.inf
+        for j in range(max(i - rad - 1, 0), i):
+            es.append((i, j))
+            es.append((j, i))
+            if (i - t0) * W + (j - t1) >= 0:
+                d[(i - t0) * W + (j - t1)] = np.inf
+    order = np.argsort(d, kind="stable")                        # :408 (ties: lowest index first)
+    for k in order.tolist():                                    # :409-433
+        if k >= cc:
+            continue
+        if d[k] > thresh:
+            continue
+        if len(es) > max_factors:
+            break
+        i, j = int(ii[k]), int(jj[k])
+        es.append((i, j))
+        es.append((j, i))
+        stamp(i, j)
+    if len(ii) > cc:                                            # :435-439
+        k = cc + int(np.argmin(d[cc:len(ii)]))
+        if d[k] < thresh and d[k] > 0:
+            es.append((int(ii[k]), int(jj[k])))
+            es.append((int(jj[k]), int(ii[k])))
+    es = np.asarray(es, np.int64).reshape(-1, 2)
+    return es[:, 0].copy(), es[:, 1].copy()
+
+
+def filter_repeated_edges(ii, jj, ex_ii, ex_jj):
+    """CovisibleGraph.__filter_repeated_edges, dbaf/covisible_graph.py:61-72: drop the new edges that the graph
+    already holds (active or inactive); order kept, duplicates inside the new list are not removed."""
+    have = set(zip(np.asarray(ex_ii).tolist(), np.asarray(ex_jj).tolist()))
+    keep = np.array([(int(i), int(j)) not in have for i, j in zip(ii, jj)], bool).reshape(-1)
+    return np.asarray(ii)[keep], np.asarray(jj)[keep]
