@@ -481,6 +481,49 @@ def bench_bacore(db, synth, cfg, dev, flush, steps):
     return out
 
 
+def bench_proximity(db, synth, dev, steps):
+    """edge selection for a new keyframe (dbaf_frontend.py:241: t0 = t-5, t1 = t-window) from the
+    DepthVideo buffers to the filtered edge list -- two frame_distance launches, the selection kernel, the duplicate
+    filter, one host read of the count -- against the numpy restatement of the reference's Python loops fed with the
+    same distances (the reference itself synchronises once per candidate and needs lietorch to import)."""
+    import dbaf_oracle as oracle
+    from dbaf_b200 import graph
+    win = synth.make_window("c2", seed=3)
+    T = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    poses, disps, intr = T(win["poses"]), T(win["disps"]), T(win["intrinsics"])
+    t = win["poses"].shape[0]
+    t0, t1 = t - 5, max(t - 12, 0)
+    act, bad, inac = (T(win["ii"][:20]), T(win["jj"][:20])), (T(win["ii"][20:24]), T(win["jj"][20:24])), (T(win["ii"][24:30]), T(win["jj"][24:30]))
+    kw = dict(rad=2, nms=1, beta=0.3, thresh=60.0, stereo=False, max_factors=48, skip_edge=[-4, -5, -6], frontend_window=5)
+
+    def ours():
+        return graph.proximity_factors(poses, disps, intr, t, t0, t1, act, bad, inac, **kw)
+
+    def port():
+        ci, cj, cc = oracle.proximity_candidates(t0, t1, t, kw["skip_edge"], kw["frontend_window"])
+        d = (0.5 * (db.frame_distance(poses, disps, intr, T(ci), T(cj), 0.3)
+                    + db.frame_distance(poses, disps, intr, T(cj), T(ci), 0.3))).cpu().numpy()
+        ei, ej = oracle.proximity_edges(d, ci, cj, cc, win["ii"][:30], win["jj"][:30], t0, t1, t, 2, 1, 60.0, False, 48)
+        return oracle.filter_repeated_edges(ei, ej, np.concatenate([win["ii"][:20], win["ii"][24:30]]),
+                                            np.concatenate([win["jj"][:20], win["jj"][24:30]]))
+
+    out = {}
+    for name, fn in (("ours_ms", ours), ("numpy_port_ms", port)):
+        ts = []
+        for it in range(3 + steps):
+            torch.cuda.synchronize()
+            a = time.perf_counter()
+            r = fn()
+            torch.cuda.synchronize()
+            if it >= 3:
+                ts.append((time.perf_counter() - a) * 1e3)
+        out[name] = statistics.mean(ts)
+        out["edges_selected"] = int(len(r[0]))
+    out["workload"] = f"c2 buffers, t = {t}, t0 = {t0}, t1 = {t1}: {(t - t0) * (t - t1)} grid candidates + 3 skip edges, 30 existing edges"
+    out["host_syncs"] = dict(ours=1, reference="one .item() per candidate, per stamp and per edge (dbaf/covisible_graph.py:61-72,384-431)")
+    return out
+
+
 def bench_altcorr(db, synth, dev, flush, steps):
     """BASELINE.json configs[3]: the on-the-fly correlation (altcorr_forward over the 4 feature-pooled levels,
     dbaf/modules/corr.py:91-139) against the materialised volume + lookup on the same 36-edge window."""
@@ -632,6 +675,7 @@ def main():
             flush = L2Flusher(dev)
             line["bacore"] = {cfg: bench_bacore(db, synth, cfg, dev, flush, min(args.steps, 10)) for cfg in ("c2_real", "c3")}
             line["c4_altcorr"] = bench_altcorr(db, synth, dev, flush, max(3, min(args.steps, 10)))
+            line["proximity"] = bench_proximity(db, synth, dev, max(3, min(args.steps, 10)))
     else:
         line, clk = bench_local(args, dev, rank, world)
 

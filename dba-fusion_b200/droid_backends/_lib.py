@@ -30,6 +30,10 @@ SIGNATURES = {
     "dbaf_last_error": (ctypes.c_char_p, []),
     "dbaf_set_option": (c_int, [ctypes.c_char_p, ctypes.c_char_p]),
     "dbaf_probe_fill": (c_int, [P, c_size_t, c_int, P]),
+    "dbaf_proximity_base_count": (c_int, [c_int, c_int, c_int, c_int]),
+    "dbaf_proximity_select": (c_int, [P, P, P, P, c_int, c_int, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_float,
+                                      c_int, c_int, P, P, P, c_int, P, P]),
+    "dbaf_filter_repeated_edges": (c_int, [P, P, P, c_int, P, P, c_int, P, P, P, P]),
     "dbaf_ba_schur": (c_int, [P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, P]),
     "dbaf_projmap": (c_int, [P, P, P, P, P, c_int, c_int, c_int, P, P, P]),
     "dbaf_frame_distance": (c_int, [P, P, P, P, P, c_int, c_int, c_int, c_float, P, P]),

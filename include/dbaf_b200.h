@@ -85,6 +85,33 @@ int dbaf_depth_filter(const float* poses, const float* disps, const float* intri
                       const int64_t* ix, const float* thresh, int n_idx, int n_frames,
                       int ht, int wd, float* counter, void* stream);
 
+/* ----------------------------------------------------------- frame-graph edges ---- */
+
+/* CovisibleGraph.add_proximity_factors, dbaf/covisible_graph.py:357-441 (a "next" row of the scope table): which
+ * edges to add, given the distances of the candidate pairs.  The candidates are the (t-t0) x (t-t1) grid in
+ * row-major order (cc = (t-t0)*(t-t1) entries: cand_ii[k] = t0 + k / (t-t1), cand_jj[k] = t1 + k % (t-t1)) followed
+ * by n_cand - cc "skip" pairs (:371-377); d1 (and d2, may be NULL) are their frame distances, d = 0.5 (d1 + d2)
+ * being DepthVideo.distance's bidirectional mean (dbaf/depth_video.py:255-261).  ex_ii/ex_jj: the edges the graph
+ * already holds (active, bad and inactive, :383-384).  The kernel applies the masks of :379-381, the suppression
+ * stamps of :386-394, emits the unconditional temporal (and stereo) edges of :396-406, runs the greedy sweep in
+ * ascending distance with its 2-D suppression (:408-433; ties go to the lower index, NaN last) and the closest
+ * skip edge (:435-439).  es_ii/es_jj [es_capacity] receive the list in the reference's order, *n_es its length
+ * (device int32); es_capacity >= dbaf_proximity_base_count(t0,t,rad,stereo) + 2*cc + 2; d_work: float[n_cand]
+ * device scratch.  One thread block; no host synchronisation (the reference does one per candidate). */
+int dbaf_proximity_base_count(int t0, int t, int rad, int stereo);
+int dbaf_proximity_select(const float* d1, const float* d2, const int64_t* cand_ii, const int64_t* cand_jj,
+                          int n_cand, int cc, const int64_t* ex_ii, const int64_t* ex_jj, int n_existing,
+                          int t0, int t1, int t, int rad, int nms, float thresh, int stereo, int max_factors,
+                          float* d_work, int64_t* es_ii, int64_t* es_jj, int es_capacity, int32_t* n_es,
+                          void* stream);
+
+/* CovisibleGraph.__filter_repeated_edges, dbaf/covisible_graph.py:61-72: the new edges (ii[k], jj[k]),
+ * k < min(*n_dev, n_max) (n_dev: device int32, may be NULL = n_max), that are not among ex_ii/ex_jj (the active and
+ * inactive edges), in their original order -> out_ii/out_jj [n_max], count in *n_out (device int32). */
+int dbaf_filter_repeated_edges(const int64_t* ii, const int64_t* jj, const int32_t* n_dev, int n_max,
+                               const int64_t* ex_ii, const int64_t* ex_jj, int n_existing, int64_t* out_ii,
+                               int64_t* out_jj, int32_t* n_out, void* stream);
+
 /* --------------------------------------------------------------- correlation ---- */
 
 /* droid_backends.corr_index_forward, src/droid.cpp:231-239, src/correlation_kernels.cu:19-70,126-155.

@@ -896,7 +896,7 @@ def proximity_edges(d, ii, jj, cc, ex_ii, ex_jj, t0, t1, t, rad, nms, thresh, st
         es.append((j, i))
         stamp(i, j)
     if len(ii) > cc:                                            # :435-439
-        k = cc + int(np.argmin(d[cc:len(ii)]))
+        k = cc + int(np.argsort(d[cc:len(ii)], kind="stable")[0])   # NaN sorts last, as in torch.argsort
         if d[k] < thresh and d[k] > 0:
             es.append((int(ii[k]), int(jj[k])))
             es.append((int(jj[k]), int(ii[k])))
