@@ -457,6 +457,7 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
 #include "ba_fast.cuh"
 #include "ba_banded.cuh"
 #include "ba_banded_reg.cuh"
+#include "ba_spike.cuh"
 #include "ba_lin2.cuh"
 #include "ba_schur_tc.cuh"
 
@@ -638,22 +639,84 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
     }
     BandPlan plan{};
     const bool single = options().band_single != 0;              // the one-CTA sweep (tests)
-    if (!single && P >= kBandTwistMinP && P >= 3 * B + 2) {
-      // two sweeps meeting at the separator [m, m+B)
-      const int m = (P - B) / 2;
-      plan.twisted = 1;
-      plan.m = m;
-      plan.part[0] = BandPart{0, m + B, m, 0};
-      plan.part[1] = BandPart{1, P - m, P - m - B, band_store_doubles(m + B, B)};
-      plan.sep = plan.part[1].store + band_store_doubles(P - m, B);
-    } else {
-      plan.part[0] = BandPart{0, P, P, 0};
-      plan.part[1] = plan.part[0];
-    }
-    // B <= 20: the sweep that keeps the window in registers; option band_sweep=smem keeps the shared-memory window
     const bool smem_sweep = B > kBandRegMaxB || options().band_smem != 0;
+    // ---- how the chain is cut: D domains (ba_spike.cuh), two sweeps meeting at one separator, or one sweep
+    SpikePlan sp{};
+    int D = 1;
+    const long long lfac_cap = (long long)(n + 1) * n + n;
+    if (!single && !options().band_twisted && !smem_sweep && B >= 1) {
+      const int n_min = B + 2;                                   // interiors longer than the band
+      const int d_max = (P + B) / (B + n_min);
+      int d_want = options().band_domains > 0 ? options().band_domains : (P + B) / (5 * std::max(B, 4));
+      D = std::min({d_want, d_max, kSpikeMaxD});
+      if (D < 3) D = 1;
+    }
+    if (D >= 3) {
+      const int NS = 6 * B, ld = spike_ld(NS);
+      auto even = [](long long x) { return (x + 1) & ~1LL; };
+      long long off = 0;
+      auto take = [&](long long doubles) { const long long o = off; off = even(off + doubles); return o; };
+      const int interior = P - (D - 1) * B;
+      int first = 0;
+      sp.D = D; sp.B = B; sp.mid = D / 2; sp.G = std::max(1, std::min(8, NS / 6));
+      sp.nlev = std::max(sp.mid - 1, D - 1 - sp.mid);
+      for (int d = 0; d < D; ++d) {
+        const int nd = interior / D + (d < interior % D ? 1 : 0);
+        BandPart& pt = plan.part[d];
+        pt.Plog = nd + B;
+        pt.n_elim = nd;
+        if (d < D - 1) {
+          pt.rev = 0;
+          pt.base = first;
+          pt.sep_first = first + nd;
+          sp.m[d + 1] = first + nd;
+        } else {
+          pt.rev = 1;
+          pt.base = P - 1;
+          pt.sep_first = sp.m[D - 1];
+        }
+        pt.store = take(band_store_doubles(pt.Plog, B));
+        pt.dump = take(band_dump_doubles(B));
+        first += nd + B;
+      }
+      for (int d = 1; d <= D - 2; ++d) {
+        sp.W[d] = take((long long)plan.part[d].n_elim * 6 * NS);
+        sp.Roff[d] = take((long long)NS * NS);
+        sp.SLL[d] = take((long long)NS * NS + NS);
+      }
+      for (int q = 1; q <= D - 1; ++q) {
+        sp.Lf[q] = take((long long)(NS + 2) * ld);
+        sp.X[q] = take((long long)NS * NS);
+        sp.U[q][0] = take((long long)NS * NS + NS);
+        sp.U[q][1] = take((long long)NS * NS + NS);
+      }
+      sp.xsep = take((long long)D * NS);
+      plan.flags = take(D + 4);
+      plan.twisted = 1;
+      if (off > lfac_cap) D = 1;                                 // does not fit the factorisation scratch: fewer sweeps
+    }
+    if (D < 3) {
+      plan = BandPlan{};
+      if (!single && P >= kBandTwistMinP && P >= 3 * B + 2) {
+        // two sweeps meeting at the separator [m, m+B)
+        const int m = (P - B) / 2;
+        plan.twisted = 1;
+        plan.m = m;
+        plan.sep = band_store_doubles(m + B, B) + band_store_doubles(P - m, B);
+        plan.flags = plan.sep + 2 * band_dump_doubles(B) + 6 * B;
+        plan.part[0] = BandPart{0, m + B, m, 0, m, 0, plan.sep};
+        plan.part[1] = BandPart{1, P - m, P - m - B, P - 1, m, band_store_doubles(m + B, B), plan.sep + band_dump_doubles(B)};
+        D = 2;
+      } else {
+        plan.part[0] = BandPart{0, P, P, 0, 0, 0, 0};
+        plan.part[1] = plan.part[0];
+        D = 1;
+      }
+    }
+    if (D >= 3) DBAF_CUDA(cudaMemsetAsync(ws.Lfac + plan.flags, 0, (size_t)(D + 4) * 8, st));
+    // B <= 20: the sweep that keeps the window in registers; option band_sweep=smem keeps the shared-memory window
     if (smem_sweep) {
-      k_solve_banded<<<plan.twisted ? 2 : 1, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
+      k_solve_banded<<<D, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
       DBAF_LAUNCH_CHECK("k_solve_banded");
     } else {
       const size_t rsm = std::max((size_t)NB * (2 * kPnS + 6) + 84 + 4 + (size_t)NB * (NB - 1) * 18 + NB * 42,
@@ -663,10 +726,51 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
         DBAF_CUDA(cudaFuncSetAttribute(k_solve_banded_reg, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
         reg_attr[dev_id & 63] = true;
       }
-      k_solve_banded_reg<<<plan.twisted ? 2 : 1, kBandThreads, rsm, st>>>(P, B, lm, ep, plan, ws);
+      k_solve_banded_reg<<<D, kBandThreads, rsm, st>>>(P, B, lm, ep, plan, ws);
       DBAF_LAUNCH_CHECK("k_solve_banded_reg");
     }
-    if (plan.twisted) {
+    if (D >= 3) {
+      const int NS = 6 * B, ld = spike_ld(NS);
+      static bool spike_attr[64] = {};
+      if (!spike_attr[dev_id & 63]) {
+        DBAF_CUDA(cudaFuncSetAttribute(k_spike_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_red_a, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_red_b, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_red_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_red_back, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_spike_back, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        spike_attr[dev_id & 63] = true;
+      }
+      const int n_mid = D - 2;
+      const int ncg = (NS + 29) / 30;
+      const size_t fsm = ((size_t)kSpikeRing * ((B + 1) * 36 + 6) + (size_t)(B + 1) * 192 + 4 * 192) * sizeof(double);
+      k_spike_fwd<<<dim3(ncg, n_mid), 128, fsm, st>>>(P, B, plan, sp, ws);
+      DBAF_LAUNCH_CHECK("k_spike_fwd");
+      const int gt = (NS + kGramTile - 1) / kGramTile;
+      k_spike_gram<<<dim3(gt * (gt + 1) / 2, n_mid), 256, 0, st>>>(B, plan, sp, ws);
+      DBAF_LAUNCH_CHECK("k_spike_gram");
+      const size_t asm_ = ((size_t)(NS + 1) * ld + NS + (size_t)5 * (kSpikeThreads / 32) * ld) * sizeof(double);
+      const size_t bsm = (size_t)NS * ld * sizeof(double);
+      for (int level = 0; level < sp.nlev; ++level) {
+        k_red_a<<<dim3(sp.G, 2), kSpikeThreads, asm_, st>>>(P, B, lm, ep, level, plan, sp, ws);
+        DBAF_LAUNCH_CHECK("k_red_a");
+        k_red_b<<<dim3(sp.G, 2), kSpikeThreads, bsm, st>>>(B, level, plan, sp, ws);
+        DBAF_LAUNCH_CHECK("k_red_b");
+      }
+      const size_t msm = ((size_t)(NS + 1) * ld + 2 * NS) * sizeof(double);
+      k_red_mid<<<1, kSpikeThreads, msm, st>>>(P, B, lm, ep, plan, sp, ws);
+      DBAF_LAUNCH_CHECK("k_red_mid");
+      if (sp.nlev > 0) {
+        k_red_back<<<2, kSpikeThreads, ((size_t)NS * ld + 3 * NS) * sizeof(double), st>>>(B, plan, sp, ws);
+        DBAF_LAUNCH_CHECK("k_red_back");
+      }
+      int nd_max = 0;
+      for (int d = 1; d <= D - 2; ++d) nd_max = std::max(nd_max, plan.part[d].n_elim);
+      k_spike_apply<<<dim3((6 * nd_max + 7) / 8, n_mid), 256, 0, st>>>(B, plan, sp, ws);
+      DBAF_LAUNCH_CHECK("k_spike_apply");
+      k_spike_back<<<D, 64, band_back_smem_doubles(B) * sizeof(double), st>>>(P, B, plan, sp, ws);
+      DBAF_LAUNCH_CHECK("k_spike_back");
+    } else if (D == 2) {
       const int ns = 6 * B;
       const size_t ssm = ((size_t)(ns + 1) * (ns | 1) + 2 * ns) * sizeof(double);
       static bool sep_attr[64] = {};

@@ -24,18 +24,25 @@ constexpr int kBandThreads = 512;
 constexpr int kBandTwistMinP = 64;   // below this the single sweep is just as fast
 
 // One sweep of the (possibly reversed) chain: logical block I is physical block  rev ? P-1-I : I.
+constexpr int kBandMaxParts = 16;
 struct BandPart {
   int rev;               // 1: bottom-up sweep
   int Plog;              // logical size of this part's leading submatrix (eliminated blocks + separator)
   int n_elim;            // number of block columns this sweep eliminates
+  int base;              // physical block of logical block 0: logical I is physical base + I (base - I when rev)
+  int sep_first;         // first physical block of the separator this sweep runs into
   long long store;       // offset (doubles) of this part's band store inside ws.Lfac
+  long long dump;        // offset (doubles) of this part's view of its separator: B*B*36 window dump + 6B rhs dump
 };
 struct BandPlan {
-  int twisted;           // 0: one CTA, everything (including the back-substitution) in k_solve_banded
-  int m;                 // first physical block of the separator
-  BandPart part[2];
-  long long sep;         // offset (doubles) of the separator exchange area inside ws.Lfac:
+  int twisted;           // 0: one CTA, everything (including the back-substitution) in the sweep kernel;
+                         // 1: several sweeps that leave their separator views for a second stage (two sweeps meeting
+                         //    at one separator: k_band_sep; more: the domain decomposition of ba_spike.cuh)
+  int m;                 // two sweeps: first physical block of the separator
+  BandPart part[kBandMaxParts];
+  long long sep;         // two sweeps: offset (doubles) of the exchange area inside ws.Lfac:
                          // 2 x (B*B*36 window dump + 6B rhs dump), 6B solution, 4 flags
+  long long flags;       // offset (doubles) of the int32 failure flags, one per sweep (then stage-specific ones)
 };
 __host__ __device__ inline long long band_store_doubles(int Plog, int B) { return (long long)Plog * (B + 1) * 36 + 12LL * Plog; }
 __host__ __device__ inline long long band_dump_doubles(int B) { return (long long)B * B * 36 + 6LL * B; }
@@ -75,7 +82,8 @@ __device__ void band_backsub(int Pphys, int B, const BandPart& pt, int m, const 
   double* xs = xsep + 6 * B;
   uint64_t* full = reinterpret_cast<uint64_t*>(xs + 8);
   uint64_t* empty = full + kBackDepth;
-  auto phys = [&](int I) { return pt.rev ? Pphys - 1 - I : I; };
+  auto phys = [&](int I) { return pt.rev ? pt.base - I : pt.base + I; };
+  (void)Pphys;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kBackDepth; ++i) {
@@ -236,7 +244,7 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
   double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
   double* y_g = dinv_g + 6 * P;
   // logical -> physical block index: p0 + sd * I
-  const int p0 = pt.rev ? Pphys - 1 : 0, sd = pt.rev ? -1 : 1;
+  const int p0 = pt.base, sd = pt.rev ? -1 : 1;
   auto slot = [&](int I, int K) { return Wd + ((size_t)(I % NB) * NB + (K % NB)) * 36; };
   const double epd = (double)ep, lmd = (double)lm;
 
@@ -511,13 +519,13 @@ k_solve_banded(int Pphys, int B, float lm, float ep, int rezero, BandPlan plan, 
   const bool ok = fail == 0;
   if (plan.twisted) {
     // leave this sweep's view of the separator (blocks [n_elim, Plog) of the window and their rhs) for k_band_sep
-    double* dump = ws.Lfac + plan.sep + (long long)blockIdx.x * band_dump_doubles(B);
+    double* dump = ws.Lfac + pt.dump;
     for (int e = tid; e < B * B * 36; e += nt) {
       const int blk = e / 36, ai = blk / B, ak = blk - ai * B;
       if (ai >= ak) dump[e] = slot(pt.n_elim + ai, pt.n_elim + ak)[e - blk * 36];
     }
     for (int e = tid; e < 6 * B; e += nt) dump[(size_t)B * B * 36 + e] = yw[((pt.n_elim + e / 6) % NB) * 6 + e % 6];
-    if (tid == 0) reinterpret_cast<int*>(ws.Lfac + plan.sep + 2 * band_dump_doubles(B) + 6 * B)[blockIdx.x] = ok ? 0 : 1;
+    if (tid == 0) reinterpret_cast<int*>(ws.Lfac + plan.flags)[blockIdx.x] = ok ? 0 : 1;
     return;
   }
   if (ok) {
@@ -588,9 +596,9 @@ k_band_back(int Pphys, int B, BandPlan plan, Ws ws) {
     // a pivot failed somewhere: the whole step is dropped (dx = 0), like the single sweep does
     for (int I = threadIdx.x; I < pt.n_elim * 6; I += blockDim.x) {
       const int J = I / 6;
-      ws.dx[6 * (pt.rev ? Pphys - 1 - J : J) + I % 6] = 0.0f;
+      ws.dx[6 * (pt.rev ? pt.base - J : pt.base + J) + I % 6] = 0.0f;
     }
     return;
   }
-  band_backsub(Pphys, B, pt, plan.m, xsep, smk, ws);
+  band_backsub(Pphys, B, pt, pt.sep_first, xsep, smk, ws);
 }

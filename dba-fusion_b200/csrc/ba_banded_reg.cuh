@@ -42,7 +42,7 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   double* Lband = ws.Lfac + pt.store;
   double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
   double* y_g = dinv_g + 6 * P;
-  const int p0 = pt.rev ? Pphys - 1 : 0, sd = pt.rev ? -1 : 1;
+  const int p0 = pt.base, sd = pt.rev ? -1 : 1;
   const double epd = (double)ep, lmd = (double)lm;
 
   // ---- static task of this thread
@@ -356,7 +356,7 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   const bool ok_all = fail == 0;
   if (plan.twisted) {
     // this sweep's view of the separator [n_elim, Plog): window blocks and rhs, for k_band_sep
-    double* dump = ws.Lfac + plan.sep + (long long)blockIdx.x * band_dump_doubles(B);
+    double* dump = ws.Lfac + pt.dump;
     if (ta >= 0) {
       const int oa = off_of(ta, jm), ob = off_of(tb, jm);
       if (oa < B && ob < B) {
@@ -376,7 +376,7 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
       }
     }
     for (int e = tid; e < 6 * B; e += nt) dump[(size_t)B * B * 36 + e] = yw[((pt.n_elim + e / 6) % NB) * 6 + e % 6];
-    if (tid == 0) reinterpret_cast<int*>(ws.Lfac + plan.sep + 2 * band_dump_doubles(B) + 6 * B)[blockIdx.x] = ok_all ? 0 : 1;
+    if (tid == 0) reinterpret_cast<int*>(ws.Lfac + plan.flags)[blockIdx.x] = ok_all ? 0 : 1;
     return;
   }
   if (ok_all) {

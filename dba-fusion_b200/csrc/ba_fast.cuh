@@ -174,7 +174,8 @@ __device__ __forceinline__ void factor_diag6(double* L, int ld, int j0, double* 
       if (c <= r) L[(size_t)(j0 + r) * ld + j0 + c] = a[r][c];
 }
 
-__device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* dinv, int* fail) {
+// factorisation part: on return (true) the lower triangle holds L, row n holds y = L^-1 b, dinv = 1 / diag(L)
+__device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fail) {
   const int tid = threadIdx.x, nt = blockDim.x;
   const int n = 6 * P;
   if (tid == 0) {
@@ -246,9 +247,12 @@ __device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* din
     }
     __syncthreads();
   }
-  // back-substitution L^T x = y, y = row n; block by block from the bottom
-  for (int i = tid; i < n; i += nt) x[i] = L[(size_t)n * ld + i];
-  __syncthreads();
+  return *fail == 0;
+}
+
+// back-substitution L^T x = y block by block from the bottom; x holds y on entry (visible to the whole CTA)
+__device__ void cholesky6_back(const double* L, int ld, int P, double* x, const double* dinv) {
+  const int tid = threadIdx.x, nt = blockDim.x;
   for (int J = P - 1; J >= 0; --J) {
     const int j0 = 6 * J;
     if (tid == 0) {
@@ -281,6 +285,15 @@ __device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* din
     }
     __syncthreads();
   }
+}
+
+__device__ bool cholesky6_solve(double* L, int ld, int P, double* x, double* dinv, int* fail) {
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int n = 6 * P;
+  if (!cholesky6_factor(L, ld, P, dinv, fail)) return false;
+  for (int i = tid; i < n; i += nt) x[i] = L[(size_t)n * ld + i];
+  __syncthreads();
+  cholesky6_back(L, ld, P, x, dinv);
   return true;
 }
 

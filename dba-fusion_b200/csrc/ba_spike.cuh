@@ -1,0 +1,530 @@
+// Domain-decomposed block-banded Cholesky solve, included by ba.cu after ba_banded_reg.cuh.
+//
+// The twisted factorisation runs two sweeps; a chain of P block columns still costs P/2 dependent steps on two
+// SMs.  Here the chain is cut into D domains by D-1 separators of B blocks each (B = block half-bandwidth):
+//
+//     [ I_0 | S_1 | I_1 | S_2 | ... | S_{D-1} | I_{D-1} ]
+//
+// Interiors are not coupled to each other, so D sweeps (the same kernels as before, one CTA each) eliminate them
+// at the same time: I_0 .. I_{D-2} top down, running into the separator on their right, I_{D-1} bottom up, running
+// into S_{D-1}.  A sweep's continuation into the separator it meets gives that separator's update for free (the
+// "dump" of the twisted scheme).  A middle domain I_d also touches the separator S_d on its LEFT through its first
+// B block rows; eliminating I_d couples S_d to itself and to S_{d+1} through the whole domain -- the "spike"
+//     W_d = G_d^-1 A(I_d, S_d)              (G_d the Cholesky factor of the interior, n_d x B blocks, dense)
+// which a second kernel computes by a blocked forward substitution with 6B right-hand sides from the band store of
+// the sweep; continuing that substitution through the rows of S_{d+1} yields the coupling block
+//     R(S_{d+1}, S_d) = - L(S_{d+1}, I_d) W_d,
+// a third kernel forms  W_d^T W_d  and  W_d^T y_d.  What is left is a block-tridiagonal SPD system over the
+// separators (6B x 6B dense blocks), eliminated from both ends towards the middle separator: per level every CTA of
+// a side factorises the current diagonal block redundantly in shared memory (no communication), solves its slice
+// of rows of X = R(t,s) L_s^-T, and after one kernel boundary forms its slice of the update X X^T of the next
+// diagonal block.  The middle block is solved densely, the chain is back-substituted, the interiors' right-hand
+// sides are corrected by  y_d -= W_d x(S_d), and D back-substitutions (k_spike_back, the streaming two-warp
+// routine of ba_banded.cuh) finish the solve.  Same arithmetic as a sequential Cholesky, reordered; replaces
+// Eigen::SimplicialLLT of the reference (src/droid_kernels.cu:1248-1269).
+#pragma once
+
+constexpr int kSpikeMaxD = kBandMaxParts;
+constexpr int kSpikeThreads = 256;
+
+struct SpikePlan {
+  int D, B, mid, G;               // domains, band, middle separator, CTAs per side in the reduced levels
+  int nlev;                       // levels of the two-sided elimination of the separator chain
+  int m[kSpikeMaxD];              // first physical block of separator s, s = 1 .. D-1
+  long long W[kSpikeMaxD];        // middle domain d: spike [n_d][6][NS] doubles
+  long long Roff[kSpikeMaxD];     // middle domain d: coupling block rows S_{d+1}, cols S_d, [NS][NS]
+  long long SLL[kSpikeMaxD];      // middle domain d: W^T W [NS][NS], then W^T y [NS]
+  long long Lf[kSpikeMaxD];       // separator s: factor [NS][ld], then y [NS], then 1/diag [NS]
+  long long X[kSpikeMaxD];        // separator s: X_s = R(t,s) L_s^-T, [NS][NS] (rows: unknowns of the next separator t)
+  long long U[kSpikeMaxD][2];     // separator s: update received from side 0 / side 1, [NS][NS] then rhs part [NS]
+  long long xsep;                 // [D][NS]: separator solutions, entry s
+};
+// flags (int32, at plan.flags): [0, D) sweeps, [D] reduced system, [D + 1] overall
+
+__host__ __device__ inline int spike_ld(int NS) { return NS | 1; }
+
+// --------------------------------------------------------------------------------------------- spike ----
+// grid (column groups, middle domains), 128 threads.  lane = right-hand-side column, warp w takes the panel
+// blocks L(I, I-o) with o % 4 == w.  Block rows of L come from the sweep's band store through a 4-deep cp.async
+// ring; the last B rows of W live in a shared-memory window.
+constexpr int kSpikeRing = 5;     // block rows in flight: three ahead, one in use, one still read by the row solver
+
+__global__ void __launch_bounds__(128)
+k_spike_fwd(int Pphys, int B, BandPlan plan, SpikePlan sp, Ws ws) {
+  extern __shared__ double sms[];
+  const int d = 1 + blockIdx.y;
+  const BandPart pt = plan.part[d];
+  const int tid = threadIdx.x, lane = tid & 31, wq = tid >> 5;
+  const int NS = 6 * B, n = 6 * Pphys;
+  const int ncg = gridDim.x;
+  const int NC = (NS + ncg - 1) / ncg;              // columns of this CTA: [c0, c0 + nc)
+  const int c0 = blockIdx.x * NC;
+  const int nc = min(NC, NS - c0);
+  const bool live = lane < nc;
+  const int nd = pt.n_elim, rows = pt.Plog;         // interior rows, then the B rows of the separator on the right
+  const int RD = (B + 1) * 36, SD = RD + 6;         // ring stage: block row of L | 1/diag
+  const int WB = B + 1;                             // window slots
+  double* ring = sms;                               // [kSpikeRing][SD]
+  double* win = ring + kSpikeRing * SD;             // [WB][6][32]
+  double* part = win + WB * 192;                    // [4][6][32]
+  const double* Lband = ws.Lfac + pt.store;
+  const double* dinv_g = Lband + (size_t)pt.Plog * RD;
+  double* Wg = ws.Lfac + sp.W[d];
+  double* Ro = ws.Lfac + sp.Roff[d];
+  const int mL = sp.m[d];                           // first physical block of the separator on the left
+
+  auto request = [&](int I) {
+    if (I < rows) {
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (I % kSpikeRing) * SD);
+      const double* src = Lband + (size_t)I * RD;
+      for (int q = tid; q < RD / 2; q += 128)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + q * 16), "l"(src + 2 * q) : "memory");
+      if (tid < 3 && I < nd)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + (RD + 2 * tid) * 8), "l"(dinv_g + 6 * I + 2 * tid) : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+  for (int I = 0; I < 3; ++I) request(I);
+  for (int I = 0; I < rows; ++I) {
+    request(I + 3);
+    asm volatile("cp.async.wait_group 3;" ::: "memory");          // everything but the 3 newest groups: row I is in
+    // right-hand side of this block row: A(I, S_left), non-zero only within the band (I < B)
+    double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    if (wq == 0 && live && I < B && I < nd) {
+      const int pr = pt.rev ? pt.base - I : pt.base + I;
+      const double* src = ws.H + (size_t)(6 * pr) * n + 6 * mL + c0 + lane;
+#pragma unroll
+      for (int r = 0; r < 6; ++r) a[r] = src[(size_t)r * n];
+    }
+    __syncthreads();                                  // ring stage visible; previous row's window entry visible
+    const double* st = ring + (I % kSpikeRing) * SD;
+    double acc[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
+    // separator rows only see the interior: o >= I - nd + 1
+    const int o_lo = max(1, I - nd + 1), o_hi = min(B, I);
+    for (int o = o_lo + ((wq - o_lo) & 3); o <= o_hi; o += 4) {
+      const double* Lt = st + o * 36;                 // transposed panel block: Lt[c * 6 + r] = L(I, I-o)[r][c]
+      const double* wv = win + ((I - o) % WB) * 192 + lane;
+#pragma unroll
+      for (int c = 0; c < 6; ++c) {
+        const double x = wv[c * 32];
+        const double2 l0 = *reinterpret_cast<const double2*>(Lt + c * 6);
+        const double2 l1 = *reinterpret_cast<const double2*>(Lt + c * 6 + 2);
+        const double2 l2 = *reinterpret_cast<const double2*>(Lt + c * 6 + 4);
+        acc[0] = fma(l0.x, x, acc[0]);
+        acc[1] = fma(l0.y, x, acc[1]);
+        acc[2] = fma(l1.x, x, acc[2]);
+        acc[3] = fma(l1.y, x, acc[3]);
+        acc[4] = fma(l2.x, x, acc[4]);
+        acc[5] = fma(l2.y, x, acc[5]);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 6; ++r) part[(wq * 6 + r) * 32 + lane] = acc[r];
+    __syncthreads();
+    if (wq == 0 && live) {
+      double x[6];
+#pragma unroll
+      for (int r = 0; r < 6; ++r)
+        x[r] = a[r] - (part[r * 32 + lane] + part[(6 + r) * 32 + lane] + part[(12 + r) * 32 + lane] + part[(18 + r) * 32 + lane]);
+      if (I < nd) {
+        const double* Ld = st;                        // diagonal factor, row-major lower
+        const double* di = st + RD;
+#pragma unroll
+        for (int c = 0; c < 6; ++c) {
+          x[c] *= di[c];
+#pragma unroll
+          for (int r = 0; r < 6; ++r)
+            if (r > c) x[r] = fma(-Ld[r * 6 + c], x[c], x[r]);
+        }
+        double* wo = win + (I % WB) * 192 + lane;
+#pragma unroll
+        for (int r = 0; r < 6; ++r) {
+          wo[r * 32] = x[r];
+          Wg[((size_t)I * 6 + r) * NS + c0 + lane] = x[r];
+        }
+      } else {
+#pragma unroll
+        for (int r = 0; r < 6; ++r) Ro[((size_t)(I - nd) * 6 + r) * NS + c0 + lane] = x[r];
+      }
+    }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+// W^T W (lower tiles and their mirror images) and W^T y of a middle domain.  grid (10 tiles, middle domains)
+constexpr int kGramTile = 32;
+__global__ void __launch_bounds__(256)
+k_spike_gram(int B, BandPlan plan, SpikePlan sp, Ws ws) {
+  __shared__ double Wi[32][kGramTile + 1], Wj[32][kGramTile + 1];
+  const int d = 1 + blockIdx.y;
+  const BandPart pt = plan.part[d];
+  const int NS = 6 * B;
+  const int nt = (NS + kGramTile - 1) / kGramTile;
+  int ti = 0, rest = blockIdx.x;                     // lower-triangular tile (ti >= tj)
+  while (rest > ti) { rest -= ti + 1; ++ti; }
+  const int tj = rest;
+  if (ti >= nt) return;
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int K = 6 * pt.n_elim;
+  const double* Wg = ws.Lfac + sp.W[d];
+  const double* y_g = ws.Lfac + pt.store + (size_t)pt.Plog * (B + 1) * 36 + 6 * pt.Plog;
+  double* S = ws.Lfac + sp.SLL[d];
+  double acc[2][2] = {{0.0, 0.0}, {0.0, 0.0}};
+  double gy[2] = {0.0, 0.0};
+  const int i0 = ti * kGramTile, j0 = tj * kGramTile;
+  for (int k0 = 0; k0 < K; k0 += 32) {
+    __syncthreads();
+    for (int e = tid; e < 32 * kGramTile; e += 256) {
+      const int kk = e / kGramTile, c = e - kk * kGramTile;
+      const bool okk = k0 + kk < K;
+      Wi[kk][c] = (okk && i0 + c < NS) ? Wg[(size_t)(k0 + kk) * NS + i0 + c] : 0.0;
+      Wj[kk][c] = (okk && j0 + c < NS) ? Wg[(size_t)(k0 + kk) * NS + j0 + c] : 0.0;
+    }
+    __syncthreads();
+    const int kn = min(32, K - k0);
+    for (int kk = 0; kk < kn; ++kk) {
+      const double a0 = Wi[kk][ty], a1 = Wi[kk][ty + 16], b0 = Wj[kk][tx], b1 = Wj[kk][tx + 16];
+      acc[0][0] = fma(a0, b0, acc[0][0]);
+      acc[0][1] = fma(a0, b1, acc[0][1]);
+      acc[1][0] = fma(a1, b0, acc[1][0]);
+      acc[1][1] = fma(a1, b1, acc[1][1]);
+      if (tj == 0 && tx == 0) {
+        const double yv = y_g[k0 + kk];
+        gy[0] = fma(a0, yv, gy[0]);
+        gy[1] = fma(a1, yv, gy[1]);
+      }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 2; ++u)
+#pragma unroll
+    for (int v = 0; v < 2; ++v) {
+      const int i = i0 + ty + 16 * u, j = j0 + tx + 16 * v;
+      if (i < NS && j < NS) {
+        S[(size_t)i * NS + j] = acc[u][v];
+        if (ti != tj) S[(size_t)j * NS + i] = acc[u][v];
+      }
+    }
+  if (tj == 0 && tx == 0) {
+#pragma unroll
+    for (int u = 0; u < 2; ++u)
+      if (i0 + ty + 16 * u < NS) S[(size_t)NS * NS + i0 + ty + 16 * u] = gy[u];
+  }
+}
+
+// --------------------------------------------------------------------------- reduced (separator) system ----
+// Entry (i, j), j <= i, of the current diagonal block of separator s, and entry i of its right-hand side:
+// what the sweeps left, minus the spike term of the domain on its right, minus the updates of the chain so far.
+struct SepAsm {
+  const double* dumpA;      // top-down sweep of domain s-1
+  const double* dumpR;      // bottom-up sweep (s == D-1 only), else nullptr
+  const double* sll;        // W^T W of domain s (middle domains), else nullptr
+  const double* u0;         // update from side 0, else nullptr
+  const double* u1;         // update from side 1, else nullptr
+  int m;                    // first physical block of the separator
+};
+__device__ __forceinline__ SepAsm sep_asm(int s, const BandPlan& plan, const SpikePlan& sp, const Ws& ws) {
+  SepAsm a;
+  a.dumpA = ws.Lfac + plan.part[s - 1].dump;
+  a.dumpR = s == sp.D - 1 ? ws.Lfac + plan.part[sp.D - 1].dump : nullptr;
+  a.sll = s <= sp.D - 2 ? ws.Lfac + sp.SLL[s] : nullptr;
+  a.u0 = (s > 1 && s <= sp.mid) ? ws.Lfac + sp.U[s][0] : nullptr;
+  a.u1 = (s < sp.D - 1 && s >= sp.mid) ? ws.Lfac + sp.U[s][1] : nullptr;
+  a.m = sp.m[s];
+  return a;
+}
+__device__ __forceinline__ double sep_entry(const SepAsm& a, int i, int j, int B, int n, float lm, float ep, const Ws& ws) {
+  const int NS = 6 * B;
+  const int bi = i / 6, r = i - 6 * bi, bj = j / 6, c = j - 6 * bj;
+  double v = a.dumpA[(size_t)(bi * B + bj) * 36 + r * 6 + c];
+  if (a.dumpR) {
+    // the bottom-up sweep works on the block-reversed ordering: physical block (bi, bj), bi >= bj, is the transpose of
+    // its logical block (B-1-bj, B-1-bi); both sweeps carry the damped A_ss, counted once
+    const int brc = bi == bj ? r * 6 + c : c * 6 + r;
+    double h = ws.H[(size_t)(6 * (a.m + bi) + r) * n + 6 * (a.m + bj) + c];
+    if (i == j) h += (double)ep + (double)lm * h;
+    v += a.dumpR[(size_t)((B - 1 - bj) * B + (B - 1 - bi)) * 36 + brc] - h;
+  }
+  if (a.sll) v -= a.sll[(size_t)i * NS + j];
+  if (a.u0) v -= a.u0[(size_t)i * NS + j];
+  if (a.u1) v -= a.u1[(size_t)i * NS + j];
+  return v;
+}
+__device__ __forceinline__ double sep_rhs(const SepAsm& a, int i, int B, const Ws& ws) {
+  const int NS = 6 * B;
+  double v = a.dumpA[(size_t)B * B * 36 + i];
+  if (a.dumpR) {
+    const int bi = i / 6, r = i - 6 * bi;
+    v += a.dumpR[(size_t)B * B * 36 + (B - 1 - bi) * 6 + r] - ws.v[6 * a.m + i];
+  }
+  if (a.sll) v -= a.sll[(size_t)NS * NS + i];
+  if (a.u0) v -= a.u0[(size_t)NS * NS + i];
+  if (a.u1) v -= a.u1[(size_t)NS * NS + i];
+  return v;
+}
+
+// which separator a side works on at a level, and its neighbour towards the middle
+__device__ __forceinline__ bool chain_step(const SpikePlan& sp, int level, int side, int& s, int& t) {
+  if (side == 0) { s = 1 + level; t = s + 1; return s <= sp.mid - 1; }
+  s = sp.D - 1 - level; t = s - 1;
+  return s >= sp.mid + 1;
+}
+
+// level, part a: factor the diagonal block (every CTA of the side, redundantly), then this CTA's rows of
+// X = R(t,s) L_s^-T and of the right-hand-side update X y_s.  grid (G, 2)
+__global__ void __launch_bounds__(kSpikeThreads)
+k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePlan sp, Ws ws) {
+  extern __shared__ double smr[];
+  __shared__ int fail;
+  int s, t;
+  if (!chain_step(sp, level, blockIdx.y, s, t)) return;
+  const int side = blockIdx.y;
+  const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, wid = tid >> 5;
+  const int NS = 6 * B, n = 6 * Pphys, ld = spike_ld(NS);
+  double* L = smr;                                   // (NS + 1) x ld
+  double* dinv = L + (size_t)(NS + 1) * ld;          // NS
+  double* xs = dinv + NS;                            // rows of X of this CTA: [rps][ld]
+  const SepAsm as = sep_asm(s, plan, sp, ws);
+  for (int e = tid; e < NS * NS; e += nt) {
+    const int i = e / NS, j = e - i * NS;
+    if (j <= i) L[(size_t)i * ld + j] = sep_entry(as, i, j, B, n, lm, ep, ws);
+  }
+  for (int i = tid; i < NS; i += nt) L[(size_t)NS * ld + i] = sep_rhs(as, i, B, ws);
+  __syncthreads();
+  const bool ok = cholesky6_factor(L, ld, B, dinv, &fail);
+  __syncthreads();
+  int* flags = reinterpret_cast<int*>(ws.Lfac + plan.flags);
+  if (!ok) {
+    if (tid == 0 && blockIdx.x == 0) atomicExch(&flags[sp.D], 1);
+    return;
+  }
+  double* Lf = ws.Lfac + sp.Lf[s];
+  if (blockIdx.x == 0) {                              // keep the factor, y and 1/diag for the back-substitution
+    for (int e = tid; e < NS * NS; e += nt) {
+      const int i = e / NS, j = e - i * NS;
+      if (j <= i) Lf[(size_t)i * ld + j] = L[(size_t)i * ld + j];
+    }
+    for (int i = tid; i < NS; i += nt) {
+      Lf[(size_t)NS * ld + i] = L[(size_t)NS * ld + i];
+      Lf[(size_t)(NS + 1) * ld + i] = dinv[i];
+    }
+  }
+  // rows [i_lo, i_hi) of X: x L^T = a, a = row of R(t,s).  Five rows per warp, six lanes per row (one per column of
+  // the current 6-wide block): the lanes of a row split the dot products, lane c == 0 finishes the block.
+  const int rps = (NS + gridDim.x - 1) / gridDim.x;
+  const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
+  const double* Rts = side == 0 ? ws.Lfac + sp.Roff[s] : ws.Lfac + sp.Roff[t];
+  const int rw = lane / 6, cw = lane - 6 * rw;       // row within the warp (0..4), column within the block
+  const int rows_per_pass = 5 * (nt / 32);
+  for (int base = i_lo; base < i_hi; base += rows_per_pass) {
+    const int li = wid * 5 + rw;                     // local row of this pass
+    const int i = base + li;
+    const bool act = rw < 5 && i < i_hi;
+    double* xr = xs + (size_t)(act ? li : 0) * ld;
+    for (int J = 0; J < B; ++J) {
+      double sum = 0.0;
+      if (act) {
+        const int c = 6 * J + cw;
+        // A(t,s)[i][c]: side 0 reads Roff[s] as stored (rows: S_{s+1}), side 1 the transpose of Roff[t] (rows: S_s)
+        sum = side == 0 ? Rts[(size_t)i * NS + c] : Rts[(size_t)c * NS + i];
+        const double* lc = L + (size_t)c * ld;
+        double s0 = 0.0, s1 = 0.0;
+        int k = 0;
+        for (; k + 1 < 6 * J; k += 2) {
+          s0 = fma(xr[k], lc[k], s0);
+          s1 = fma(xr[k + 1], lc[k + 1], s1);
+        }
+        sum -= s0 + s1;
+      }
+      // finish the 6x6 triangular solve of the block on the lanes of the row: column sweep through shuffles
+#pragma unroll
+      for (int c2 = 0; c2 < 6; ++c2) {
+        const int srcl = rw * 6 + c2;
+        double xc = sum * (act ? dinv[6 * J + c2] : 0.0);
+        xc = __shfl_sync(0xffffffffu, xc, srcl);                    // x[c2] of this row, final
+        if (act && cw > c2) sum = fma(-xc, L[(size_t)(6 * J + cw) * ld + 6 * J + c2], sum);
+        if (act && cw == c2) { sum = xc; }
+      }
+      if (act) xr[6 * J + cw] = sum;
+      __syncwarp();
+    }
+    // rows of this pass: X to global, and their entry of X y_s
+    double* Xg = ws.Lfac + sp.X[s];
+    double* Ug = ws.Lfac + sp.U[t][side];
+    double dot = 0.0;
+    if (act) {
+      for (int k = cw; k < NS; k += 6) {
+        Xg[(size_t)i * NS + k] = xr[k];
+        dot = fma(xr[k], L[(size_t)NS * ld + k], dot);
+      }
+    }
+    double tot = 0.0;                                 // sum over the six lanes of the row (all lanes take part)
+#pragma unroll
+    for (int q = 0; q < 6; ++q) tot += __shfl_sync(0xffffffffu, dot, (rw * 6 + q) & 31);
+    if (act && cw == 0) Ug[(size_t)NS * NS + i] = tot;
+    __syncwarp();
+  }
+}
+
+// level, part b: this CTA's rows of the update  U(t) = X_s X_s^T  (lower triangle).  grid (G, 2)
+__global__ void __launch_bounds__(kSpikeThreads)
+k_red_b(int B, int level, BandPlan plan, SpikePlan sp, Ws ws) {
+  extern __shared__ double smx[];
+  int s, t;
+  if (!chain_step(sp, level, blockIdx.y, s, t)) return;
+  const int side = blockIdx.y;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int NS = 6 * B, ld = spike_ld(NS);
+  const int* flags = reinterpret_cast<const int*>(ws.Lfac + plan.flags);
+  if (flags[sp.D] != 0) return;
+  const double* Xg = ws.Lfac + sp.X[s];
+  double* Ug = ws.Lfac + sp.U[t][side];
+  for (int e = tid; e < NS * NS; e += nt) {
+    const int i = e / NS, k = e - i * NS;
+    smx[(size_t)i * ld + k] = Xg[e];
+  }
+  __syncthreads();
+  const int rps = (NS + gridDim.x - 1) / gridDim.x;
+  const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
+  for (int e = tid; e < (i_hi - i_lo) * NS; e += nt) {
+    const int i = i_lo + e / NS, j = e % NS;
+    if (j > i) continue;
+    const double* xi = smx + (size_t)i * ld;
+    const double* xj = smx + (size_t)j * ld;
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int k = 0;
+    for (; k + 3 < NS; k += 4) {
+      s0 = fma(xi[k], xj[k], s0);
+      s1 = fma(xi[k + 1], xj[k + 1], s1);
+      s2 = fma(xi[k + 2], xj[k + 2], s2);
+      s3 = fma(xi[k + 3], xj[k + 3], s3);
+    }
+    for (; k < NS; ++k) s0 = fma(xi[k], xj[k], s0);
+    Ug[(size_t)i * NS + j] = (s0 + s1) + (s2 + s3);
+  }
+}
+
+// the middle separator: dense solve; decides whether the whole step is kept.  one CTA
+__global__ void __launch_bounds__(kSpikeThreads)
+k_red_mid(int Pphys, int B, float lm, float ep, BandPlan plan, SpikePlan sp, Ws ws) {
+  extern __shared__ double smm[];
+  __shared__ int fail;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int NS = 6 * B, n = 6 * Pphys, ld = spike_ld(NS), s = sp.mid;
+  double* L = smm;
+  double* x = L + (size_t)(NS + 1) * ld;
+  double* dinv = x + NS;
+  const SepAsm as = sep_asm(s, plan, sp, ws);
+  for (int e = tid; e < NS * NS; e += nt) {
+    const int i = e / NS, j = e - i * NS;
+    if (j <= i) L[(size_t)i * ld + j] = sep_entry(as, i, j, B, n, lm, ep, ws);
+  }
+  for (int i = tid; i < NS; i += nt) L[(size_t)NS * ld + i] = sep_rhs(as, i, B, ws);
+  __syncthreads();
+  bool ok = cholesky6_solve(L, ld, B, x, dinv, &fail);
+  __syncthreads();
+  int* flags = reinterpret_cast<int*>(ws.Lfac + plan.flags);
+  for (int q = 0; q <= sp.D; ++q) ok = ok && flags[q] == 0;
+  double* xsep = ws.Lfac + sp.xsep + (size_t)s * NS;
+  for (int i = tid; i < NS; i += nt) {
+    xsep[i] = ok ? x[i] : 0.0;
+    ws.dx[6 * sp.m[s] + i] = ok ? (float)x[i] : 0.0f;
+  }
+  if (tid == 0) {
+    flags[sp.D + 1] = ok ? 0 : 1;
+    if (!ok) atomicAdd(&ws.info[1], 1);
+  }
+}
+
+// back-substitution of the separator chain, outwards from the middle: x_s = L_s^-T (y_s - X_s^T x_t).  grid 2
+__global__ void __launch_bounds__(kSpikeThreads)
+k_red_back(int B, BandPlan plan, SpikePlan sp, Ws ws) {
+  extern __shared__ double smk2[];
+  const int side = blockIdx.x;
+  const int tid = threadIdx.x, nt = blockDim.x;
+  const int NS = 6 * B, ld = spike_ld(NS);
+  const int* flags = reinterpret_cast<const int*>(ws.Lfac + plan.flags);
+  const bool ok = flags[sp.D + 1] == 0;
+  double* L = smk2;                                  // NS x ld
+  double* x = L + (size_t)NS * ld;
+  double* dinv = x + NS;
+  double* xt = dinv + NS;
+  const int first = side == 0 ? sp.mid - 1 : sp.mid + 1, step = side == 0 ? -1 : 1;
+  for (int s = first; s >= 1 && s <= sp.D - 1; s += step) {
+    const int t = s - step;                           // the neighbour towards the middle, already solved
+    double* xs_g = ws.Lfac + sp.xsep + (size_t)s * NS;
+    if (!ok) {
+      for (int i = tid; i < NS; i += nt) {
+        xs_g[i] = 0.0;
+        ws.dx[6 * sp.m[s] + i] = 0.0f;
+      }
+      continue;
+    }
+    const double* Lf = ws.Lfac + sp.Lf[s];
+    const double* Xg = ws.Lfac + sp.X[s];
+    const double* xt_g = ws.Lfac + sp.xsep + (size_t)t * NS;
+    __syncthreads();
+    for (int e = tid; e < NS * NS; e += nt) {
+      const int i = e / NS, j = e - i * NS;
+      if (j <= i) L[(size_t)i * ld + j] = Lf[(size_t)i * ld + j];
+    }
+    for (int i = tid; i < NS; i += nt) {
+      dinv[i] = Lf[(size_t)(NS + 1) * ld + i];
+      xt[i] = xt_g[i];
+    }
+    __syncthreads();
+    for (int k = tid; k < NS; k += nt) {
+      double sum = Lf[(size_t)NS * ld + k];
+      for (int i = 0; i < NS; ++i) sum = fma(-Xg[(size_t)i * NS + k], xt[i], sum);
+      x[k] = sum;
+    }
+    __syncthreads();
+    cholesky6_back(L, ld, B, x, dinv);
+    for (int i = tid; i < NS; i += nt) {
+      xs_g[i] = x[i];
+      ws.dx[6 * sp.m[s] + i] = (float)x[i];
+    }
+    __syncthreads();                                  // xs_g is read as x_t by the next separator of this side
+    __threadfence_block();
+  }
+}
+
+// y_d -= W_d x(S_d) for the middle domains.  grid (row groups, middle domains), one warp per scalar row
+__global__ void __launch_bounds__(256)
+k_spike_apply(int B, BandPlan plan, SpikePlan sp, Ws ws) {
+  const int d = 1 + blockIdx.y;
+  const BandPart pt = plan.part[d];
+  const int NS = 6 * B;
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (row >= 6 * pt.n_elim) return;
+  const int* flags = reinterpret_cast<const int*>(ws.Lfac + plan.flags);
+  if (flags[sp.D + 1] != 0) return;
+  const double* Wg = ws.Lfac + sp.W[d] + (size_t)row * NS;
+  const double* xs = ws.Lfac + sp.xsep + (size_t)d * NS;
+  double sum = 0.0;
+  for (int c = lane; c < NS; c += 32) sum = fma(Wg[c], xs[c], sum);
+  sum = warp_sum_d(sum);
+  if (lane == 0) {
+    double* y_g = ws.Lfac + pt.store + (size_t)pt.Plog * (B + 1) * 36 + 6 * pt.Plog;
+    y_g[row] -= sum;
+  }
+}
+
+// the D interior back-substitutions.  grid D, 64 threads
+__global__ void __launch_bounds__(64)
+k_spike_back(int Pphys, int B, BandPlan plan, SpikePlan sp, Ws ws) {
+  extern __shared__ double smk3[];
+  const int d = blockIdx.x;
+  const BandPart pt = plan.part[d];
+  const int* flags = reinterpret_cast<const int*>(ws.Lfac + plan.flags);
+  if (flags[sp.D + 1] != 0) {
+    for (int I = threadIdx.x; I < pt.n_elim * 6; I += blockDim.x) {
+      const int J = I / 6;
+      ws.dx[6 * (pt.rev ? pt.base - J : pt.base + J) + I % 6] = 0.0f;
+    }
+    return;
+  }
+  const int s = d == sp.D - 1 ? sp.D - 1 : d + 1;     // the separator this part's sweep ran into
+  band_backsub(Pphys, B, pt, pt.sep_first, ws.Lfac + sp.xsep + (size_t)s * 6 * B, smk3, ws);
+}

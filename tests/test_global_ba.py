@@ -376,6 +376,71 @@ def test_banded_solvers_on_random_band_systems(dev, db, oracle, synth, P, B):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("P,B,D", [(128, 20, 3), (203, 13, 5), (300, 5, 12), (400, 20, 8), (999, 20, 8), (999, 20, 16),
+                                   (999, 20, 0), (96, 1, 16), (64, 3, 7), (250, 10, 4), (130, 6, 3)])
+def test_domain_decomposed_banded_solve(dev, db, oracle, synth, P, B, D):
+    """The banded solve cut into D domains (ba_spike.cuh: D sweeps, spikes of the middle domains, two-sided
+    elimination of the separator chain): dx against numpy's dense float64 solve on random block-banded SPD systems,
+    at the size and band of the global-BA workload (P = 999, B = 20) among others; D = 0 is the automatic choice.
+    A non-positive pivot anywhere (interior, separator) drops the whole step."""
+    rng = np.random.default_rng(1000 * P + 10 * B + D)
+    w = synth.make_window("tiny", seed=1, n_extra_frames=P + 1 - 5, graph="banded", reach=1)
+    assert w["t1"] - w["t0"] == P
+    n = 6 * P
+    blk = np.arange(n) // 6
+    # G G^T with G banded (half the band) gives an SPD matrix of block bandwidth <= B without forming n x n products
+    H = np.zeros((n, n))
+    hb = B // 2 + (B % 2)
+    G = rng.normal(0, 1, (n, 6 * (2 * hb + 1)))
+    for I in range(P):
+        lo, hi = max(0, I - hb), min(P, I + hb + 1)
+        Gi = G[6 * I:6 * I + 6, :6 * (hi - lo)]
+        for J in range(max(0, I - B), I + 1):
+            lj, hj = max(0, J - hb), min(P, J + hb + 1)
+            a, b = max(lo, lj), min(hi, hj)
+            if a < b:
+                Gj = G[6 * J:6 * J + 6, :6 * (hj - lj)]
+                blkv = Gi[:, 6 * (a - lo):6 * (b - lo)] @ Gj[:, 6 * (a - lj):6 * (b - lj)].T
+                H[6 * I:6 * I + 6, 6 * J:6 * J + 6] = blkv
+                H[6 * J:6 * J + 6, 6 * I:6 * I + 6] = blkv.T
+    H[np.abs(blk[:, None] - blk[None, :]) > B] = 0.0
+    H += np.diag(rng.uniform(1.0, 2.0, n)) * (6 * (2 * hb + 1)) * 0.3
+    v = rng.normal(0, 1, n)
+    want, ok = oracle.damped_solve(H, v, 1e-4, 0.1)
+    assert ok
+    t = to_torch(w, dev)
+    win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                     t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+    win.prepare()
+    Hd, vd = torch.from_numpy(H).to(dev), torch.from_numpy(v).to(dev)
+    out = {}
+    for impl, dom in (("auto", D), ("twisted", 0), ("single", 0)):
+        db.set_option("band_impl", impl)
+        db.set_option("band_domains", str(dom))
+        win.H().copy_(Hd)
+        win.v().copy_(vd)
+        win.solve(1e-4, 0.1, band=B)
+        assert int(win.info().cpu()[1]) == 0
+        out[impl] = win.dx().cpu().numpy().reshape(-1).copy()
+        assert relerr(out[impl], want) < 2e-6, (impl, relerr(out[impl], want))
+    from helpers import record
+    record(f"spike_solve[P={P},B={B},D={D}]", spike=relerr(out["auto"], want), twisted=relerr(out["twisted"], want),
+           single=relerr(out["single"], want))
+    # failures: a bad pivot inside a middle domain, inside a separator, inside the last domain
+    db.set_option("band_impl", "auto")
+    db.set_option("band_domains", str(D))
+    fails = 0
+    for pos in (P // 2, P // 3, P - 2, 1):
+        win.H().copy_(Hd)
+        win.v().copy_(vd)
+        win.H()[6 * pos, 6 * pos] = -1.0e9
+        win.solve(1e-4, 0.1, band=B)
+        fails += 1
+        assert int(win.info().cpu()[1]) == fails, pos
+        assert float(win.dx().abs().max()) == 0.0, pos
+
+
+@pytest.mark.gpu
 def test_c5_full_size_properties(dev, db, synth):
     """BASELINE.json configs[4] at full size (1000 keyframes, 19 890 edges, 64x64): too large for the oracle, so
     the checks are size-independent properties: the reduced system of two shards sums to the unsharded one
