@@ -234,13 +234,22 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
 #pragma unroll
           for (int kk = 0; kk < 6; ++kk) a[kk] = lr[kk];
           const int cmax = min(ro, mrows - 2);
-          for (int co = tx; co <= cmax; co += 16) {
-            if (ro < 6 && co < 6) continue;            // next diagonal block: look-ahead warp
-            const double* lc = L + (size_t)(r0 + co) * ld + j0;
-            double sum = 0.0;
+          double* out = L + (size_t)(r0 + ro) * ld + r0;
+          // two columns per pass: independent dot products keep the fp64 pipe busy while the loads are in flight
+          for (int co = tx; co <= cmax; co += 32) {
+            const int c2 = co + 16;
+            const bool do1 = !(ro < 6 && co < 6);      // next diagonal block: look-ahead warp
+            const bool do2 = c2 <= cmax;
+            const double* lc1 = L + (size_t)(r0 + co) * ld + j0;
+            const double* lc2 = L + (size_t)(r0 + (do2 ? c2 : co)) * ld + j0;
+            double s1 = 0.0, s2 = 0.0;
 #pragma unroll
-            for (int kk = 0; kk < 6; ++kk) sum += a[kk] * lc[kk];
-            L[(size_t)(r0 + ro) * ld + r0 + co] -= sum;
+            for (int kk = 0; kk < 6; ++kk) {
+              s1 = fma(a[kk], lc1[kk], s1);
+              s2 = fma(a[kk], lc2[kk], s2);
+            }
+            if (do1) out[co] -= s1;
+            if (do2) out[c2] -= s2;
           }
         }
       }

@@ -25,7 +25,7 @@
 #pragma once
 
 constexpr int kSpikeMaxD = kBandMaxParts;
-constexpr int kSpikeThreads = 256;
+constexpr int kSpikeThreads = 512;   // 4 warps per scheduler: the dense kernels are chains of short shared-memory round trips
 
 struct SpikePlan {
   int D, B, mid, G;               // domains, band, middle separator, CTAs per side in the reduced levels
@@ -155,7 +155,7 @@ k_spike_fwd(int Pphys, int B, BandPlan plan, SpikePlan sp, Ws ws) {
 constexpr int kGramTile = 32;
 __global__ void __launch_bounds__(256)
 k_spike_gram(int B, BandPlan plan, SpikePlan sp, Ws ws) {
-  __shared__ double Wi[32][kGramTile + 1], Wj[32][kGramTile + 1];
+  __shared__ double Wi[32][kGramTile + 1], Wj[32][kGramTile + 1], ys[32];
   const int d = 1 + blockIdx.y;
   const BandPart pt = plan.part[d];
   const int NS = 6 * B;
@@ -180,6 +180,7 @@ k_spike_gram(int B, BandPlan plan, SpikePlan sp, Ws ws) {
       Wi[kk][c] = (okk && i0 + c < NS) ? Wg[(size_t)(k0 + kk) * NS + i0 + c] : 0.0;
       Wj[kk][c] = (okk && j0 + c < NS) ? Wg[(size_t)(k0 + kk) * NS + j0 + c] : 0.0;
     }
+    if (tid < 32) ys[tid] = k0 + tid < K ? y_g[k0 + tid] : 0.0;
     __syncthreads();
     const int kn = min(32, K - k0);
     for (int kk = 0; kk < kn; ++kk) {
@@ -189,7 +190,7 @@ k_spike_gram(int B, BandPlan plan, SpikePlan sp, Ws ws) {
       acc[1][0] = fma(a1, b0, acc[1][0]);
       acc[1][1] = fma(a1, b1, acc[1][1]);
       if (tj == 0 && tx == 0) {
-        const double yv = y_g[k0 + kk];
+        const double yv = ys[kk];
         gy[0] = fma(a0, yv, gy[0]);
         gy[1] = fma(a1, yv, gy[1]);
       }
@@ -233,34 +234,74 @@ __device__ __forceinline__ SepAsm sep_asm(int s, const BandPlan& plan, const Spi
   a.m = sp.m[s];
   return a;
 }
-__device__ __forceinline__ double sep_entry(const SepAsm& a, int i, int j, int B, int n, float lm, float ep, const Ws& ws) {
+// L (lower triangle, leading dimension ld) and the right-hand side in row NS, whole CTA; one simple pass per term
+__device__ void sep_assemble(const SepAsm& a, double* L, int ld, int B, int n, float lm, float ep, const Ws& ws) {
+  const int tid = threadIdx.x, nt = blockDim.x;
   const int NS = 6 * B;
-  const int bi = i / 6, r = i - 6 * bi, bj = j / 6, c = j - 6 * bj;
-  double v = a.dumpA[(size_t)(bi * B + bj) * 36 + r * 6 + c];
-  if (a.dumpR) {
-    // the bottom-up sweep works on the block-reversed ordering: physical block (bi, bj), bi >= bj, is the transpose of
-    // its logical block (B-1-bj, B-1-bi); both sweeps carry the damped A_ss, counted once
-    const int brc = bi == bj ? r * 6 + c : c * 6 + r;
-    double h = ws.H[(size_t)(6 * (a.m + bi) + r) * n + 6 * (a.m + bj) + c];
-    if (i == j) h += (double)ep + (double)lm * h;
-    v += a.dumpR[(size_t)((B - 1 - bj) * B + (B - 1 - bi)) * 36 + brc] - h;
+  // blocks (bi >= bj) of the top-down sweep's view of the separator, 36 consecutive doubles each; four elements per
+  // pass so that four loads are in flight per thread
+  for (int e0 = tid; e0 < B * B * 36; e0 += 4 * nt) {
+    double v[4];
+    int dst[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * nt;
+      dst[u] = -1;
+      v[u] = 0.0;
+      if (e >= B * B * 36) continue;
+      const int blk = e / 36, rc = e - blk * 36, bi = blk / B, bj = blk - bi * B;
+      const int r = rc / 6, c = rc - 6 * r;
+      if (bi < bj || (bi == bj && c > r)) continue;
+      dst[u] = (6 * bi + r) * ld + 6 * bj + c;
+      v[u] = a.dumpA[e];
+      if (a.dumpR) {
+        // the bottom-up sweep works on the block-reversed ordering: physical block (bi, bj), bi >= bj, is the transpose
+        // of its logical block (B-1-bj, B-1-bi); both sweeps carry the damped A_ss, counted once
+        const int brc = bi == bj ? r * 6 + c : c * 6 + r;
+        double h = ws.H[(size_t)(6 * (a.m + bi) + r) * n + 6 * (a.m + bj) + c];
+        if (bi == bj && r == c) h += (double)ep + (double)lm * h;
+        v[u] += a.dumpR[(size_t)((B - 1 - bj) * B + (B - 1 - bi)) * 36 + brc] - h;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (dst[u] >= 0) L[dst[u]] = v[u];
   }
-  if (a.sll) v -= a.sll[(size_t)i * NS + j];
-  if (a.u0) v -= a.u0[(size_t)i * NS + j];
-  if (a.u1) v -= a.u1[(size_t)i * NS + j];
-  return v;
-}
-__device__ __forceinline__ double sep_rhs(const SepAsm& a, int i, int B, const Ws& ws) {
-  const int NS = 6 * B;
-  double v = a.dumpA[(size_t)B * B * 36 + i];
-  if (a.dumpR) {
-    const int bi = i / 6, r = i - 6 * bi;
-    v += a.dumpR[(size_t)B * B * 36 + (B - 1 - bi) * 6 + r] - ws.v[6 * a.m + i];
+  for (int i = tid; i < NS; i += nt) {
+    double v = a.dumpA[(size_t)B * B * 36 + i];
+    if (a.dumpR) {
+      const int bi = i / 6, r = i - 6 * bi;
+      v += a.dumpR[(size_t)B * B * 36 + (B - 1 - bi) * 6 + r] - ws.v[6 * a.m + i];
+    }
+    L[(size_t)NS * ld + i] = v;
   }
-  if (a.sll) v -= a.sll[(size_t)NS * NS + i];
-  if (a.u0) v -= a.u0[(size_t)NS * NS + i];
-  if (a.u1) v -= a.u1[(size_t)NS * NS + i];
-  return v;
+  __syncthreads();
+  // the spike term and the chain updates: one warp per row (row NS = right-hand-side part behind each matrix), all
+  // loads of a pass issued before the first use
+  for (int i = tid >> 5; i <= NS; i += nt >> 5) {
+    const int jn = i < NS ? i + 1 : NS;
+    for (int j0 = tid & 31; j0 < jn; j0 += 128) {
+      double t[4] = {0.0, 0.0, 0.0, 0.0};
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + 32 * u;
+        if (j < jn) {
+          const size_t o = (size_t)i * NS + j;
+          double x = 0.0;
+          if (a.sll) x += a.sll[o];
+          if (a.u0) x += a.u0[o];
+          if (a.u1) x += a.u1[o];
+          t[u] = x;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int j = j0 + 32 * u;
+        if (j < jn) L[(size_t)i * ld + j] -= t[u];
+      }
+    }
+  }
+  __syncthreads();
 }
 
 // which separator a side works on at a level, and its neighbour towards the middle
@@ -285,12 +326,7 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
   double* dinv = L + (size_t)(NS + 1) * ld;          // NS
   double* xs = dinv + NS;                            // rows of X of this CTA: [rps][ld]
   const SepAsm as = sep_asm(s, plan, sp, ws);
-  for (int e = tid; e < NS * NS; e += nt) {
-    const int i = e / NS, j = e - i * NS;
-    if (j <= i) L[(size_t)i * ld + j] = sep_entry(as, i, j, B, n, lm, ep, ws);
-  }
-  for (int i = tid; i < NS; i += nt) L[(size_t)NS * ld + i] = sep_rhs(as, i, B, ws);
-  __syncthreads();
+  sep_assemble(as, L, ld, B, n, lm, ep, ws);
   const bool ok = cholesky6_factor(L, ld, B, dinv, &fail);
   __syncthreads();
   int* flags = reinterpret_cast<int*>(ws.Lfac + plan.flags);
@@ -300,14 +336,8 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
   }
   double* Lf = ws.Lfac + sp.Lf[s];
   if (blockIdx.x == 0) {                              // keep the factor, y and 1/diag for the back-substitution
-    for (int e = tid; e < NS * NS; e += nt) {
-      const int i = e / NS, j = e - i * NS;
-      if (j <= i) Lf[(size_t)i * ld + j] = L[(size_t)i * ld + j];
-    }
-    for (int i = tid; i < NS; i += nt) {
-      Lf[(size_t)NS * ld + i] = L[(size_t)NS * ld + i];
-      Lf[(size_t)(NS + 1) * ld + i] = dinv[i];
-    }
+    for (int e = tid; e < (NS + 1) * ld; e += nt) Lf[e] = L[e];   // (the unused upper triangle travels along)
+    for (int i = tid; i < NS; i += nt) Lf[(size_t)(NS + 1) * ld + i] = dinv[i];
   }
   // rows [i_lo, i_hi) of X: x L^T = a, a = row of R(t,s).  Five rows per warp, six lanes per row (one per column of
   // the current 6-wide block): the lanes of a row split the dot products, lane c == 0 finishes the block.
@@ -315,7 +345,9 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
   const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
   const double* Rts = side == 0 ? ws.Lfac + sp.Roff[s] : ws.Lfac + sp.Roff[t];
   const int rw = lane / 6, cw = lane - 6 * rw;       // row within the warp (0..4), column within the block
-  const int rows_per_pass = 5 * (nt / 32);
+  constexpr int kRowWarps = 8;                       // warps that hold row buffers (shared-memory budget)
+  const int rows_per_pass = 5 * kRowWarps;
+  if (wid >= kRowWarps) return;
   for (int base = i_lo; base < i_hi; base += rows_per_pass) {
     const int li = wid * 5 + rw;                     // local row of this pass
     const int i = base + li;
@@ -379,28 +411,37 @@ k_red_b(int B, int level, BandPlan plan, SpikePlan sp, Ws ws) {
   if (flags[sp.D] != 0) return;
   const double* Xg = ws.Lfac + sp.X[s];
   double* Ug = ws.Lfac + sp.U[t][side];
+  // X transposed: smx[k][i], so that the lanes of a warp (consecutive columns j) read consecutive words
   for (int e = tid; e < NS * NS; e += nt) {
     const int i = e / NS, k = e - i * NS;
-    smx[(size_t)i * ld + k] = Xg[e];
+    smx[(size_t)k * ld + i] = Xg[e];
   }
   __syncthreads();
   const int rps = (NS + gridDim.x - 1) / gridDim.x;
   const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
-  for (int e = tid; e < (i_hi - i_lo) * NS; e += nt) {
-    const int i = i_lo + e / NS, j = e % NS;
-    if (j > i) continue;
-    const double* xi = smx + (size_t)i * ld;
-    const double* xj = smx + (size_t)j * ld;
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-    int k = 0;
-    for (; k + 3 < NS; k += 4) {
-      s0 = fma(xi[k], xj[k], s0);
-      s1 = fma(xi[k + 1], xj[k + 1], s1);
-      s2 = fma(xi[k + 2], xj[k + 2], s2);
-      s3 = fma(xi[k + 3], xj[k + 3], s3);
+  // a warp task = 3 rows x 32 columns: per k two wavefronts for the columns, three broadcasts for the rows, 96 FMAs
+  const int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
+  const int n_rt = (i_hi - i_lo + 2) / 3, n_ct = (NS + 31) / 32;
+  for (int task = wid; task < n_rt * n_ct; task += nw) {
+    const int rt = task / n_ct, ct = task - rt * n_ct;
+    const int i0 = i_lo + 3 * rt, j = ct * 32 + lane;
+    if (ct * 32 > min(i0 + 2, i_hi - 1)) continue;               // the whole tile lies above the diagonal
+    const int ia = i0, ib = min(i0 + 1, i_hi - 1), ic = min(i0 + 2, i_hi - 1);
+    const int jj = min(j, NS - 1);
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0;
+#pragma unroll 4
+    for (int k = 0; k < NS; ++k) {
+      const double* row = smx + (size_t)k * ld;
+      const double xj = row[jj];
+      s0 = fma(row[ia], xj, s0);
+      s1 = fma(row[ib], xj, s1);
+      s2 = fma(row[ic], xj, s2);
     }
-    for (; k < NS; ++k) s0 = fma(xi[k], xj[k], s0);
-    Ug[(size_t)i * NS + j] = (s0 + s1) + (s2 + s3);
+    if (j < NS) {
+      if (j <= ia) Ug[(size_t)ia * NS + j] = s0;
+      if (i0 + 1 < i_hi && j <= ib) Ug[(size_t)ib * NS + j] = s1;
+      if (i0 + 2 < i_hi && j <= ic) Ug[(size_t)ic * NS + j] = s2;
+    }
   }
 }
 
@@ -415,12 +456,7 @@ k_red_mid(int Pphys, int B, float lm, float ep, BandPlan plan, SpikePlan sp, Ws 
   double* x = L + (size_t)(NS + 1) * ld;
   double* dinv = x + NS;
   const SepAsm as = sep_asm(s, plan, sp, ws);
-  for (int e = tid; e < NS * NS; e += nt) {
-    const int i = e / NS, j = e - i * NS;
-    if (j <= i) L[(size_t)i * ld + j] = sep_entry(as, i, j, B, n, lm, ep, ws);
-  }
-  for (int i = tid; i < NS; i += nt) L[(size_t)NS * ld + i] = sep_rhs(as, i, B, ws);
-  __syncthreads();
+  sep_assemble(as, L, ld, B, n, lm, ep, ws);
   bool ok = cholesky6_solve(L, ld, B, x, dinv, &fail);
   __syncthreads();
   int* flags = reinterpret_cast<int*>(ws.Lfac + plan.flags);
@@ -464,21 +500,28 @@ k_red_back(int B, BandPlan plan, SpikePlan sp, Ws ws) {
     const double* Xg = ws.Lfac + sp.X[s];
     const double* xt_g = ws.Lfac + sp.xsep + (size_t)t * NS;
     __syncthreads();
-    for (int e = tid; e < NS * NS; e += nt) {
-      const int i = e / NS, j = e - i * NS;
-      if (j <= i) L[(size_t)i * ld + j] = Lf[(size_t)i * ld + j];
-    }
+    for (int e = tid; e < NS * ld; e += nt) L[e] = Lf[e];
     for (int i = tid; i < NS; i += nt) {
       dinv[i] = Lf[(size_t)(NS + 1) * ld + i];
       xt[i] = xt_g[i];
+      x[i] = Lf[(size_t)NS * ld + i];
     }
     __syncthreads();
-    for (int k = tid; k < NS; k += nt) {
-      double sum = Lf[(size_t)NS * ld + k];
-      for (int i = 0; i < NS; ++i) sum = fma(-Xg[(size_t)i * NS + k], xt[i], sum);
-      x[k] = sum;
+    {
+      // z = y - X^T x_t: thread (k, part) sums a slice of the rows, partial sums meet in shared memory
+      const int parts = max(1, nt / NS), k = tid % NS, part = tid / NS;
+      double sum = 0.0;
+      if (part < parts) {
+        const int per = (NS + parts - 1) / parts;
+        const int a0 = part * per, a1 = min(NS, a0 + per);
+#pragma unroll 8
+        for (int i = a0; i < a1; ++i) sum = fma(Xg[(size_t)i * NS + k], xt[i], sum);
+      }
+      for (int q = 0; q < parts; ++q) {
+        if (part == q) x[k] -= sum;
+        __syncthreads();
+      }
     }
-    __syncthreads();
     cholesky6_back(L, ld, B, x, dinv);
     for (int i = tid; i < NS; i += nt) {
       xs_g[i] = x[i];
