@@ -605,6 +605,23 @@ extern "C" int dbaf_ba_schur(void* workspace, const int64_t* jj, int E, int N, i
 }
 
 namespace {
+// number of domains the banded solve of P poses with block half-bandwidth B is cut into (1: one sweep, 2: two sweeps
+// meeting at one separator, >= 3: ba_spike.cuh), before the check against the size of the factorisation scratch
+int banded_domains(int P, int B) {
+  const bool single = options().band_single != 0;
+  const bool smem_sweep = B > kBandRegMaxB || options().band_smem != 0;
+  int D = 1;
+  if (!single && !options().band_twisted && !smem_sweep && B >= 1) {
+    const int n_min = B + 2;                                   // interiors longer than the band
+    const int d_max = (P + B) / (B + n_min);
+    const int d_want = options().band_domains > 0 ? options().band_domains : (P + B) / (5 * std::max(B, 4));
+    D = std::min({d_want, d_max, kSpikeMaxD});
+    if (D < 3) D = 1;
+  }
+  if (D < 3) D = (!single && P >= kBandTwistMinP && P >= 3 * B + 2) ? 2 : 1;
+  return D;
+}
+
 int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const double* prior, int prior_rows,
                  int prior_cols, int rezero, cudaStream_t st, int band_blocks = 0) {
   // Only info, H, v, dx and Lfac are touched; their offsets depend on P alone.
@@ -642,15 +659,8 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
     const bool smem_sweep = B > kBandRegMaxB || options().band_smem != 0;
     // ---- how the chain is cut: D domains (ba_spike.cuh), two sweeps meeting at one separator, or one sweep
     SpikePlan sp{};
-    int D = 1;
+    int D = banded_domains(P, B);
     const long long lfac_cap = (long long)(n + 1) * n + n;
-    if (!single && !options().band_twisted && !smem_sweep && B >= 1) {
-      const int n_min = B + 2;                                   // interiors longer than the band
-      const int d_max = (P + B) / (B + n_min);
-      int d_want = options().band_domains > 0 ? options().band_domains : (P + B) / (5 * std::max(B, 4));
-      D = std::min({d_want, d_max, kSpikeMaxD});
-      if (D < 3) D = 1;
-    }
     if (D >= 3) {
       const int NS = 6 * B, ld = spike_ld(NS);
       auto even = [](long long x) { return (x + 1) & ~1LL; };
@@ -811,6 +821,18 @@ extern "C" int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, f
   DBAF_REQUIRE(t1 >= t0, "t1 < t0");
   DBAF_REQUIRE(band_blocks >= 0, "negative band");
   return launch_solve(workspace, t0, t1, lm, ep, nullptr, 0, 0, 0, (cudaStream_t)stream, band_blocks);
+}
+
+extern "C" int dbaf_ba_solve_banded_launches(int n_poses, int band_blocks) {
+  const int P = n_poses, n = 6 * P;
+  if (n == 0) return 0;
+  if (n <= kSmemSolveMaxN || band_blocks <= 0 || band_blocks > kBandMaxB) return 1;
+  const int B = std::min(band_blocks, P - 1);
+  const int D = banded_domains(P, B);
+  if (D == 1) return 1;
+  if (D == 2) return 3;                                        // two sweeps, separator, two back-substitutions
+  const int mid = D / 2, nlev = std::max(mid - 1, D - 1 - mid);
+  return 1 + 2 + 2 * nlev + 1 + (nlev > 0 ? 1 : 0) + 1 + 1;      // sweeps, spike + Gram, levels, middle, chain back, apply, back
 }
 
 extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,

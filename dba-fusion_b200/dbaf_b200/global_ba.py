@@ -136,11 +136,10 @@ class GlobalBA:
         sys_flat.index_copy_(0, idx, packed)
 
     def launches_per_iteration(self):
-        """Kernels of this library enqueued by one `iterate` (k_linearize2, k_schur_tc, k_schur_smem, k_schur when a
-        frame has > 96 rows, the banded solve's kernels, k_backsub_fused)."""
+        """Kernels of this library enqueued by one `iterate`: k_linearize2, k_schur_tc, k_schur_smem, k_schur, the banded
+        solve's kernels (sweeps, spike, separator chain, back-substitutions), k_backsub_fused."""
         import droid_backends as db
-        n_solve = db.banded_solve_launches(self.P, self.band) if hasattr(db, "banded_solve_launches") else 3
-        return 3 + n_solve + 1
+        return 4 + db.banded_solve_launches(self.P, self.band) + 1
 
     def run(self, iterations, lm=1e-4, ep=0.1):
         for _ in range(iterations):
@@ -381,7 +380,7 @@ def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
                 warmup=max(3, args.warmup), ms_per_step=step_ms, higher_is_better=False, scaling="strong",
                 vs_baseline=None, dtype="f32", data="synthetic", config=c5_config(),
                 shard=dict(depth_frame_ranges=[list(r) for r in gba.ranges], band_blocks=gba.band,
-                           solve=eng.solve_kind() if hasattr(eng, "solve_kind") else None),
+                           solve_launches=gba.launches_per_iteration() - 5),
                 roofline=roof, stages_ms=stages, parity_vs_1gpu=parity,
                 e2e=dict(value=float(e2e[0]), unit="ms/iter", h2d_bytes_per_step=int(e2e[1]),
                          d2h_bytes_per_step=int(e2e[2]), ms_per_step=float(e2e[0]),

@@ -43,6 +43,11 @@ def probe_fill(buf, kind):
     check(lib.dbaf_probe_fill(_p(buf), buf.numel() * buf.element_size(), int(kind), _stream()), "dbaf_probe_fill")
 
 
+def banded_solve_launches(n_poses, band):
+    """Number of kernels dbaf_ba_solve_banded enqueues for a window of n_poses poses with that block band."""
+    return int(lib.dbaf_ba_solve_banded_launches(int(n_poses), int(band)))
+
+
 def set_strict(on=True):
     """In strict mode `ba` synchronises after the call and raises on a bad edge index or an eta/K mismatch."""
     global _strict

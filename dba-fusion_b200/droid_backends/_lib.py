@@ -65,6 +65,7 @@ SIGNATURES = {
                                   c_int, c_float, c_int, c_int, c_int, c_int, P]),
     "dbaf_ba_solve": (c_int, [P, c_int, c_int, c_float, c_float, P, c_int, c_int, P]),
     "dbaf_ba_solve_banded": (c_int, [P, c_int, c_int, c_float, c_float, c_int, P]),
+    "dbaf_ba_solve_banded_launches": (c_int, [c_int, c_int]),
     "dbaf_ba_retract": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                 c_int, c_int, P, P, P]),
     "dbaf_ba": (c_int, [P, P, P, P, P, P, P, P, c_int, P, P, c_int, c_int, c_int, c_int, c_int, c_int,

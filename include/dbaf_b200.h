@@ -274,10 +274,14 @@ int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep,
  * satisfies |I-J| <= band_blocks (a temporal graph with edges reaching `reach` frames gives 2*reach).
  * Windows up to 6P = 160 ignore the hint and use the dense shared-memory solver; beyond that a band of
  * 1..25 blocks selects the sliding-window factorisation, anything else the slow dense fallback.
- * Chains of 64 or more poses are factorised from both ends at once (two thread blocks meeting at a separator).
+ * Chains of 64 or more poses are factorised from both ends at once (two thread blocks meeting at a separator);
+ * long chains with a band of at most 20 blocks are cut into up to 16 domains that are swept concurrently, with a
+ * block-tridiagonal system over the separators solved afterwards (csrc/ba_spike.cuh).
  * The workspace must have gone through dbaf_ba_prepare (it zeroes the failure counter info[1]).
  * Replaces Eigen::SimplicialLLT on the host (src/droid_kernels.cu:1248-1269). */
 int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, int band_blocks, void* stream);
+/* how many kernels dbaf_ba_solve_banded enqueues for that many poses and that band (bench.py counts launches with it) */
+int dbaf_ba_solve_banded_launches(int n_poses, int band_blocks);
 
 /* EvT6x1_kernel + dz + pose_retr_kernel + disp_retr_kernel, src/droid_kernels.cu:1140-1160,
  * 1486-1506,943-991.  dx_in: float32 [P,6] (NULL = the workspace's dx).  poses/disps are updated
