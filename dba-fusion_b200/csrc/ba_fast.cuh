@@ -319,6 +319,12 @@ k_solve6(int P, float lm, float ep, const double* __restrict__ prior, int prior_
   double* L = smd;                                     // (n+1) x ld
   double* x = L + (size_t)(n + 1) * ld;                // n
   double* dinv = x + n;                                // n
+#ifdef DBAF_SOLVE6_PROFILE
+  long long sq[5], sq0 = clock64();
+#define SQ_TICK(i) do { __syncthreads(); const long long now = clock64(); sq[i] = now - sq0; sq0 = now; } while (0)
+#else
+#define SQ_TICK(i) do {} while (0)
+#endif
   for (int i = tid >> 4; i < n; i += (nt >> 4)) {
     for (int c = tid & 15; c <= i; c += 16) {
       const size_t t = (size_t)i * n + c;
@@ -330,13 +336,29 @@ k_solve6(int P, float lm, float ep, const double* __restrict__ prior, int prior_
   }
   for (int i = tid; i < n; i += nt) L[(size_t)n * ld + i] = ws.v[i];
   __syncthreads();
+  SQ_TICK(0);
+#ifdef DBAF_SOLVE6_PROFILE
+  bool ok = cholesky6_factor(L, ld, P, dinv, &fail);
+  SQ_TICK(1);
+  if (ok) {
+    for (int i = tid; i < n; i += nt) x[i] = L[(size_t)n * ld + i];
+    __syncthreads();
+    cholesky6_back(L, ld, P, x, dinv);
+  }
+  SQ_TICK(2);
+#else
   const bool ok = cholesky6_solve(L, ld, P, x, dinv, &fail);
+#endif
   __syncthreads();
   for (int i = tid; i < n; i += nt) ws.dx[i] = ok ? (float)x[i] : 0.0f;
   if (!ok && tid == 0) atomicAdd(&ws.info[1], 1);
   if (rezero) {
     for (int t = tid; t < n * n + n; t += nt) ws.H[t] = 0.0;   // v follows H directly
   }
+#ifdef DBAF_SOLVE6_PROFILE
+  SQ_TICK(3);
+  if (tid == 0) printf("k_solve6 P=%d cycles: load %lld, factor %lld, back-substitution %lld, store + rezero %lld\n", P, sq[0], sq[1], sq[2], sq[3]);
+#endif
 }
 
 // ---------------------------------------------------------------- retract ----

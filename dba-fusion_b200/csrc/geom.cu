@@ -295,18 +295,34 @@ __global__ void __launch_bounds__(256) k_fill128(uint4* __restrict__ dst, size_t
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride) dst[i] = val;
 }
+// the store pattern of the correlation-volume kernel: a CTA owns 128 rows of `pitch` bytes and writes them in chunks
+// of `seg` bytes per row (row after row inside a chunk), chunk after chunk
+__global__ void __launch_bounds__(256) k_fill_tiled(uint4* __restrict__ dst, size_t n_tiles, int pitch16, int seg16, uint4 val) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  for (size_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    uint4* base = dst + tile * 128 * (size_t)pitch16;
+    for (int c0 = 0; c0 < pitch16; c0 += seg16)
+      for (int r = wid; r < 128; r += 8)
+        for (int q = lane; q < seg16; q += 32) base[(size_t)r * pitch16 + c0 + q] = val;
+  }
+}
 }  // namespace
 }  // namespace dbaf
 
 extern "C" int dbaf_probe_fill(void* dst, size_t bytes, int kind, void* stream) {
   DBAF_REQUIRE(dst != nullptr && (reinterpret_cast<uintptr_t>(dst) & 15) == 0, "dst must be 16-byte aligned");
-  DBAF_REQUIRE(kind == 0 || kind == 1, "kind: 0 = cudaMemsetAsync, 1 = 128-bit store kernel");
+  DBAF_REQUIRE(kind >= 0 && kind <= 5, "kind: 0 = cudaMemsetAsync, 1 = 128-bit store kernel, 2..5 = tiled store patterns");
   cudaStream_t st = (cudaStream_t)stream;
   if (kind == 0) {
     DBAF_CUDA(cudaMemsetAsync(dst, 1, bytes, st));
-  } else {
+  } else if (kind == 1) {
     k_fill128<<<148 * 8, 256, 0, st>>>(static_cast<uint4*>(dst), bytes / 16, make_uint4(1u, 2u, 3u, 4u));
     DBAF_LAUNCH_CHECK("k_fill128");
+  } else {
+    // 128 rows x 8 KB tiles written in 512 B (2), 1 KB (3), 2 KB (4) or 8 KB (5) pieces per row
+    const int pitch16 = 8192 / 16, seg16 = (kind == 2 ? 512 : kind == 3 ? 1024 : kind == 4 ? 2048 : 8192) / 16;
+    k_fill_tiled<<<148 * 2, 256, 0, st>>>(static_cast<uint4*>(dst), bytes / (128 * 8192), pitch16, seg16, make_uint4(1u, 2u, 3u, 4u));
+    DBAF_LAUNCH_CHECK("k_fill_tiled");
   }
   return DBAF_OK;
 }

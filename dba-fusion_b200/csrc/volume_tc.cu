@@ -35,10 +35,20 @@ constexpr int kC = 128;           // channels (K)
 constexpr int kKBlock = 64;       // channels per 128-byte swizzle row
 constexpr int kSmemA = kBM * kC * 2;                 // 32 KB
 constexpr int kSmemB = kBN * kC * 2;                 // 64 KB
-constexpr int kStageWarp = 5 * 4096;                 // per epilogue warp: 4 level-0 boxes + 1 level-1 box, 32 px x 128 B each
-constexpr int kSmemStage = 4 * kStageWarp;           // 80 KB
+constexpr int kStageWarp = 3 * 4096;                 // per fused epilogue warp: 2 level-0 boxes + 1 level-1 box, 32 px x 128 B each
+constexpr int kSmemStage = 8 * kStageWarp;           // 96 KB (the four generic-shape epilogue warps use 24 KB each)
+// pipeline depth.  Fused (64-wide frames): chunks of 128 target pixels (two image rows), two B buffers of 32 KB and
+// four 128-column accumulators, so that the next B tile is on its way while the tensor core and the epilogue work.
+// Generic shapes: chunks of up to 256 pixels, one B buffer, two 256-column accumulators.
+template <bool FUSE> struct Pipe {
+  static constexpr int kNB = FUSE ? 2 : 1;           // B buffers
+  static constexpr int kNAcc = FUSE ? 4 : 2;         // TMEM accumulator stages
+  static constexpr int kAccCols = FUSE ? 128 : 256;  // columns per stage
+};
+constexpr int kBarA = 0, kBarBFull = 1, kBarBFree = 3, kBarAccFull = 5 /* [epilogue set][stage] */, kBarAccFree = 13, kNumBars = 17;
 constexpr int kSmemBytes = kSmemA + kSmemB + kSmemStage + 1024 /*alignment slack*/ + 256 /*barriers*/;
 constexpr int kThreadsTc = 256;   // warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7: epilogue
+constexpr int kThreadsTcFused = 384;   // fused kernel: a second set of epilogue warps (8-11) takes every other group of chunks
 
 // instruction descriptor, kind::f16: D = F32 (bit 4), A = B = F16, both K-major, N >> 3 at bit 17, M >> 4 at bit 24
 
@@ -79,7 +89,7 @@ __global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict
 
 // ------------------------------------------------------------------ main kernel ----
 template <bool FUSE>
-__global__ void __launch_bounds__(kThreadsTc, 1)
+__global__ void __launch_bounds__(FUSE ? kThreadsTcFused : kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
             int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2,
@@ -94,27 +104,36 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
   uint8_t* sB = smem + kSmemA;
   uint8_t* sStage = smem + kSmemA + kSmemB;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kSmemA + kSmemB + kSmemStage);
-  // bars[0]: A landed, bars[1]: B landed, bars[2]: B buffer free, bars[3..4]: accumulator full,
-  // bars[5..6]: accumulator drained
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  // bars[kBarA]: A landed, [kBarBFull + b]: B buffer b landed, [kBarBFree + b]: B buffer b free,
+  // [kBarAccFull + s]: accumulator stage s complete, [kBarAccFree + s]: accumulator stage s drained
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kNumBars + 1);
+  constexpr int NB = Pipe<FUSE>::kNB, NACC = Pipe<FUSE>::kNAcc, ACC_COLS = Pipe<FUSE>::kAccCols;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int e = blockIdx.x / m_tiles;
   const int m0 = (blockIdx.x - e * m_tiles) * kBM;
   const int n_chunks = (HW + chunk_px - 1) / chunk_px;
+  // The CTAs of an edge all walk the same target frame.  Started together at chunk 0 they would ask the same few L2
+  // slices for the same B tile at the same time; each M tile therefore starts at its own chunk (a multiple of four:
+  // the fused pooling works on groups of four chunks) and wraps around.
+  const int rot = (((blockIdx.x - e * m_tiles) * 4) % n_chunks) & ~3;
+  auto data_chunk = [&](int k) { const int cd = k + rot; return cd >= n_chunks ? cd - n_chunks : cd; };
   // operand rows: the edge's own maps, or frames picked by index (video.fmaps[ii] / [jj], covisible_graph.py:129-130)
   const int ea = idx1 ? idx1[e] : e, eb = idx2 ? idx2[e] : e;
   // where the edge's volume goes: its own position, or a slot of a larger pool (CorrPool)
   const int eo = out_slot ? out_slot[e] : e;
 
   if (threadIdx.x == 0) {
-    mbar_init(smem_u32(&bars[0]), 1);
-    mbar_init(smem_u32(&bars[1]), 1);
-    mbar_init(smem_u32(&bars[2]), 1);
-    mbar_init(smem_u32(&bars[3]), 1);
-    mbar_init(smem_u32(&bars[4]), 1);
-    mbar_init(smem_u32(&bars[5]), 4);   // one arrival per epilogue warp
-    mbar_init(smem_u32(&bars[6]), 4);
+    mbar_init(smem_u32(&bars[kBarA]), 1);
+    for (int b = 0; b < NB; ++b) {
+      mbar_init(smem_u32(&bars[kBarBFull + b]), 1);
+      mbar_init(smem_u32(&bars[kBarBFree + b]), 1);
+    }
+    for (int a = 0; a < NACC; ++a) {
+      mbar_init(smem_u32(&bars[kBarAccFull + a]), 1);
+      mbar_init(smem_u32(&bars[kBarAccFull + 4 + a]), 1);
+      mbar_init(smem_u32(&bars[kBarAccFree + a]), 4);   // one arrival per epilogue warp of the set that owns the chunk
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
@@ -132,155 +151,248 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
     // ---------------------------------------------------------------- TMA producer
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
-    const uint32_t barA = smem_u32(&bars[0]), barB = smem_u32(&bars[1]), barFree = smem_u32(&bars[2]);
+    const uint32_t barA = smem_u32(&bars[kBarA]);
     mbar_expect_tx(barA, kSmemA);
     tma_load_2d(smem_u32(sA), &mapA, barA, 0, ea * HW + m0);
     tma_load_2d(smem_u32(sA) + kBM * 128, &mapA, barA, kKBlock, ea * HW + m0);
+#ifdef DBAF_VOL_PROFILE
+    long long pp = 0;
+#endif
     for (int c = 0; c < n_chunks; ++c) {
-      mbar_wait(barFree, (c + 1) & 1);
+      const int b = c % NB, use = c / NB;
+      const uint32_t barB = smem_u32(&bars[kBarBFull + b]);
+      const uint32_t dstB = smem_u32(sB) + (uint32_t)b * (kSmemB / NB);
+#ifdef DBAF_VOL_PROFILE
+      const long long p0c = clock64();
+#endif
+      mbar_wait(smem_u32(&bars[kBarBFree + b]), (use + 1) & 1);
+#ifdef DBAF_VOL_PROFILE
+      pp += clock64() - p0c;
+      if (FUSE && blockIdx.x == 700 && c == n_chunks - 1) printf("k_volume_tc producer: wait B buffer free %lld cycles per chunk\n", pp / n_chunks);
+#endif
+#ifdef DBAF_VOL_NOLOAD
+      if (c >= NB) { mbar_arrive(barB); continue; }             // experiment: the B tiles are loaded once
+#endif
       mbar_expect_tx(barB, (uint32_t)n_mma * 256u);
-      tma_load_2d(smem_u32(sB), &mapB, barB, 0, eb * HW + c * chunk_px);
-      tma_load_2d(smem_u32(sB) + n_mma * 128, &mapB, barB, kKBlock, eb * HW + c * chunk_px);
+      const int cd = data_chunk(c);
+      tma_load_2d(dstB, &mapB, barB, 0, eb * HW + cd * chunk_px);
+      tma_load_2d(dstB + n_mma * 128, &mapB, barB, kKBlock, eb * HW + cd * chunk_px);
     }
     }
     __syncwarp();
   } else if (warp == 1) {
     if (lane == 0) {
     // ---------------------------------------------------------------- MMA issuer
-    const uint32_t barA = smem_u32(&bars[0]), barB = smem_u32(&bars[1]), barFree = smem_u32(&bars[2]);
-    mbar_wait(barA, 0);
+    mbar_wait(smem_u32(&bars[kBarA]), 0);
     const uint32_t idesc = (1u << 4) | ((uint32_t)(n_mma >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
+#ifdef DBAF_VOL_PROFILE
+    long long mp[3] = {0, 0, 0}, m0c, m1c;
+#define MP_TICK(i) do { m1c = clock64(); mp[i] += m1c - m0c; m0c = m1c; } while (0)
+#else
+#define MP_TICK(i) do {} while (0)
+#endif
     for (int c = 0; c < n_chunks; ++c) {
-      const int s = c & 1, u = c >> 1;
-      mbar_wait(smem_u32(&bars[5 + s]), (u + 1) & 1);      // epilogue has drained this accumulator stage
-      mbar_wait(barB, c & 1);
+      const int s = c % NACC, u = c / NACC, b = c % NB;
+#ifdef DBAF_VOL_PROFILE
+      m0c = clock64();
+#endif
+      mbar_wait(smem_u32(&bars[kBarAccFree + s]), (u + 1) & 1);      // epilogue has drained this accumulator stage
+      MP_TICK(0);
+      mbar_wait(smem_u32(&bars[kBarBFull + b]), (c / NB) & 1);
+      MP_TICK(1);
       tc_fence_after();
-      const uint32_t d_tmem = tmem_base + (uint32_t)(s * kBN);
+      const uint32_t d_tmem = tmem_base + (uint32_t)(s * ACC_COLS);
+      const uint32_t bB = smem_u32(sB) + (uint32_t)b * (kSmemB / NB);
 #pragma unroll
       for (int kb = 0; kb < 2; ++kb) {
 #pragma unroll
         for (int k4 = 0; k4 < 4; ++k4) {
           const uint64_t ad = umma_desc_k128(smem_u32(sA) + kb * (kBM * 128) + k4 * 32);
-          const uint64_t bd = umma_desc_k128(smem_u32(sB) + kb * (n_mma * 128) + k4 * 32);
+          const uint64_t bd = umma_desc_k128(bB + kb * (n_mma * 128) + k4 * 32);
           tc_mma_f16(d_tmem, ad, bd, idesc, (kb | k4) ? 1u : 0u);
         }
       }
-      tc_commit(barFree);                 // B buffer may be overwritten once these MMAs are done
-      tc_commit(smem_u32(&bars[3 + s]));  // accumulator stage s is complete
+      tc_commit(smem_u32(&bars[kBarBFree + b]));     // B buffer may be overwritten once these MMAs are done
+      // accumulator stage s is complete: tell the epilogue warp set that owns this chunk (each set has its own
+      // barriers, so that it sees their phases one by one whatever the other set does)
+      tc_commit(smem_u32(&bars[kBarAccFull + (FUSE ? ((c >> 2) & 1) * 4 : 0) + s]));
+      MP_TICK(2);
     }
+#ifdef DBAF_VOL_PROFILE
+    if (FUSE && blockIdx.x == 700)
+      printf("k_volume_tc MMA thread, cycles per chunk: wait accumulator drained %lld, wait B tile %lld, issue %lld\n",
+             mp[0] / n_chunks, mp[1] / n_chunks, mp[2] / n_chunks);
+#endif
     }
     __syncwarp();
   } else if (warp >= 4) {
     // ---------------------------------------------------------------- epilogue
-    const int q = warp - 4;                           // TMEM lane quarter == warp % 4
+    const int q = (warp - 4) & 3;                     // TMEM lane quarter == warp % 4
+    const int eset = (warp - 4) >> 2;                 // fused: which set of epilogue warps (groups of four chunks alternate)
     const int m = m0 + q * 32 + lane;                 // this thread's source pixel
     const bool mok = m < HW;
     const size_t row = (size_t)eo * HW + (mok ? m : 0);
-    uint32_t carry2[8];                               // level-2 row of the even chunk (FUSE)
+    uint32_t carry1[16];                              // level-1 row of the even chunk (FUSE)
+    uint32_t carry2[8];                               // level-2 row of the even chunk pair (FUSE)
+#pragma unroll
+    for (int i = 0; i < 16; ++i) carry1[i] = 0;
 #pragma unroll
     for (int i = 0; i < 8; ++i) carry2[i] = 0;
+#ifdef DBAF_VOL_PROFILE
+    long long vp[4] = {0, 0, 0, 0}, v0, v1;
+#define VP_TICK(i) do { v1 = clock64(); vp[i] += v1 - v0; v0 = v1; } while (0)
+#else
+#define VP_TICK(i) do {} while (0)
+#endif
     for (int c = 0; c < n_chunks; ++c) {
-      const int s = c & 1, u = c >> 1;
-      mbar_wait(smem_u32(&bars[3 + s]), u & 1);
+      const int s = c % NACC, u = c / NACC;
+#ifdef DBAF_VOL_PROFILE
+      v0 = clock64();
+#endif
+      // fused: four chunks (eight target rows, one level-3 row) form a group and the two warp sets take the groups
+      // in turn
+      if (FUSE && ((c >> 2) & 1) != eset) continue;
+      const int cd = data_chunk(c);                    // which chunk of the target frame this pipeline step holds
+      mbar_wait(smem_u32(&bars[kBarAccFull + eset * 4 + s]), (FUSE ? (c >> 3) : u) & 1);
       tc_fence_after();
-      const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * kBN);
+      VP_TICK(0);
+      const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * ACC_COLS);
       if constexpr (FUSE) {
-        // chunk = target rows 4c .. 4c+3 of a 64-wide frame
-        uint8_t* stage = sStage + q * kStageWarp;
-        if (lane == 0) bulk_wait_read0();        // the previous chunk's tiles have left shared memory
+        // chunk = target rows 2c, 2c+1 of a 64-wide frame = level-1 row c.  The stores are issued by different lanes
+        // (bulk groups are per thread): lane 0 / lane 1 own the two level-0 boxes of a chunk, lane 4 the level-1
+        // box, which is filled by two consecutive chunks.
+        uint8_t* stage = sStage + (eset * 4 + q) * kStageWarp;
+        uint8_t* b0 = stage;
+        uint8_t* b1 = b0 + 4096;
+        uint8_t* l1box = stage + 2 * 4096;
+#ifdef DBAF_VOL_TMA_L0
+        if (lane < 2) bulk_wait_read0();                        // this lane's box of the previous chunk has left shared memory
+#endif
+        if (lane == 4 && (c & 1) == 0) bulk_wait_read0();       // the level-1 box of the previous chunk pair
         __syncwarp();
-        uint32_t l1row[2][16];                        // level-1 rows 2c, 2c+1 (32 halves each)
+        VP_TICK(1);
+        uint32_t l1row[16];                                     // level-1 row c (32 halves)
 #pragma unroll
-        for (int j = 0; j < 2; ++j) {
+        for (int xb = 0; xb < 2; ++xb) {
+          uint32_t r0[32], r1[32];
+          tc_ld32x2(t0 + (uint32_t)(xb * 32), t0 + (uint32_t)(64 + xb * 32), r0, r1);
+          // fp32 -> fp16 two at a time; the pooled value is built from the ROUNDED level-0 values
+          __half2 p0[16], p1[16];
 #pragma unroll
-          for (int xb = 0; xb < 2; ++xb) {
-            uint32_t r0[32], r1[32];
-            tc_ld32x2(t0 + (uint32_t)((2 * j) * 64 + xb * 32), t0 + (uint32_t)((2 * j + 1) * 64 + xb * 32), r0, r1);
-            // fp32 -> fp16 two at a time; the pooled value is built from the ROUNDED level-0 values
-            __half2 p0[16], p1[16];
+          for (int i = 0; i < 16; ++i) {
+            p0[i] = __floats2half2_rn(__uint_as_float(r0[2 * i]), __uint_as_float(r0[2 * i + 1]));
+            p1[i] = __floats2half2_rn(__uint_as_float(r1[2 * i]), __uint_as_float(r1[2 * i + 1]));
+          }
+          {
+            const uint32_t* w0 = reinterpret_cast<const uint32_t*>(p0);
+            const uint32_t* w1 = reinterpret_cast<const uint32_t*>(p1);
 #pragma unroll
-            for (int i = 0; i < 16; ++i) {
-              p0[i] = __floats2half2_rn(__uint_as_float(r0[2 * i]), __uint_as_float(r0[2 * i + 1]));
-              p1[i] = __floats2half2_rn(__uint_as_float(r1[2 * i]), __uint_as_float(r1[2 * i + 1]));
-            }
-            {
-              uint8_t* b0 = stage + (2 * j) * 4096;
-              uint8_t* b1 = stage + (2 * j + 1) * 4096;
-              const uint32_t* w0 = reinterpret_cast<const uint32_t*>(p0);
-              const uint32_t* w1 = reinterpret_cast<const uint32_t*>(p1);
-#pragma unroll
-              for (int g = 0; g < 4; ++g) {
-                *swz(b0, lane, xb * 4 + g) = make_uint4(w0[4 * g], w0[4 * g + 1], w0[4 * g + 2], w0[4 * g + 3]);
-                *swz(b1, lane, xb * 4 + g) = make_uint4(w1[4 * g], w1[4 * g + 1], w1[4 * g + 2], w1[4 * g + 3]);
-              }
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-              // level-1 columns 2i and 2i+1 of this half row: ((a+b)+c)+d, *0.25, one rounding
-              const float2 a0 = __half22float2(p0[2 * i]), a1 = __half22float2(p1[2 * i]);
-              const float2 c0 = __half22float2(p0[2 * i + 1]), c1 = __half22float2(p1[2 * i + 1]);
-              const float lo = (((a0.x + a0.y) + a1.x) + a1.y) * 0.25f;
-              const float hi = (((c0.x + c0.y) + c1.x) + c1.y) * 0.25f;
-              const __half2 pr = __floats2half2_rn(lo, hi);
-              l1row[j][xb * 8 + i] = *reinterpret_cast<const uint32_t*>(&pr);
+            for (int g = 0; g < 4; ++g) {
+              *swz(b0, lane, xb * 4 + g) = make_uint4(w0[4 * g], w0[4 * g + 1], w0[4 * g + 2], w0[4 * g + 3]);
+              *swz(b1, lane, xb * 4 + g) = make_uint4(w1[4 * g], w1[4 * g + 1], w1[4 * g + 2], w1[4 * g + 3]);
             }
           }
-          if (out.l[1]) {
 #pragma unroll
-            for (int g = 0; g < 4; ++g)
-              *swz(stage + 4 * 4096, lane, j * 4 + g) =
-                  make_uint4(l1row[j][4 * g], l1row[j][4 * g + 1], l1row[j][4 * g + 2], l1row[j][4 * g + 3]);
+          for (int i = 0; i < 8; ++i) {
+            // level-1 columns 2i and 2i+1 of this half row: ((a+b)+c)+d, *0.25, one rounding
+            const float2 a0 = __half22float2(p0[2 * i]), a1 = __half22float2(p1[2 * i]);
+            const float2 c0 = __half22float2(p0[2 * i + 1]), c1 = __half22float2(p1[2 * i + 1]);
+            const float lo = (((a0.x + a0.y) + a1.x) + a1.y) * 0.25f;
+            const float hi = (((c0.x + c0.y) + c1.x) + c1.y) * 0.25f;
+            const __half2 pr = __floats2half2_rn(lo, hi);
+            l1row[xb * 8 + i] = *reinterpret_cast<const uint32_t*>(&pr);
           }
-        }
-        // hand the staged tiles to the TMA store engine: 4 level-0 boxes (one per target row) + level 1
-        fence_async_smem();
-        __syncwarp();
-        if (lane == 0) {
-          const int r0 = eo * HW + m0 + q * 32;
-#pragma unroll
-          for (int rr = 0; rr < 4; ++rr) tma_store_2d(&mapO0, smem_u32(stage + rr * 4096), c * kBN + rr * 64, r0);
-          if (out.l[1]) tma_store_2d(&mapO1, smem_u32(stage + 4 * 4096), c * 64, r0);
-          bulk_commit();
         }
         // this accumulator stage has been read completely
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars[5 + s]));
-        // level 2: row c (16 values) from level-1 rows 2c, 2c+1
-        uint32_t l2[8];
+        if (lane == 0) mbar_arrive(smem_u32(&bars[kBarAccFree + s]));
+        if (out.l[1]) {
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const uint32_t a0 = l1row[0][2 * i], a1 = l1row[0][2 * i + 1];
-          const uint32_t b0 = l1row[1][2 * i], b1 = l1row[1][2 * i + 1];
-          const __half x = pool_h(__ushort_as_half(a0 & 0xffff), __ushort_as_half(a0 >> 16),
-                                  __ushort_as_half(b0 & 0xffff), __ushort_as_half(b0 >> 16));
-          const __half y = pool_h(__ushort_as_half(a1 & 0xffff), __ushort_as_half(a1 >> 16),
-                                  __ushort_as_half(b1 & 0xffff), __ushort_as_half(b1 >> 16));
-          l2[i] = pack_h2(x, y);
+          for (int g = 0; g < 4; ++g)
+            *swz(l1box, lane, (c & 1) * 4 + g) = make_uint4(l1row[4 * g], l1row[4 * g + 1], l1row[4 * g + 2], l1row[4 * g + 3]);
         }
-        if (mok && out.l[2]) {
-          uint4* d = reinterpret_cast<uint4*>(out.l[2] + row * (size_t)(HW / 16) + (size_t)c * 16);
-          d[0] = make_uint4(l2[0], l2[1], l2[2], l2[3]);
-          d[1] = make_uint4(l2[4], l2[5], l2[6], l2[7]);
+        VP_TICK(2);
+        const int r0g = eo * HW + m0 + q * 32;
+#ifdef DBAF_VOL_TMA_L0
+        // hand the staged tiles to the TMA store engine
+        fence_async_smem();
+        __syncwarp();
+        if (lane < 2) {
+          tma_store_2d(&mapO0, smem_u32(lane == 0 ? b0 : b1), cd * 128 + lane * 64, r0g);
+          bulk_commit();
+        } else if (lane == 4 && (c & 1) && out.l[1]) {
+          tma_store_2d(&mapO1, smem_u32(l1box), (cd >> 1) * 64, r0g);
+          bulk_commit();
         }
+#else
+        // Level 0 leaves through the load/store unit: the two boxes hold target rows 2c and 2c+1, which are adjacent
+        // in the volume (256 contiguous bytes per source pixel), so half a warp writes one source pixel's 256 bytes
+        // with 16-byte stores and a warp instruction covers two source pixels.  (Measured on this part: 128-byte TMA
+        // store boxes top out near 4.1 TB/s chip-wide, plain 16-byte stores in this pattern reach 5.8 TB/s.)
+        if ((c & 1) && out.l[1]) fence_async_smem();            // the level-1 box still goes through TMA
+        __syncwarp();
+        {
+          const int half_id = lane >> 4, piece = lane & 15;     // which of the two source pixels, which 16 bytes of 256
+          const uint8_t* box = (piece & 8) ? b1 : b0;
+          const int nrow = min(32, HW - (m0 + q * 32));
+          __half* dst0 = out.l[0] + (size_t)r0g * (size_t)HW + (size_t)cd * 128 + piece * 8;
+#pragma unroll 4
+          for (int r = half_id; r < nrow; r += 2) {
+            const uint4 v = *reinterpret_cast<const uint4*>(box + r * 128 + (((piece & 7) ^ (r & 7)) << 4));
+#ifndef DBAF_VOL_NOSTORE
+            *reinterpret_cast<uint4*>(dst0 + (size_t)r * HW) = v;
+#endif
+          }
+        }
+        if (lane == 4 && (c & 1) && out.l[1]) {
+          tma_store_2d(&mapO1, smem_u32(l1box), (cd >> 1) * 64, r0g);
+          bulk_commit();
+        }
+        __syncwarp();                                           // the boxes may be overwritten by the next chunk
+#endif
         if ((c & 1) == 0) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) carry2[i] = l2[i];
-        } else if (mok && out.l[3]) {
-          uint32_t l3[4];
+          for (int i = 0; i < 16; ++i) carry1[i] = l1row[i];
+        } else {
+          // level 2: row c/2 (16 values) from level-1 rows c-1, c
+          uint32_t l2[8];
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const uint32_t a0 = carry2[2 * i], a1 = carry2[2 * i + 1];
-            const uint32_t b0 = l2[2 * i], b1 = l2[2 * i + 1];
+          for (int i = 0; i < 8; ++i) {
+            const uint32_t a0 = carry1[2 * i], a1 = carry1[2 * i + 1];
+            const uint32_t b0v = l1row[2 * i], b1v = l1row[2 * i + 1];
             const __half x = pool_h(__ushort_as_half(a0 & 0xffff), __ushort_as_half(a0 >> 16),
-                                    __ushort_as_half(b0 & 0xffff), __ushort_as_half(b0 >> 16));
+                                    __ushort_as_half(b0v & 0xffff), __ushort_as_half(b0v >> 16));
             const __half y = pool_h(__ushort_as_half(a1 & 0xffff), __ushort_as_half(a1 >> 16),
-                                    __ushort_as_half(b1 & 0xffff), __ushort_as_half(b1 >> 16));
-            l3[i] = pack_h2(x, y);
+                                    __ushort_as_half(b1v & 0xffff), __ushort_as_half(b1v >> 16));
+            l2[i] = pack_h2(x, y);
           }
-          *reinterpret_cast<uint4*>(out.l[3] + row * (size_t)(HW / 64) + (size_t)(c >> 1) * 8) =
-              make_uint4(l3[0], l3[1], l3[2], l3[3]);
+          const int c2 = cd >> 1;
+          if (mok && out.l[2]) {
+            uint4* d = reinterpret_cast<uint4*>(out.l[2] + row * (size_t)(HW / 16) + (size_t)c2 * 16);
+            d[0] = make_uint4(l2[0], l2[1], l2[2], l2[3]);
+            d[1] = make_uint4(l2[4], l2[5], l2[6], l2[7]);
+          }
+          if ((c2 & 1) == 0) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) carry2[i] = l2[i];
+          } else if (mok && out.l[3]) {
+            uint32_t l3[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t a0 = carry2[2 * i], a1 = carry2[2 * i + 1];
+              const uint32_t b0v = l2[2 * i], b1v = l2[2 * i + 1];
+              const __half x = pool_h(__ushort_as_half(a0 & 0xffff), __ushort_as_half(a0 >> 16),
+                                      __ushort_as_half(b0v & 0xffff), __ushort_as_half(b0v >> 16));
+              const __half y = pool_h(__ushort_as_half(a1 & 0xffff), __ushort_as_half(a1 >> 16),
+                                      __ushort_as_half(b1v & 0xffff), __ushort_as_half(b1v >> 16));
+              l3[i] = pack_h2(x, y);
+            }
+            *reinterpret_cast<uint4*>(out.l[3] + row * (size_t)(HW / 64) + (size_t)(c2 >> 1) * 8) =
+                make_uint4(l3[0], l3[1], l3[2], l3[3]);
+          }
         }
+        VP_TICK(3);
       } else {
         // generic shapes: a chunk is 2*kr whole target-image rows (or 256 consecutive pixels when a row pair does
         // not fit); level 0 is written here, level 1 is pooled from the staged tile.  A row of the volume is
@@ -288,8 +400,8 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         // accumulator layout is turned around through shared memory: the warp's 32 x 256 tile is staged with a
         // 129-word row pitch (conflict-free both ways) and written out row by row, every store instruction
         // covering 64 contiguous bytes of one row.
-        const int n0 = c * chunk_px;
-        uint32_t* tile = reinterpret_cast<uint32_t*>(sStage + q * kStageWarp);      // [32][129] words
+        const int n0 = cd * chunk_px;
+        uint32_t* tile = reinterpret_cast<uint32_t*>(sStage + q * (2 * kStageWarp));      // [32][129] words
         __syncwarp();                                    // the previous chunk's rows have been read out
 #pragma unroll 1
         for (int b = 0; b < kBN / 32; ++b) {
@@ -302,7 +414,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         // the accumulator stage is free as soon as it sits in shared memory
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(smem_u32(&bars[5 + s]));
+        if (lane == 0) mbar_arrive(smem_u32(&bars[kBarAccFree + s]));
         const int ncol = min(chunk_px, HW - n0);
         const int mrow0 = m0 + q * 32;
         // (all eight loads issued before the first store, and plain shared-memory loads: as generic loads with a
@@ -336,7 +448,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
           }
           const unsigned short* t16 = reinterpret_cast<const unsigned short*>(tile);
           unsigned short* l1base = reinterpret_cast<unsigned short*>(out.l[1]) + ((size_t)eo * HW + mrow0) * (size_t)hw1 +
-                                   (size_t)c * kr * w1;
+                                   (size_t)cd * kr * w1;
 #pragma unroll 4
           for (int r = 0; r < nrow; ++r) {
             const unsigned short* row16 = t16 + r * 258;
@@ -353,9 +465,14 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         }
       }
     }
+#ifdef DBAF_VOL_PROFILE
+    if (FUSE && warp == 4 && lane == 0 && blockIdx.x == 700)
+      printf("k_volume_tc epilogue warp, cycles per chunk: wait accumulator %lld, wait store read-out %lld, tmem->fp16->stage %lld, stores + levels 2,3 %lld\n",
+             vp[0] / n_chunks, vp[1] / n_chunks, vp[2] / n_chunks, vp[3] / n_chunks);
+#endif
   }
 
-  if (FUSE && warp >= 4 && lane == 0) bulk_wait0();
+  if (FUSE && warp >= 4 && (lane < 2 || lane == 4)) bulk_wait0();   // (no-op for lanes that never committed a group)
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
@@ -442,6 +559,7 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
   // generic shapes: a chunk of 2*kr whole image rows (so that level 1 can be pooled from it) when a row pair fits
   // into one UMMA (N <= 256), else 256 consecutive pixels and level 0 only
   int kr = 0, chunk_px = kBN, n_mma = kBN;
+  if (fuse) chunk_px = n_mma = Pipe<true>::kAccCols;        // two rows of a 64-wide frame per chunk
   if (!fuse && 2 * wd <= kBN && levels > 1) {
     kr = kBN / (2 * wd);
     chunk_px = 2 * wd * kr;
@@ -468,7 +586,7 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[dev_id & 63][fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTcFused, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
   else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
   DBAF_LAUNCH_CHECK("k_volume_tc");
   // fused: all requested levels are written; generic with row-pair chunks: levels 0 and 1; otherwise level 0 only.

@@ -1,21 +1,15 @@
-"""Write-only / copy HBM bandwidth on this box (context for the volume kernel's roofline)."""
-import torch, json
-def t(fn, n=10):
-    for _ in range(3): fn()
-    torch.cuda.synchronize()
+"""HBM write ceilings on this box: cudaMemsetAsync, a linear 128-bit-store kernel, and the tiled store patterns of the
+correlation-volume kernel (128 rows of 8 KB written in 512 B .. 8 KB pieces per row).  python scripts/hbm_write_probe.py"""
+import os, sys, torch
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [os.path.join(ROOT, "dba-fusion_b200")]
+import droid_backends as db
+x = torch.empty(1 << 31, dtype=torch.uint8, device="cuda")
+names = {0: "cudaMemsetAsync", 1: "linear st.v4", 2: "tiled 512 B", 3: "tiled 1 KB", 4: "tiled 2 KB", 5: "tiled 8 KB"}
+for kind in range(6):
     best = 1e9
-    for _ in range(n):
+    for _ in range(7):
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record(); fn(); b.record(); b.synchronize()
+        a.record(); db.probe_fill(x, kind); b.record(); b.synchronize()
         best = min(best, a.elapsed_time(b))
-    return best
-res = {}
-for gb in (2, 8):
-    x = torch.empty(gb * (1 << 30) // 2, dtype=torch.float16, device="cuda")
-    y = torch.empty_like(x)
-    res[f"fill_{gb}GB_GBps"] = gb * (1 << 30) / t(lambda: x.fill_(1.0)) / 1e6
-    res[f"memset_{gb}GB_GBps"] = gb * (1 << 30) / t(lambda: x.zero_()) / 1e6
-    res[f"copy_{gb}GB_GBps_rw"] = 2 * gb * (1 << 30) / t(lambda: y.copy_(x)) / 1e6
-    res[f"sum_{gb}GB_GBps_read"] = gb * (1 << 30) / t(lambda: x.view(torch.int16).sum()) / 1e6
-    del x, y
-print(json.dumps(res))
+    print(f"{names[kind]:18s} {x.numel() / best / 1e6:8.1f} GB/s")
