@@ -16,6 +16,7 @@
 #include <cstring>
 
 #include <algorithm>
+#include <atomic>
 
 namespace dbaf {
 
@@ -1051,7 +1052,7 @@ static_assert(4ull * (4ull * kNoAllocMaxFrames + kNoAllocMaxEdges + 2) + 3 * 256
 static __device__ __align__(256) unsigned char g_tables_scratch[kNoAllocScratchBytes];
 
 constexpr int kMaxDevices = 64;
-unsigned char* g_tables_scratch_addr[kMaxDevices] = {};   // device address per device, filled on first use
+std::atomic<unsigned char*> g_tables_scratch_addr[kMaxDevices];   // device address per device, filled on first use
 
 // The array's name is only a host-side handle here; the kernel needs the address the symbol has
 // on the device that is current right now.
@@ -1059,13 +1060,16 @@ int tables_scratch_for_current_device(unsigned char** out) {
   int dev = 0;
   DBAF_CUDA(cudaGetDevice(&dev));
   DBAF_REQUIRE(dev >= 0 && dev < kMaxDevices, "device ordinal out of range");
-  if (g_tables_scratch_addr[dev] == nullptr) {
+  unsigned char* addr = g_tables_scratch_addr[dev].load(std::memory_order_acquire);
+  if (addr == nullptr) {
+    // two host threads may both get here; they resolve the same address, so the second store is harmless
     void* p = nullptr;
     DBAF_CUDA(cudaGetSymbolAddress(&p, g_tables_scratch));
     DBAF_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned a null address");
-    g_tables_scratch_addr[dev] = static_cast<unsigned char*>(p);
+    addr = static_cast<unsigned char*>(p);
+    g_tables_scratch_addr[dev].store(addr, std::memory_order_release);
   }
-  *out = g_tables_scratch_addr[dev];
+  *out = addr;
   return DBAF_OK;
 }
 

@@ -54,6 +54,10 @@ Options& options();
 constexpr float kMinDepth = 0.25f;   // MIN_DEPTH, src/droid_kernels.cu:29
 
 // ------------------------------------------------------------------ SE3 ----
+// rotate / act / relative / adjoint_T / so3_exp / se3_exp / cross_into / retract_pose below restate the closed-form
+// quaternion algebra of the reference, src/droid_kernels.cu:61-178 (actSO3, actSE3, relSE3, adjSE3, expSO3, expSE3,
+// crossInplace, retrSE3), with the same operation order, series constants and small-angle thresholds: the 1e-6 pose
+// parity depends on evaluating these few formulas the way the reference does.
 struct Se3 {
   float t[3];
   float q[4];  // x y z w

@@ -16,7 +16,7 @@ namespace dbaf {
 // volume_tc.cu
 int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
                    int ht, int wd, int levels, __half* const* out, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st, int* levels_done, const int* out_slot, int n_out);
+                   cudaStream_t st, int* levels_done, const int* out_slot, int n_out, const int* bad_flag);
 size_t corr_volume_tc_workspace(int n1, int n2, int C, int ht, int wd);
 
 namespace {
@@ -26,9 +26,11 @@ constexpr int kTile = 64;
 // 64x64 output tile per CTA, 256 threads x (4x4), K staged 32 channels at a time.
 __global__ void __launch_bounds__(256)
 k_volume_simt(const __half* __restrict__ f1, const __half* __restrict__ f2, const int* __restrict__ idx1,
-              const int* __restrict__ idx2, int C, int HW, __half* __restrict__ out, const int* __restrict__ out_slot) {
+              const int* __restrict__ idx2, int C, int HW, __half* __restrict__ out, const int* __restrict__ out_slot,
+              const int* __restrict__ bad_flag) {
   __shared__ float As[32][kTile + 1];
   __shared__ float Bs[32][kTile + 1];
+  if (bad_flag && *bad_flag) return;                 // an index outside its stack: nothing is read or written
   const int e = blockIdx.z;
   const int m0 = blockIdx.y * kTile, n0 = blockIdx.x * kTile;
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
@@ -85,7 +87,8 @@ __device__ __forceinline__ void group_sync(int gthreads) {
 __global__ void __launch_bounds__(128)
 k_pyramid(const __half* __restrict__ L0, long long slabs, int h2, int w2, int levels,
           __half* __restrict__ L1, __half* __restrict__ L2, __half* __restrict__ L3, int gthreads, int group_halves,
-          const int* __restrict__ slot, int hw_src, long long total_slabs) {
+          const int* __restrict__ slot, int hw_src, long long total_slabs, const int* __restrict__ bad_flag) {
+  if (bad_flag && *bad_flag) return;
   // slot != null: logical slab s = (edge, source pixel) lives at physical slab slot[edge] * hw_src + pixel of buffers
   // that hold total_slabs slabs
   extern __shared__ __half sm[];
@@ -150,7 +153,7 @@ __global__ void k_check_index(const int* __restrict__ idx, int n, int limit, int
 
 int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
                    int ht, int wd, int levels, void* const* out_host, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st, const int* out_slot = nullptr, int n_out = -1) {
+                   cudaStream_t st, const int* out_slot = nullptr, int n_out = -1, const int* bad_flag = nullptr) {
   const int HW = ht * wd;
   if (n_out < 0) n_out = n;
   __half* outs[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -161,13 +164,13 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
   int done = 0;
   if (!force_simt) {
     const int rc = corr_volume_tc(f1, n1, f2, n2, idx1, idx2, n, C, ht, wd, levels, outs, workspace, workspace_bytes, st,
-                                  &done, out_slot, n_out);
+                                  &done, out_slot, n_out, bad_flag);
     if (rc != DBAF_OK) return rc;
     if (done >= levels) return DBAF_OK;
   }
   if (done == 0) {
     dim3 grid((HW + kTile - 1) / kTile, (HW + kTile - 1) / kTile, n);
-    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, idx1, idx2, C, HW, outs[0], out_slot);
+    k_volume_simt<<<grid, 256, 0, st>>>(f1, f2, idx1, idx2, C, HW, outs[0], out_slot, bad_flag);
     DBAF_LAUNCH_CHECK("k_volume_simt");
   }
   if (levels > std::max(done, 1)) {
@@ -189,7 +192,7 @@ int volume_pyramid(const __half* f1, int n1, const __half* f2, int n2, const int
     const int blocks = (int)std::min<long long>((slabs + 128 / gthreads - 1) / (128 / gthreads), 148LL * 16);
     k_pyramid<<<blocks, 128, smem, st>>>(outs[src], slabs, hs, wsz, levels - src, outs[src + 1], src + 2 < 4 ? outs[src + 2] : nullptr,
                                          src + 3 < 4 ? outs[src + 3] : nullptr, gthreads, group_halves, out_slot, HW,
-                                         (long long)n_out * HW);
+                                         (long long)n_out * HW, bad_flag);
     DBAF_LAUNCH_CHECK("k_pyramid");
   }
   return DBAF_OK;
@@ -226,23 +229,24 @@ extern "C" int dbaf_corr_volume_pyramid_indexed(const void* fmaps1, int n1, cons
   DBAF_REQUIRE(out_host != nullptr && ii != nullptr && jj != nullptr, "null output list or index array");
   if (n_edges == 0) return DBAF_OK;
   cudaStream_t st = (cudaStream_t)stream;
-  // an index outside its frame stack would read foreign memory: checked on the device before anything is computed
-  // when the caller gives scratch (the flag is read back, which synchronises the stream once)
-  size_t ws_bytes = workspace_bytes;
-  if (workspace != nullptr && workspace_bytes >= 256) {
-    int* flag = reinterpret_cast<int*>((reinterpret_cast<uintptr_t>(workspace) + workspace_bytes - 64) & ~(uintptr_t)63);
-    DBAF_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), st));
-    k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(ii, n_edges, n1, flag);
-    k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(jj, n_edges, n2, flag);
-    DBAF_LAUNCH_CHECK("k_check_index");
-    int bad = 0;
-    DBAF_CUDA(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
-    DBAF_CUDA(cudaStreamSynchronize(st));
-    DBAF_REQUIRE(bad == 0, "frame index out of range");
-    ws_bytes = workspace_bytes - 256;
-  }
+  // An index outside its frame stack would read foreign memory.  It is checked on the device before anything is
+  // computed: the check raises a flag in the last 256 bytes of the workspace and every later kernel of this call
+  // returns at once when it is set; nothing synchronises here, dbaf_corr_volume_status() reads the flag.
+  DBAF_REQUIRE(workspace != nullptr && workspace_bytes >= 256, "workspace too small (dbaf_corr_volume_indexed_workspace_bytes)");
+  int* flag = reinterpret_cast<int*>((reinterpret_cast<uintptr_t>(workspace) + workspace_bytes - 64) & ~(uintptr_t)63);
+  DBAF_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), st));
+  k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(ii, n_edges, n1, flag);
+  k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(jj, n_edges, n2, flag);
+  DBAF_LAUNCH_CHECK("k_check_index");
   return volume_pyramid(static_cast<const __half*>(fmaps1), n1, static_cast<const __half*>(fmaps2), n2, ii, jj, n_edges,
-                        C, ht, wd, levels, out_host, workspace, ws_bytes, st);
+                        C, ht, wd, levels, out_host, workspace, workspace_bytes - 256, st, nullptr, -1, flag);
+}
+
+extern "C" int dbaf_corr_volume_status(const void* workspace, size_t workspace_bytes, int32_t* status_host, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr && workspace_bytes >= 256 && status_host != nullptr, "null pointer or workspace too small");
+  const int* flag = reinterpret_cast<const int*>((reinterpret_cast<uintptr_t>(workspace) + workspace_bytes - 64) & ~(uintptr_t)63);
+  DBAF_CUDA(cudaMemcpyAsync(status_host, flag, sizeof(int32_t), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  return DBAF_OK;
 }
 
 // ---------------------------------------------------------------- slot pool (CorrBlock bookkeeping) ----
@@ -262,10 +266,6 @@ extern "C" int dbaf_corr_volume_pyramid_pool(const void* fmaps1, int n1, const v
   k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(jj, n_edges, n2, flag);
   k_check_index<<<(n_edges + 255) / 256, 256, 0, st>>>(slots, n_edges, capacity, flag);
   DBAF_LAUNCH_CHECK("k_check_index");
-  int bad = 0;
-  DBAF_CUDA(cudaMemcpyAsync(&bad, flag, sizeof(int), cudaMemcpyDeviceToHost, st));
-  DBAF_CUDA(cudaStreamSynchronize(st));
-  DBAF_REQUIRE(bad == 0, "frame index or slot out of range");
   return volume_pyramid(static_cast<const __half*>(fmaps1), n1, static_cast<const __half*>(fmaps2), n2, ii, jj, n_edges,
-                        C, ht, wd, levels, pool_host, workspace, workspace_bytes - 256, st, slots, capacity);
+                        C, ht, wd, levels, pool_host, workspace, workspace_bytes - 256, st, slots, capacity, flag);
 }

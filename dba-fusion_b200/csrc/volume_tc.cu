@@ -93,7 +93,8 @@ __global__ void __launch_bounds__(FUSE ? kThreadsTcFused : kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
             int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2,
-            int chunk_px, int n_mma, int kr, int wd, const int* __restrict__ out_slot) {
+            int chunk_px, int n_mma, int kr, int wd, const int* __restrict__ out_slot, const int* __restrict__ bad_flag) {
+  if (bad_flag && *bad_flag) return;                 // an edge index outside its frame stack (checked by k_check_index)
   // chunk_px: target pixels a chunk advances by; n_mma: UMMA N (chunk_px rounded up to 16, <= 256);
   // kr > 0 (generic shapes only): a chunk is 2*kr whole image rows of width wd, and level 1 is pooled from it here
   extern __shared__ uint8_t smem_raw[];
@@ -539,7 +540,7 @@ size_t corr_volume_tc_workspace(int n1, int n2, int C, int ht, int wd) {
 // f1 [n1,C,ht,wd], f2 [n2,C,ht,wd]; edge e correlates f1[idx1[e]] with f2[idx2[e]] (idx null: e itself).
 int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int* idx1, const int* idx2, int n, int C,
                    int ht, int wd, int levels, __half* const* out, void* workspace, size_t workspace_bytes,
-                   cudaStream_t st, int* levels_done, const int* out_slot, int n_out) {
+                   cudaStream_t st, int* levels_done, const int* out_slot, int n_out, const int* bad_flag) {
   // out_slot / n_out: edge e is written to slot out_slot[e] of outputs that hold n_out volumes (null: e itself, n)
   *levels_done = 0;
   const int HW = ht * wd;
@@ -586,8 +587,8 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[dev_id & 63][fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTcFused, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
-  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot);
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTcFused, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot, bad_flag);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot, bad_flag);
   DBAF_LAUNCH_CHECK("k_volume_tc");
   // fused: all requested levels are written; generic with row-pair chunks: levels 0 and 1; otherwise level 0 only.
   // The caller pools the rest.

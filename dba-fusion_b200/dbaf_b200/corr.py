@@ -3,7 +3,12 @@ by the native volume+pyramid kernel and the single-launch pyramid lookup.
 
 Differences from the reference are internal only: the volume and its pyramid come from one
 native call instead of torch.matmul + 3x avg_pool2d, and the four per-level lookups are one
-launch.  Shapes, dtypes and values of everything a caller sees are the same.
+launch.  Shapes and values of everything a caller sees are the same on the inference path
+(float16 feature maps under torch.no_grad, what DBA-Fusion runs: dbaf/depth_video.py:64, dbaf/dbaf.py:53).
+
+Restriction: the native volume kernel is float16 and not an autograd op.  Float32 feature maps are cast to half
+(the reference's float32 training path keeps float32 volumes), and no gradient reaches the feature maps through
+CorrBlock; with gradients enabled on the inputs the constructors raise instead of silently cutting the graph.
 """
 from __future__ import annotations
 
@@ -39,6 +44,9 @@ class CorrBlock:
         self.num_levels = num_levels
         self.radius = radius
         batch, num, dim, ht, wd = fmap1.shape
+        if torch.is_grad_enabled() and (fmap1.requires_grad or fmap2.requires_grad):
+            raise RuntimeError("CorrBlock (B200): inference only -- the native volume kernel has no backward; build the "
+                               "volume with torch.matmul + avg_pool2d to train through it")
         f1 = fmap1.reshape(batch * num, dim, ht, wd).contiguous()
         f2 = fmap2.reshape(batch * num, dim, ht, wd).contiguous()
         if f1.dtype != torch.float16:
@@ -162,6 +170,7 @@ class CorrPool:
         self.pool = [torch.empty(self.capacity, ht, wd, ht >> l, wd >> l, dtype=dtype, device=device)
                      for l in range(self.num_levels)]
         self.slots = torch.empty(0, dtype=torch.int32, device=device)      # slot of every live edge, in edge order
+        self._slots_host = []                                              # the same list on the host
         self._free = list(range(self.capacity - 1, -1, -1))               # host-side free list (pop from the end)
 
     def __len__(self):
@@ -181,13 +190,17 @@ class CorrPool:
         f2 = f1 if fmaps2 is fmaps1 else (fmaps2 if fmaps2.dtype == torch.float16 else fmaps2.half())
         droid_backends.corr_volume_pyramid_pool(f1.contiguous(), f2.contiguous(), ii, jj, new_t, self.pool)
         self.slots = torch.cat([self.slots, new_t])
+        self._slots_host.extend(new)
 
     def keep(self, mask):
         """Drop the edges where `mask` is False (the reference's `corr = corr[~remove_mask]`)."""
-        mask = mask.to(self.slots.device)
-        gone = self.slots[~mask].tolist()
+        keep = mask.detach().to("cpu", torch.bool).tolist()      # the one host read: the mask itself
+        if len(keep) != len(self._slots_host):
+            raise RuntimeError("mask must have one entry per live edge")
+        gone = [s for s, k in zip(self._slots_host, keep) if not k]
         self._free.extend(reversed(gone))
-        self.slots = self.slots[mask].contiguous()
+        self._slots_host = [s for s, k in zip(self._slots_host, keep) if k]
+        self.slots = torch.tensor(self._slots_host, dtype=torch.int32, device=self.slots.device)
 
     def __call__(self, coords):
         """coords [batch=1, num, ht, wd, 2] as for CorrBlock.__call__ -> [1, num, levels*49, ht, wd]."""

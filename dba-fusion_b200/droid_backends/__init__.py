@@ -27,7 +27,7 @@ from ._lib import BaLayout, c_void_p, check, lib
 
 __all__ = ["set_option", "set_strict", "ba", "ba_extend", "frame_distance", "projmap", "depth_filter", "iproj",
            "altcorr_forward", "altcorr_backward", "corr_index_forward", "corr_index_backward",
-           "BACore", "corr_volume_pyramid", "corr_lookup_pyramid", "ba_tables", "ba_info"]
+           "BACore", "ba2gtsam_matrix", "corr_volume_pyramid", "corr_lookup_pyramid", "corr_volume_status", "ba_tables", "ba_info"]
 
 DBAF_F16, DBAF_F32 = 0, 1
 _strict = os.environ.get("DBAF_STRICT", "0") not in ("", "0")
@@ -52,6 +52,28 @@ def set_strict(on=True):
     """In strict mode `ba` synchronises after the call and raises on a bad edge index or an eta/K mismatch."""
     global _strict
     _strict = bool(on)
+
+
+_volume_ws = None          # workspace of the most recent indexed / pool volume build: its tail holds the status word
+
+
+def corr_volume_status():
+    """0 if the most recent corr_volume_pyramid_indexed / corr_volume_pyramid_pool call had all its frame indices and
+    slots in range, 1 otherwise (the call then wrote nothing).  Synchronises the current stream."""
+    if _volume_ws is None:
+        return 0
+    ws, nbytes = _volume_ws
+    st = torch.zeros(1, dtype=torch.int32).pin_memory()
+    check(lib.dbaf_corr_volume_status(_p(ws), nbytes, _p(st), _stream()), "dbaf_corr_volume_status")
+    torch.cuda.current_stream().synchronize()
+    return int(st[0])
+
+
+def _volume_done(ws, nbytes, what):
+    global _volume_ws
+    _volume_ws = (ws, nbytes)
+    if _strict and corr_volume_status():
+        raise RuntimeError(f"{what}: frame index or slot out of range")
 
 
 def _raise_on_flags(info, what):
@@ -445,6 +467,24 @@ class BACore:
         return [self.dx, self.dz]
 
 
+def ba2gtsam_matrix(Tbc):
+    """The 6x6 matrix A of BA2GTSAM (dbaf/depth_video.py:21-23) from the body<-camera extrinsic Tbc, given as a 4x4
+    homogeneous matrix (what gtsam.Pose3.matrix() returns): A0 = -Adjoint(Tbc^-1) in GTSAM's (rotation, translation)
+    tangent order, i.e. for T = (R, t) Adjoint(T) = [[R, 0], [skew(t) R, R]], then the two row triples swapped.
+    Feed the result to BACore.hessian_gtsam."""
+    import numpy as np
+    T = np.asarray(Tbc, np.float64).reshape(4, 4)
+    R, t = T[:3, :3], T[:3, 3]
+    Ri, ti = R.T, -R.T @ t                                  # Tbc^-1
+    sk = np.array([[0.0, -ti[2], ti[1]], [ti[2], 0.0, -ti[0]], [-ti[1], ti[0], 0.0]])
+    A0 = np.zeros((6, 6))
+    A0[:3, :3] = Ri
+    A0[3:, :3] = sk @ Ri
+    A0[3:, 3:] = Ri
+    A0 = -A0
+    return np.concatenate([A0[3:6], A0[0:3]], axis=0)
+
+
 def ba_tables(ii, jj, t0, t1, n_frames, ht=1, wd=1):
     """Graph bookkeeping tables built on the device (kx, kk_exp, csr_ptr/csr_idx, srow_ptr/srow_idx)
     as int64 CPU tensors -- the tables ba_cuda derives at src/droid_kernels.cu:1416-1424,
@@ -626,7 +666,8 @@ def corr_volume_pyramid_indexed(fmaps1, fmaps2, ii, jj, num_levels=4):
     """CorrBlock(video.fmaps[ii,0], video.fmaps[jj,c]) (dbaf/covisible_graph.py:129-131) without the gather:
     fmaps1 [n1,C,ht,wd], fmaps2 [n2,C,ht,wd] float16 frame stacks (they may be the same tensor), ii/jj edge
     lists -> list of `num_levels` tensors [E,ht,wd,ht>>l,wd>>l] float16, bit-identical to
-    corr_volume_pyramid(fmaps1[ii], fmaps2[jj])."""
+    corr_volume_pyramid(fmaps1[ii], fmaps2[jj]).  An index outside its stack makes the call write nothing; it is
+    reported by corr_volume_status() (or raised here in strict mode) -- the call itself never synchronises."""
     _contig(fmaps1=fmaps1, fmaps2=fmaps2)
     _cuda(torch.float16, fmaps1=fmaps1, fmaps2=fmaps2)
     n1, C, ht, wd = fmaps1.shape
@@ -646,6 +687,7 @@ def corr_volume_pyramid_indexed(fmaps1, fmaps2, ii, jj, num_levels=4):
     check(lib.dbaf_corr_volume_pyramid_indexed(_p(fmaps1), n1, _p(fmaps2), n2, _p(ii32), _p(jj32), E, C, ht, wd,
                                                num_levels, arr, _p(ws), nbytes, _stream()),
           "dbaf_corr_volume_pyramid_indexed")
+    _volume_done(ws, nbytes, "corr_volume_pyramid_indexed")
     return outs
 
 
@@ -674,6 +716,7 @@ def corr_volume_pyramid_pool(fmaps1, fmaps2, ii, jj, slots, pool):
     check(lib.dbaf_corr_volume_pyramid_pool(_p(fmaps1), n1, _p(fmaps2), n2, _p(ii32), _p(jj32), _p(sl32), E, cap, C, ht,
                                             wd, len(pool), arr, _p(ws), nbytes, _stream()),
           "dbaf_corr_volume_pyramid_pool")
+    _volume_done(ws, nbytes, "corr_volume_pyramid_pool")
 
 
 def corr_lookup_pyramid_pool(pool, coords, slots, radius=3):

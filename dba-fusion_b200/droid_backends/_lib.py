@@ -52,6 +52,7 @@ SIGNATURES = {
     "dbaf_corr_volume_indexed_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int]),
     "dbaf_corr_volume_pyramid_indexed": (c_int, [P, c_int, P, c_int, P, P, c_int, c_int, c_int, c_int, c_int,
                                                  ctypes.POINTER(c_void_p), P, c_size_t, P]),
+    "dbaf_corr_volume_status": (c_int, [P, c_size_t, P, P]),
     "dbaf_corr_volume_pyramid_pool": (c_int, [P, c_int, P, c_int, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int,
                                               ctypes.POINTER(c_void_p), P, c_size_t, P]),
     "dbaf_corr_lookup_pyramid_pool": (c_int, [ctypes.POINTER(c_void_p), c_int, c_int, P, P] + [c_int] * 7 + [P, P]),

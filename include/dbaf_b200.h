@@ -162,10 +162,13 @@ int dbaf_corr_volume_pyramid(const void* fmap1, const void* fmap2, int n, int C,
  * of dbaf/covisible_graph.py:129-131 with the two gathers folded in: edge e correlates fmaps1[ii[e]] with
  * fmaps2[jj[e]].  fmaps1 [n1,C,ht,wd], fmaps2 [n2,C,ht,wd] fp16 (may be the same pointer: it is then laid out
  * once); ii, jj int32[n_edges] on the device; out_host[l] is [n_edges,ht,wd,ht>>l,wd>>l] fp16.  Results are
- * bit-identical to dbaf_corr_volume_pyramid on the gathered maps.  An index outside its stack is an error
- * (checked on the device; the call synchronises the stream once to read the flag).
- * workspace: dbaf_corr_volume_indexed_workspace_bytes(n1,n2,C,ht,wd) bytes of device scratch. */
+ * bit-identical to dbaf_corr_volume_pyramid on the gathered maps.  An index (or, for the pool variant, a slot) outside
+ * its range is caught on the device before anything is computed: the call raises a status word inside the workspace,
+ * its remaining kernels write nothing, and nothing synchronises; dbaf_corr_volume_status() copies the word (0 = ok,
+ * 1 = bad index) to the host on `stream` for the caller to read after its next synchronisation.
+ * workspace: dbaf_corr_volume_indexed_workspace_bytes(n1,n2,C,ht,wd) bytes of device scratch (required). */
 size_t dbaf_corr_volume_indexed_workspace_bytes(int n1, int n2, int C, int ht, int wd);
+int dbaf_corr_volume_status(const void* workspace, size_t workspace_bytes, int32_t* status_host, void* stream);
 int dbaf_corr_volume_pyramid_indexed(const void* fmaps1, int n1, const void* fmaps2, int n2,
                                      const int32_t* ii, const int32_t* jj, int n_edges, int C, int ht,
                                      int wd, int levels, void* const* out_host, void* workspace,

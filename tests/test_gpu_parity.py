@@ -403,11 +403,18 @@ def test_volume_pyramid_indexed_equals_gathered(dev, db, synth, cfg, shared):
 def test_volume_pyramid_indexed_rejects_bad_index(dev, db, synth):
     fa = torch.from_numpy(synth.make_features("tiny", seed=5, n_frames=3)).to(dev)
     ii = torch.tensor([0, 1], device=dev)
+    # the call never synchronises: a bad index raises a status word on the device and nothing is written
+    out = db.corr_volume_pyramid_indexed(fa, fa, ii, torch.tensor([1, 3], device=dev), 2)
+    assert db.corr_volume_status() == 1
+    for o in out:
+        o.fill_(7.0)
+    db.corr_volume_pyramid_indexed(fa, fa, torch.tensor([-1, 0], device=dev), ii, 2)
+    assert db.corr_volume_status() == 1 and all(float(o.min()) == 7.0 for o in out)
+    db.corr_volume_pyramid_indexed(fa, fa, ii, torch.tensor([1, 2], device=dev), 2)
+    assert db.corr_volume_status() == 0
+    db.set_strict(True)
     with pytest.raises(RuntimeError, match="out of range"):
         db.corr_volume_pyramid_indexed(fa, fa, ii, torch.tensor([1, 3], device=dev), 2)
-    with pytest.raises(RuntimeError, match="out of range"):
-        db.corr_volume_pyramid_indexed(fa, fa, torch.tensor([-1, 0], device=dev), ii, 2)
-    db.corr_volume_pyramid_indexed(fa, fa, ii, torch.tensor([1, 2], device=dev), 2)
 
 
 def test_altcorr_vs_oracle_and_volume_path(dev, db, oracle, synth):

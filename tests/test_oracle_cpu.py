@@ -345,3 +345,32 @@ def test_ba2gtsam_blockwise(oracle):
     assert np.allclose(Hg, Hg.T)
     H2, v2 = oracle.ba2gtsam(H, v, -np.eye(6))
     assert np.allclose(H2, H) and np.allclose(v2, -v)
+
+
+def test_ba2gtsam_matrix_is_the_row_swapped_negative_adjoint(db):
+    """A = rows-swapped -Adjoint(Tbc^-1) (dbaf/depth_video.py:21-23).  The Adjoint is pinned by its defining property
+    T hat(xi) T^-1 = hat(Adjoint(T) xi) for GTSAM's (omega, v) tangent order, checked on random poses."""
+    rng = np.random.default_rng(0)
+
+    def hat(xi):
+        w, v = xi[:3], xi[3:]
+        M = np.zeros((4, 4))
+        M[:3, :3] = [[0, -w[2], w[1]], [w[2], 0, -w[0]], [-w[1], w[0], 0]]
+        M[:3, 3] = v
+        return M
+
+    for _ in range(5):
+        q = rng.normal(size=4)
+        q /= np.linalg.norm(q)
+        x, y, z, w = q
+        R = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)],
+                      [2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)],
+                      [2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)]])
+        T = np.eye(4)
+        T[:3, :3], T[:3, 3] = R, rng.normal(size=3)
+        A = db.ba2gtsam_matrix(T)
+        A0 = -np.concatenate([A[3:6], A[0:3]], axis=0)            # undo the swap and the sign: Adjoint(T^-1)
+        Ti = np.linalg.inv(T)
+        for _ in range(3):
+            xi = rng.normal(size=6)
+            assert np.allclose(Ti @ hat(xi) @ T, hat(A0 @ xi), atol=1e-12)

@@ -57,6 +57,38 @@ def test_noalloc_tables_match_regular_entry_point_twice(dev, db):
         assert np.array_equal(got["csr_idx"], want["csr_idx"].numpy())
 
 
+def _numpy_tables(ii, jj, t0, t1):
+    """The same tables from first principles: kx = sorted unique of cat(arange(t0,t1), ii) with its inverse map
+    (src/droid_kernels.cu:1416-1424), and the edges grouped by source frame in ascending edge order."""
+    ii = np.asarray(ii, np.int64)
+    P = t1 - t0
+    kx, inv = np.unique(np.concatenate([np.arange(t0, t1, dtype=np.int64), ii]), return_inverse=True)
+    k_of_edge = inv[P:]
+    order = np.argsort(k_of_edge, kind="stable")
+    ptr = np.concatenate([[0], np.cumsum(np.bincount(k_of_edge, minlength=len(kx)))])
+    return kx, inv, ptr, order
+
+
+def test_noalloc_tables_match_numpy_at_the_size_limits(dev):
+    """Exactly at the advertised limits (16 384 frames, 262 144 edges), where the carve-up of the fixed array reaches
+    its largest offsets, and compared with numpy rather than with the other entry point (which runs the same
+    kernel); then a small graph again to show that nothing of the large call survives in the shared array."""
+    from droid_backends import _lib
+    lib = _lib.lib
+    rng = np.random.default_rng(7)
+    for n_frames, n_edges, t0 in ((16384, 262144, 3), (12, 30, 2)):
+        t1 = n_frames
+        ii_h = rng.integers(0, n_frames, n_edges)
+        jj_h = rng.integers(0, n_frames, n_edges)
+        got = _noalloc_tables(lib, torch.from_numpy(ii_h).to(dev), torch.from_numpy(jj_h).to(dev), t0, t1, n_frames, dev)
+        kx, inv, ptr, order = _numpy_tables(ii_h, jj_h, t0, t1)
+        assert got["K"] == len(kx) and got["info"][2] == 0
+        assert np.array_equal(got["kx"], kx)
+        assert np.array_equal(got["kk_exp"], inv)
+        assert np.array_equal(got["csr_ptr"], ptr)
+        assert np.array_equal(got["csr_idx"], order)
+
+
 def test_noalloc_rejects_sizes_beyond_its_fixed_array(dev):
     from droid_backends import _lib
     lib = _lib.lib
