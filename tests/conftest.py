@@ -58,6 +58,20 @@ def _default_kernel_options():
 
 
 @pytest.fixture(scope="session")
+def dbt():
+    """droid_backends as a compiled torch extension over the same C ABI (dba-fusion_b200/torch_ext)."""
+    import importlib.util
+    path = os.path.join(ROOT, "dba-fusion_b200", "torch_ext", "build.py")
+    spec = importlib.util.spec_from_file_location("dbaf_torch_ext_build", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    ext = mod.load()
+    if ext is None:
+        pytest.skip("droid_backends_torch.so not built (python dba-fusion_b200/torch_ext/build.py)")
+    return ext
+
+
+@pytest.fixture(scope="session")
 def ref():
     """The reference CUDA extension rebuilt for sm_100a (oracle/_ref/droid_backends_ref.so)."""
     import build_ref

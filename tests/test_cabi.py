@@ -60,3 +60,19 @@ def test_contiguity_errors_like_the_reference(db):
         db.frame_distance(t.t(), t, t, t.long(), t.long(), 0.3)
     with pytest.raises(RuntimeError, match="CUDA"):
         db.iproj(t, torch.zeros(4, 2, 2), torch.zeros(4))
+
+
+def test_compiled_torch_extension_exports_the_reference_surface(dbt):
+    """The torch-extension build of the binding (what src/droid.cpp becomes) loads without a GPU and registers the
+    eleven names of src/droid.cpp:297-316."""
+    for name in ("ba", "ba_extend", "frame_distance", "projmap", "depth_filter", "iproj",
+                 "altcorr_forward", "altcorr_backward", "corr_index_forward", "corr_index_backward", "BACore"):
+        assert hasattr(dbt, name)
+    core = dbt.BACore()
+    for m in ("init", "hessian", "optimize", "retract"):
+        assert callable(getattr(core, m))
+    import pytest
+    import torch
+    t = torch.zeros(4, 7)
+    with pytest.raises(RuntimeError, match="must be contiguous"):
+        dbt.frame_distance(t.t(), t, t, t.long(), t.long(), 0.3)

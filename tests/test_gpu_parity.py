@@ -567,3 +567,50 @@ def test_corr_pool_matches_rebuilt_corrblock(dev, db, synth, cfg):
         assert torch.equal(got.view(torch.int16), want.view(torch.int16)), (cfg, step)
     with pytest.raises(RuntimeError, match="full"):
         pool.append(f, f, torch.zeros(30, dtype=torch.long, device=dev), torch.zeros(30, dtype=torch.long, device=dev))
+
+
+# ------------------------------------------------------------- compiled torch extension ----
+def test_torch_extension_matches_ctypes_binding(dev, db, dbt, synth):
+    """droid_backends_torch (pybind/torch extension over the C ABI, dba-fusion_b200/torch_ext) against the ctypes
+    package: same library underneath, so identical bits for every operator of the reference surface."""
+    w = _window(synth, "tiny", seed=9, sensor_frac=0.3)
+    n = 6 * (w["t1"] - w["t0"])
+    res = []
+    for mod in (db, dbt):
+        t = to_torch(w, dev)
+        out = {}
+        dx, dz = mod.ba(*ba_args(t), w["t0"], w["t1"], 2, 1e-4, 0.1, False)
+        out["ba"] = (dx.clone(), dz.clone(), t["poses"].clone(), t["disps"].clone())
+        t = to_torch(w, dev)
+        core = mod.BACore()
+        core.init(*ba_args(t), w["t0"], w["t1"], 2, 1e-4, 0.1, False)
+        H = torch.zeros(n, n, dtype=torch.float64)
+        v = torch.zeros(n, dtype=torch.float64)
+        core.hessian(H, v)
+        dxr, dzr = core.retract(torch.from_numpy(np.random.default_rng(5).normal(0, 1e-3, n)))
+        out["core"] = (H.clone(), v.clone(), dxr.clone(), dzr.clone(), t["poses"].clone(), t["disps"].clone())
+        t = to_torch(w, dev)
+        H2 = torch.zeros(n, n, dtype=torch.float64)
+        v2 = torch.zeros(n, dtype=torch.float64)
+        prior = torch.eye(12, dtype=torch.float64) * 1e6
+        dxe, dze = mod.ba_extend(*ba_args(t), H2, v2, prior, w["t0"], w["t1"], 1, 1e-4, 0.1, False, False)
+        out["ext"] = (H2.clone(), v2.clone(), dxe.clone(), dze.clone())
+        t = to_torch(w, dev)
+        out["geom"] = (mod.frame_distance(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"], 0.3),
+                       *mod.projmap(t["poses"], t["disps"], t["intrinsics"], t["ii"], t["jj"]),
+                       mod.iproj(t["poses"], t["disps"], t["intrinsics"]))
+        res.append(out)
+    a, b = res
+    for key in a:
+        for x, y in zip(a[key], b[key]):
+            assert x.shape == y.shape and torch.equal(x.cpu(), y.cpu()), key
+    f1, f2, coords = _corr_case(synth, "tiny", 3)
+    vol = db.corr_volume_pyramid(torch.from_numpy(f1).to(dev), torch.from_numpy(f2).to(dev), 1)[0]
+    ct = torch.from_numpy(coords).to(dev)
+    assert torch.equal(db.corr_index_forward(vol, ct, 3)[0], dbt.corr_index_forward(vol, ct, 3)[0])
+    g = torch.randn_like(db.corr_index_forward(vol.float(), ct, 3)[0])
+    assert torch.equal(db.corr_index_backward(vol.float(), ct, g, 3)[0], dbt.corr_index_backward(vol.float(), ct, g, 3)[0])
+    af1 = torch.from_numpy(np.ascontiguousarray((f1.astype(np.float32) / 4.0).transpose(0, 2, 3, 1))).to(dev)
+    af2 = torch.from_numpy(np.ascontiguousarray((f2.astype(np.float32) / 4.0).transpose(0, 2, 3, 1))).to(dev)
+    ac = ct.permute(0, 2, 3, 1)[:, None].contiguous()
+    assert torch.equal(db.altcorr_forward(af1, af2, ac, 3)[0], dbt.altcorr_forward(af1, af2, ac, 3)[0])
