@@ -183,12 +183,15 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
     factor_diag6(L, ld, 0, dinv, fail);
   }
   __syncthreads();
+  const int nwork = nt - 32;                           // the last warp runs the look-ahead chain
   for (int J = 0; J < P; ++J) {
     const int j0 = 6 * J;
     // the diagonal block of this column was factorised during the previous step (look-ahead, see below)
     if (*fail) return false;
-    // (1) panel below the block (rows j0+6 .. n, row n = rhs): X L_JJ^T = A
-    for (int r = j0 + 6 + tid; r <= n; r += nt) {
+    const int r0 = j0 + 6;
+    const int mrows = n - r0 + 1;                      // rows below the block, the right-hand side (row n) included
+    // row r of the panel: x L_JJ^T = a
+    auto panel_row = [&](int r) {
       double row[6];
 #pragma unroll
       for (int c = 0; c < 6; ++c) {
@@ -200,18 +203,17 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
       }
 #pragma unroll
       for (int c = 0; c < 6; ++c) L[(size_t)r * ld + j0 + c] = row[c];
-    }
-    __syncthreads();
-    // (2) trailing update A[r][c] -= sum_k L[r][j0+k] L[c][j0+k] for j0+6 <= c <= min(r, n-1), r <= n.
-    //     Look-ahead: the last warp first updates the next diagonal block (21 entries, one lane each) and
-    //     its lane 0 factorises it at once, so the serial pivot chain of column J+1 runs under the bulk of this
-    //     update instead of after it; the other warps skip that block.
-    const int r0 = j0 + 6;
-    const int mrows = n - r0 + 1;
-    const int nwork = nt - 32;
-    if (mrows > 1) {
-      if (tid >= nwork) {
-        const int ln = tid - nwork;
+    };
+    if (tid >= nwork) {
+      // Look-ahead warp: the serial chain of the factorisation.  It solves the six panel rows of the NEXT block row
+      // itself, publishes them to the other warps (arrive, no wait), applies this column's update to the next
+      // diagonal block (21 entries, one lane each) and factorises it on lane 0 -- so the chain from one diagonal
+      // factor to the next never waits for the rest of the panel or for the trailing update.
+      const int ln = tid - nwork;
+      if (mrows > 1 && ln < 6) panel_row(r0 + ln);
+      __syncwarp();
+      asm volatile("bar.arrive 1, %0;" ::"r"(nt) : "memory");
+      if (mrows > 1) {
         if (ln < 21) {
           int r, c;
           tri_unpack(ln, r, c);
@@ -224,7 +226,14 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
         }
         __syncwarp();
         if (ln == 0) factor_diag6(L, ld, r0, dinv, fail);
-      } else {
+      }
+    } else {
+      // (1) the rest of the panel (the next block's six rows are the look-ahead warp's), row n = right-hand side
+      for (int r = (mrows > 1 ? r0 + 6 : r0) + tid; r <= n; r += nwork) panel_row(r);
+      asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");      // the whole panel, the look-ahead warp's rows included
+      // (2) trailing update A[r][c] -= sum_k L[r][j0+k] L[c][j0+k] for j0+6 <= c <= min(r, n-1), r <= n; the next
+      //     diagonal block is the look-ahead warp's
+      if (mrows > 1) {
         // 15 x 16 thread grid over the (rows x cols) triangle: no integer division, the row's six panel
         // values are loaded once per row and reused along it
         const int ty = tid >> 4, tx = tid & 15;
@@ -325,13 +334,29 @@ k_solve6(int P, float lm, float ep, const double* __restrict__ prior, int prior_
 #else
 #define SQ_TICK(i) do {} while (0)
 #endif
-  for (int i = tid >> 4; i < n; i += (nt >> 4)) {
-    for (int c = tid & 15; c <= i; c += 16) {
-      const size_t t = (size_t)i * n + c;
-      double a = ws.H[t];
-      if (prior) a += (i < prior_rows && c < prior_cols) ? prior[(size_t)i * prior_cols + c] : ws.H[t];
-      if (i == c) a += (double)ep + (double)lm * a;
-      L[(size_t)i * ld + c] = a;
+  // lower triangle, eight independent loads per thread and pass (the matrix comes from HBM or a far L2 slice: one
+  // exposed latency per pass instead of one per element)
+  const int n_tri = n * (n + 1) / 2;
+  for (int t0 = tid; t0 < n_tri; t0 += 8 * nt) {
+    double a[8];
+    int ii[8], cc[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int t = t0 + u * nt;
+      ii[u] = -1;
+      if (t < n_tri) {
+        tri_unpack(t, ii[u], cc[u]);
+        a[u] = ws.H[(size_t)ii[u] * n + cc[u]];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      if (ii[u] < 0) continue;
+      const int i = ii[u], c = cc[u];
+      double v = a[u];
+      if (prior) v += (i < prior_rows && c < prior_cols) ? prior[(size_t)i * prior_cols + c] : v;
+      if (i == c) v += (double)ep + (double)lm * v;
+      L[(size_t)i * ld + c] = v;
     }
   }
   for (int i = tid; i < n; i += nt) L[(size_t)n * ld + i] = ws.v[i];

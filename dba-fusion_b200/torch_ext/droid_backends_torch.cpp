@@ -222,7 +222,9 @@ std::vector<torch::Tensor> altcorr_backward(torch::Tensor fmap1, torch::Tensor f
   return {g1, g2, gc};
 }
 
-// src/bacore.h:4-70, src/droid_kernels.cu:1786-1956
+// src/bacore.h:4-70, src/droid_kernels.cu:1786-1956.  (In a namespace of its own and registered module-local: the
+// reference extension, when loaded into the same process, registers a global C++ type of the same name.)
+namespace dbaf_torch {
 class BACore {
  public:
   void init(torch::Tensor _poses, torch::Tensor _disps, torch::Tensor _intrinsics, torch::Tensor _disps_sens,
@@ -268,6 +270,8 @@ class BACore {
   float lm = 0.f, ep = 0.f;
   Window w;
 };
+}  // namespace dbaf_torch
+using dbaf_torch::BACore;
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("ba", &ba, "bundle adjustment");
@@ -280,7 +284,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("altcorr_backward", &altcorr_backward, "ALTCORR backward");
   m.def("corr_index_forward", &corr_index_forward, "INDEX forward");
   m.def("corr_index_backward", &corr_index_backward, "INDEX backward");
-  py::class_<BACore>(m, "BACore").def(py::init<>())
+  py::class_<BACore>(m, "BACore", py::module_local()).def(py::init<>())
       .def("init", &BACore::init)
       .def("hessian", &BACore::hessian)
       .def("optimize", &BACore::optimize)
