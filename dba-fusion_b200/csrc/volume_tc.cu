@@ -36,7 +36,9 @@ constexpr int kKBlock = 64;       // channels per 128-byte swizzle row
 constexpr int kSmemA = kBM * kC * 2;                 // 32 KB
 constexpr int kSmemB = kBN * kC * 2;                 // 64 KB
 constexpr int kStageWarp = 3 * 4096;                 // per fused epilogue warp: 2 level-0 boxes + 1 level-1 box, 32 px x 128 B each
-constexpr int kSmemStage = 8 * kStageWarp;           // 96 KB (the four generic-shape epilogue warps use 24 KB each)
+// generic shapes stage a 32 x n_mma tile per epilogue warp with an odd word pitch; eight warps fit up to a pitch of 121
+constexpr int kGenPitchMax = 121;
+constexpr int kSmemStage = 8 * 32 * kGenPitchMax * 4;    // 121 KB (the fused kernel uses 8 x 12 KB of it)
 // pipeline depth.  Fused (64-wide frames): chunks of 128 target pixels (two image rows), two B buffers of 32 KB and
 // four 128-column accumulators, so that the next B tile is on its way while the tensor core and the epilogue work.
 // Generic shapes: chunks of up to 256 pixels, one B buffer, two 256-column accumulators.
@@ -47,8 +49,9 @@ template <bool FUSE> struct Pipe {
 };
 constexpr int kBarA = 0, kBarBFull = 1, kBarBFree = 3, kBarAccFull = 5 /* [epilogue set][stage] */, kBarAccFree = 13, kNumBars = 17;
 constexpr int kSmemBytes = kSmemA + kSmemB + kSmemStage + 1024 /*alignment slack*/ + 256 /*barriers*/;
-constexpr int kThreadsTc = 256;   // warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7: epilogue
-constexpr int kThreadsTcFused = 384;   // fused kernel: a second set of epilogue warps (8-11) takes every other group of chunks
+// warp 0: TMA, warp 1: MMA, warp 2: TMEM alloc, warps 4-7 and 8-11: two sets of epilogue warps that take the chunks
+// in turn (fused: groups of four chunks; generic shapes: every other chunk)
+constexpr int kThreadsTc = 384;
 
 // instruction descriptor, kind::f16: D = F32 (bit 4), A = B = F16, both K-major, N >> 3 at bit 17, M >> 4 at bit 24
 
@@ -89,11 +92,13 @@ __global__ void __launch_bounds__(256) k_to_pixel_major(const __half* __restrict
 
 // ------------------------------------------------------------------ main kernel ----
 template <bool FUSE>
-__global__ void __launch_bounds__(FUSE ? kThreadsTcFused : kThreadsTc, 1)
+__global__ void __launch_bounds__(kThreadsTc, 1)
 k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB,
             const __grid_constant__ CUtensorMap mapO0, const __grid_constant__ CUtensorMap mapO1,
             int HW, int m_tiles, Pyr out, const int* __restrict__ idx1, const int* __restrict__ idx2,
-            int chunk_px, int n_mma, int kr, int wd, const int* __restrict__ out_slot, const int* __restrict__ bad_flag) {
+            int chunk_px, int n_mma, int kr, int wd, const int* __restrict__ out_slot, const int* __restrict__ bad_flag,
+            int n_sets) {
+  // n_sets: generic shapes only -- 2 when the staged tiles of eight epilogue warps fit into shared memory, else 1
   if (bad_flag && *bad_flag) return;                 // an edge index outside its frame stack (checked by k_check_index)
   // chunk_px: target pixels a chunk advances by; n_mma: UMMA N (chunk_px rounded up to 16, <= 256);
   // kr > 0 (generic shapes only): a chunk is 2*kr whole image rows of width wd, and level 1 is pooled from it here
@@ -216,7 +221,7 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
       tc_commit(smem_u32(&bars[kBarBFree + b]));     // B buffer may be overwritten once these MMAs are done
       // accumulator stage s is complete: tell the epilogue warp set that owns this chunk (each set has its own
       // barriers, so that it sees their phases one by one whatever the other set does)
-      tc_commit(smem_u32(&bars[kBarAccFull + (FUSE ? ((c >> 2) & 1) * 4 : 0) + s]));
+      tc_commit(smem_u32(&bars[kBarAccFull + (FUSE ? ((c >> 2) & 1) : (n_sets == 2 ? (c & 1) : 0)) * 4 + s]));
       MP_TICK(2);
     }
 #ifdef DBAF_VOL_PROFILE
@@ -253,8 +258,9 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
       // fused: four chunks (eight target rows, one level-3 row) form a group and the two warp sets take the groups
       // in turn
       if (FUSE && ((c >> 2) & 1) != eset) continue;
+      if (!FUSE && (n_sets == 2 ? (c & 1) != eset : eset != 0)) continue;    // generic: every other chunk (= one stage each)
       const int cd = data_chunk(c);                    // which chunk of the target frame this pipeline step holds
-      mbar_wait(smem_u32(&bars[kBarAccFull + eset * 4 + s]), (FUSE ? (c >> 3) : u) & 1);
+      mbar_wait(smem_u32(&bars[kBarAccFull + eset * 4 + s]), (FUSE ? (c >> 3) : (n_sets == 2 ? (c >> 1) : u)) & 1);
       tc_fence_after();
       VP_TICK(0);
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * ACC_COLS);
@@ -402,15 +408,17 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         // 129-word row pitch (conflict-free both ways) and written out row by row, every store instruction
         // covering 64 contiguous bytes of one row.
         const int n0 = cd * chunk_px;
-        uint32_t* tile = reinterpret_cast<uint32_t*>(sStage + q * (2 * kStageWarp));      // [32][129] words
+        const int nb = (n_mma + 31) >> 5;                // 32-column blocks of the accumulator that hold data
+        const int tp = 16 * nb + 1;                      // tile pitch in words (odd: conflict-free both ways)
+        uint32_t* tile = reinterpret_cast<uint32_t*>(sStage) + (size_t)(eset * 4 + q) * 32 * tp;      // [32][tp] words
         __syncwarp();                                    // the previous chunk's rows have been read out
 #pragma unroll 1
-        for (int b = 0; b < kBN / 32; ++b) {
+        for (int b = 0; b < nb; ++b) {
           float v[32];
           tc_ld32(t0 + (uint32_t)(b * 32), v);
 #pragma unroll
           for (int i = 0; i < 16; ++i)
-            tile[lane * 129 + b * 16 + i] = pack_h2(__float2half_rn(v[2 * i]), __float2half_rn(v[2 * i + 1]));
+            tile[lane * tp + b * 16 + i] = pack_h2(__float2half_rn(v[2 * i]), __float2half_rn(v[2 * i + 1]));
         }
         // the accumulator stage is free as soon as it sits in shared memory
         tc_fence_before();
@@ -425,9 +433,9 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
         for (int r = 0; r < nrow; ++r) {
           unsigned short* dst = reinterpret_cast<unsigned short*>(out.l[0]) + ((size_t)eo * HW + mrow0 + r) * (size_t)HW + n0 + lane;
           unsigned short v[kBN / 32];
-          const unsigned short* src = reinterpret_cast<const unsigned short*>(tile) + r * 258 + lane;
+          const unsigned short* src = reinterpret_cast<const unsigned short*>(tile) + r * (2 * tp) + lane;
 #pragma unroll
-          for (int k = 0; k < kBN / 32; ++k) v[k] = src[k * 32];
+          for (int k = 0; k < kBN / 32; ++k) v[k] = k < nb ? src[k * 32] : (unsigned short)0;
 #pragma unroll
           for (int k = 0; k < kBN / 32; ++k)
             if (k * 32 + lane < ncol) dst[k * 32] = v[k];
@@ -452,8 +460,8 @@ k_volume_tc(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CU
                                    (size_t)cd * kr * w1;
 #pragma unroll 4
           for (int r = 0; r < nrow; ++r) {
-            const unsigned short* row16 = t16 + r * 258;
-            const uint32_t* row32 = tile + r * 129;
+            const unsigned short* row16 = t16 + r * (2 * tp);
+            const uint32_t* row32 = tile + r * tp;
 #pragma unroll
             for (int t = 0; t < 2; ++t) {
               const uint32_t ab = row32[colA[t] >> 1];
@@ -587,8 +595,10 @@ int corr_volume_tc(const __half* f1, int n1, const __half* f2, int n2, const int
     else DBAF_CUDA(cudaFuncSetAttribute(k_volume_tc<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes));
     attr[dev_id & 63][fuse] = true;
   }
-  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTcFused, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot, bad_flag);
-  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot, bad_flag);
+  // generic shapes: two sets of epilogue warps when their staged tiles fit (pitch 16 * ceil(n_mma / 32) + 1 words)
+  const int n_sets = (16 * ((n_mma + 31) / 32) + 1 <= kGenPitchMax) ? 2 : 1;
+  if (fuse) k_volume_tc<true><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot, bad_flag, 2);
+  else k_volume_tc<false><<<n * m_tiles, kThreadsTc, kSmemBytes, st>>>(mapA, mapB, mapO0, mapO1, HW, m_tiles, pyr, idx1, idx2, chunk_px, n_mma, kr, wd, out_slot, bad_flag, n_sets);
   DBAF_LAUNCH_CHECK("k_volume_tc");
   // fused: all requested levels are written; generic with row-pair chunks: levels 0 and 1; otherwise level 0 only.
   // The caller pools the rest.
