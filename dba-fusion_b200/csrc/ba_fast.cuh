@@ -123,17 +123,19 @@ k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k
 }
 
 // ------------------------------------------------------------------ solve ----
-// 1/sqrt(d) from the single-precision hardware estimate plus one Newton step in double; the library
-// rsqrt(double) is several times longer and sits on the critical path of the pivot chain.
+// 1/sqrt(d): the double-precision hardware estimate (MUFU.RSQ64H, relative error e0 ~ 2^-20) refined by one
+// third-order step, y = y0 (1 + e/2 + 3 e^2 / 8) with e = 1 - d y0^2, five dependent FMAs, error O(e0^3): full double
+// precision.  This sits on the serial pivot chain of every factorisation here.  Measured per dependent pivot step on
+// this part (scripts/experiments/pivot_chain_probe.cu): 115 cycles with a float estimate and one Newton step (two
+// format conversions on the chain), 70 with the library rsqrt, 56 with the double estimate and one Newton step
+// (1e-13 only), 8.7 for one dependent DFMA.
 __device__ __forceinline__ double rsqrt_nr(double d) {
-  if (!(d > 1e-30 && d < 1e30)) return rsqrt(d);
-  // one Newton step written as three dependent FMAs (a dependent DFMA takes ~9 cycles on this part,
-  // scripts/experiments/fp64_rate_probe.cu, and the pivot chain is pure latency): error (3/8) e0^2 with
-  // e0 ~ 2^-22, i.e. ~1e-13
-  const double y0 = (double)rsqrtf((float)d);
+  double y0;
+  asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y0) : "d"(d));
   const double t = d * y0;
   const double e = fma(-t, y0, 1.0);
-  return fma(0.5 * y0, e, y0);
+  const double q = e * fma(0.375, e, 0.5);
+  return fma(y0, q, y0);
 }
 
 // Blocked right-looking Cholesky on 6x6 pose blocks, matrix (plus the right-hand side as an extra
