@@ -46,6 +46,9 @@ struct Ws {
   float* Ei;
   float* Eij;
   double* Lfac;
+  int* fused;     // [Kcap] 1: the frame went through k_linschur_tc (no Eij; the back-substitution recomputes it)
+  float* exf;     // [E][24] relative-pose record of every edge of such a frame (LsEdge), read by k_backsub_rc
+  const float** rc_ptrs;  // [2] weights and intrinsics pointers of the last fused linearisation
   int Kcap;
 };
 
@@ -71,6 +74,9 @@ void fill_layout(int N, int E, int t0, int t1, int ht, int wd, dbaf_ba_layout* L
   L->w = take(Kcap * HW * 4);
   L->Ei = take(P * 6 * HW * 4);
   L->Eij = take((int64_t)E * 6 * HW * 4);
+  L->fused = take(Kcap * 4);
+  L->exf = take(std::max<int64_t>(1, E) * 24 * 4);
+  L->rc_ptrs = take(2 * 8);
   L->Kcap = Kcap;
   L->total_bytes = off;
 }
@@ -95,6 +101,9 @@ Ws view(void* base, const dbaf_ba_layout& L) {
   w.Ei = (float*)(b + L.Ei);
   w.Eij = (float*)(b + L.Eij);
   w.Lfac = (double*)(b + L.Lfac);
+  w.fused = (int*)(b + L.fused);
+  w.exf = (float*)(b + L.exf);
+  w.rc_ptrs = (const float**)(b + L.rc_ptrs);
   w.Kcap = (int)L.Kcap;
   return w;
 }
@@ -149,6 +158,9 @@ __global__ void __launch_bounds__(1024) k_tables(const int64_t* __restrict__ ii,
   const int P = t1 - t0;
   int* f2k = ws.frame2k;
   if (tid < 16) ws.info[tid] = 0;
+  if (ws.fused) {
+    for (int q = tid; q < ws.Kcap; q += 1024) ws.fused[q] = 0;
+  }
   for (int f = tid; f < N; f += 1024) f2k[f] = (f >= t0 && f < t1) ? 1 : 0;
   __syncthreads();
   for (int e = tid; e < E; e += 1024) {
@@ -455,12 +467,24 @@ __global__ void k_pose_retract(float* __restrict__ poses, const float* __restric
   }
 }
 
+// Dense frame graphs (global BA): frames with 8..21 row blocks go to the tensor-core Schur kernel; those with at
+// most 20 out-edges among them can be linearised and Schur-complemented in one kernel (ba_linschur_tc.cuh).
+constexpr int kStcMaxM = 21;                 // 6 * 21 = 126 rows + w + q = 128
+constexpr int kStcMinM = 8;
+constexpr int kLsMaxDeg = 20;                // out-edges per frame (120 operand rows)
+__device__ __forceinline__ bool ls_eligible(const Ws& ws, int k, int min_m) {
+  const int m = ws.srow_ptr[k + 1] - ws.srow_ptr[k];
+  const int deg = ws.csr_ptr[k + 1] - ws.csr_ptr[k];
+  return m >= min_m && m <= kStcMaxM && deg >= 1 && deg <= kLsMaxDeg;
+}
+
 #include "ba_fast.cuh"
 #include "ba_banded.cuh"
 #include "ba_banded_reg.cuh"
 #include "ba_spike.cuh"
 #include "ba_lin2.cuh"
 #include "ba_schur_tc.cuh"
+#include "ba_linschur_tc.cuh"
 
 int check_dims(int N, int E, int t0, int t1, int ht, int wd) {
   DBAF_REQUIRE(N > 0 && E >= 0 && ht > 0 && wd > 0, "non-positive size");
@@ -505,8 +529,12 @@ int pick_pxt(int Kcap, int HW) {
 }  // namespace
 
 namespace {
+// mean out-degree >= 7 over the window (frames with >= 8 row blocks exist), whole 32-pixel slices
+bool dense_graph(int E, int Kcap, int HW) { return options().schur_simt == 0 && E >= 7 * Kcap && HW % 32 == 0; }
+
 // Schur complement of the depth frames [k_lo, k_lo + k_cap): H -= E Q E^T, v -= E Q w from the E, Q, w in the workspace.
-int launch_schur(Ws ws, const int64_t* jj, int E, int t0, int P, int HW, int k_lo, int k_hi, int k_cap, cudaStream_t st) {
+int launch_schur(Ws ws, const int64_t* jj, int E, int t0, int P, int HW, int k_lo, int k_hi, int k_cap, cudaStream_t st,
+                 bool fused = false) {
   static bool schur_attr[64] = {};
   int dev_id = 0;
   DBAF_CUDA(cudaGetDevice(&dev_id));
@@ -518,9 +546,9 @@ int launch_schur(Ws ws, const int64_t* jj, int E, int t0, int P, int HW, int k_l
   // with the square of the row count; dbaf_set_option("schur_impl", "simt") keeps everything on the fp32 SIMT kernels
   const bool simt_only = options().schur_simt != 0;
   // mean out-degree >= 7, i.e. frames with >= 8 row blocks exist; whole 32-pixel slices for the 16-byte copies
-  const bool use_tc = !simt_only && E >= 7 * k_cap && HW % 32 == 0;
-  const int tc_min_m = 8;
-  if (use_tc) {
+  const bool use_tc = fused || (!simt_only && E >= 7 * k_cap && HW % 32 == 0);
+  const int tc_min_m = kStcMinM;
+  if (use_tc && !fused) {      // (fused: k_linschur_tc has already subtracted the Schur terms of the frames it took)
     static bool tc_attr[64] = {};
     if (!tc_attr[dev_id & 63]) {
       DBAF_CUDA(cudaFuncSetAttribute(k_schur_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStcSmemBytes));
@@ -536,7 +564,7 @@ int launch_schur(Ws ws, const int64_t* jj, int E, int t0, int P, int HW, int k_l
   const int S = 256;
   dim3 sgrid((HW + S - 1) / S, k_cap);
   k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, use_tc ? tc_min_m : 1,
-                                                         use_tc ? kStcMaxM : 0, ws);
+                                                         use_tc ? kStcMaxM : 0, fused ? 1 : 0, ws);
   DBAF_LAUNCH_CHECK("k_schur_smem");
   if (E + 1 > kSchurMaxRows) {
     // a depth frame can only have more than kSchurMaxRows rows if the graph has that many edges
@@ -571,12 +599,40 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
   if (k_lo < 0) k_lo = 0;
   const int k_cap = (k_hi >= 0 ? std::min(k_hi, ws.Kcap) : ws.Kcap) - k_lo;
   if (k_cap <= 0) return DBAF_OK;
+  // Dense graphs: eligible frames are linearised and Schur-complemented in one kernel that keeps the pose-depth
+  // blocks on the SM (dbaf_set_option("eij", "store") keeps the two-kernel path that writes them to the workspace).
+  // The decision uses the window's totals, not this call's frame range, so that a window processed in several
+  // ranges (dbaf_b200.global_ba) takes the same path in each.
+  const auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool fused = motion_only == 0 && P > 0 && dense_graph(E, ws.Kcap, HW) && options().eij_recompute != 0 &&
+                     al16(disps) && al16(disps_sens) && al16(targets) && al16(weights) && al16(eta);
+  if (fused) {
+    static bool ls_attr[64] = {};
+    int dev_id = 0;
+    DBAF_CUDA(cudaGetDevice(&dev_id));
+    if (!ls_attr[dev_id & 63]) {
+      DBAF_CUDA(cudaFuncSetAttribute(k_linschur_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsSmemBytes));
+      ls_attr[dev_id & 63] = true;
+    }
+    // one CTA per frame when there are enough frames to fill the machine, else split the pixels
+    int splits = std::max(1, std::min((2 * 148 + k_cap - 1) / k_cap, (HW + 255) / 256));
+    const int St = (((HW + splits - 1) / splits) + 31) & ~31;
+    splits = (HW + St - 1) / St;
+    k_depth_diag<<<dim3((HW / 4 + 127) / 128, k_cap), 128, 0, st>>>(poses, disps, intrinsics, disps_sens, weights, eta,
+                                                                   eta_rows, jj, t0, P, HW, wd, alpha, kStcMinM, k_lo,
+                                                                   k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_depth_diag");
+    k_linschur_tc<<<dim3(splits, k_cap), kLsThreads, kLsSmemBytes, st>>>(disps, intrinsics, disps_sens, targets, weights, t0,
+                                                                      P, HW, wd, alpha, St, kStcMinM, k_lo, k_hi, ws);
+    DBAF_LAUNCH_CHECK("k_linschur_tc");
+  }
+  const int skip_min_m = fused ? kStcMinM : 0;
   const int pxt = pick_pxt(k_cap, HW);
   dim3 grid((HW + 256 * pxt - 1) / (256 * pxt), k_cap);
 #define DBAF_LIN(PX, MO)                                                                       \
   k_linearize2<PX, MO><<<grid, kThreads, 0, st>>>(poses, disps, intrinsics, disps_sens, targets, \
                                                  weights, eta, eta_rows, jj, t0, P, HW, wd,    \
-                                                 alpha, k_lo, k_hi, ws)
+                                                 alpha, k_lo, k_hi, skip_min_m, ws)
   if (motion_only == 1) {
     if (pxt == 2) DBAF_LIN(2, true); else DBAF_LIN(1, true);
   } else {
@@ -585,7 +641,7 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
 #undef DBAF_LIN
   DBAF_LAUNCH_CHECK("k_linearize2");
   if (motion_only == 0 && P > 0) {
-    if (int rc = launch_schur(ws, jj, E, t0, P, HW, k_lo, k_hi, k_cap, st)) return rc;
+    if (int rc = launch_schur(ws, jj, E, t0, P, HW, k_lo, k_hi, k_cap, st, fused)) return rc;
   }
   return DBAF_OK;
 }
@@ -858,6 +914,11 @@ extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, cons
                                                pose_work ? dx_out : nullptr, t0, P, pose_work ? P : 0, HW,
                                                k_lo, k_hi, ws);
     DBAF_LAUNCH_CHECK("k_backsub_fused");
+    if (E >= 7 * ws.Kcap && HW % 32 == 0) {
+      // frames whose pose-depth blocks were not stored (flagged on the device by k_linschur_tc)
+      k_backsub_rc<<<dim3((HW / 4 + 127) / 128, k_cap), 128, 0, st>>>(dx, disps, dz_out, t0, P, HW, wd, k_lo, k_hi, ws);
+      DBAF_LAUNCH_CHECK("k_backsub_rc");
+    }
   } else if (pose_work) {
     k_pose_retract<<<1, 128, 0, st>>>(update_poses ? poses : nullptr, dx, t0, P, dx_out);
     DBAF_LAUNCH_CHECK("k_pose_retract");

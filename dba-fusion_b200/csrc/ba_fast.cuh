@@ -29,7 +29,7 @@ constexpr size_t kSchurSmemBytes = (size_t)(kSchurCapFloats + 2 * 256) * 4 + 2 *
 
 __global__ void __launch_bounds__(kThreads)
 k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k_lo, int k_hi, int skip_lo, int skip_hi,
-             Ws ws) {
+             int skip_fused, Ws ws) {
   extern __shared__ float smf[];
   const int k = k_lo + blockIdx.y;
   const int K = ws.info[0];
@@ -38,7 +38,7 @@ k_schur_smem(const int64_t* __restrict__ jj, int t0, int P, int HW, int S, int k
   const int r_lo = ws.srow_ptr[k];
   const int m = ws.srow_ptr[k + 1] - r_lo;
   if (m == 0 || m > kSchurMaxRows) return;
-  if (m >= skip_lo && m <= skip_hi) return;      // taken by k_schur_tc
+  if (skip_fused ? ls_eligible(ws, k, skip_lo) : (m >= skip_lo && m <= skip_hi)) return;   // taken by k_schur_tc / k_linschur_tc
   const int rows6 = 6 * m;
   const int tp = min(256, (kSchurCapFloats / rows6) & ~31);
   float* Es = smf;                                // [rows6][tp]
@@ -416,6 +416,7 @@ k_backsub_fused(const int64_t* __restrict__ jj, const float* __restrict__ dx, fl
   const int k = k_lo + blockIdx.y;
   const int K = ws.info[0];
   if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  if (ws.fused[k] != 0) return;                        // no Eij in the workspace: k_backsub_rc recomputes it
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   const bool live = p < HW;
   const int f = ws.kx[k];

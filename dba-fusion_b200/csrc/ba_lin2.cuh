@@ -53,11 +53,13 @@ k_linearize2(const float* __restrict__ poses, const float* __restrict__ disps,
              const float* __restrict__ intr, const float* __restrict__ sens,
              const float* __restrict__ targets, const float* __restrict__ weights,
              const float* __restrict__ eta, int eta_rows, const int64_t* __restrict__ jj,
-             int t0, int P, int HW, int wd, float alpha, int k_lo, int k_hi, Ws ws) {
+             int t0, int P, int HW, int wd, float alpha, int k_lo, int k_hi, int skip_min_m, Ws ws) {
   const int k = k_lo + blockIdx.y;
   const int K = ws.info[0];
   if (k >= K || (k_hi >= 0 && k >= k_hi)) return;
+  if (skip_min_m > 0 && ls_eligible(ws, k, skip_min_m)) return;   // taken by k_linschur_tc
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  if (!MOTION_ONLY && blockIdx.x == 0 && tid == 0) ws.fused[k] = 0;   // this frame's Eij is (again) in the workspace
   const int ix = ws.kx[k];
   const float fx = __ldg(intr), fy = __ldg(intr + 1), cx = __ldg(intr + 2), cy = __ldg(intr + 3);
   const int n6 = 6 * P;

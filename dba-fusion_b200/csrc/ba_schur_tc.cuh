@@ -21,7 +21,6 @@
 // Frames with fewer than `min_m` or more than 21 row blocks are left to the SIMT kernels.
 #pragma once   // needs tc_ptx.cuh, included by ba.cu at file scope
 
-constexpr int kStcMaxM = 21;                 // 6 * 21 = 126 rows + w + q = 128
 constexpr int kStcOpStages = 4;             // operand stages = TMEM accumulators (4 x 128 columns): slice c uses slot c & 3
 constexpr int kStcRawStages = 4;
 constexpr int kStcTile = 128 * 128;          // bytes of one tile: 128 rows x 32 floats

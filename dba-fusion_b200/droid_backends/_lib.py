@@ -20,7 +20,7 @@ class BaLayout(ctypes.Structure):
     """Mirror of `dbaf_ba_layout` (include/dbaf_b200.h)."""
     _fields_ = [(name, c_int64) for name in (
         "total_bytes", "info", "H", "v", "dx", "Lfac", "kx", "kk_exp", "csr_ptr", "csr_idx",
-        "srow_ptr", "srow_idx", "frame2k", "cursor", "Q", "w", "Ei", "Eij", "Kcap")]
+        "srow_ptr", "srow_idx", "frame2k", "cursor", "Q", "w", "Ei", "Eij", "fused", "exf", "rc_ptrs", "Kcap")]
 
 
 # name -> (restype, argtypes); must list every symbol include/dbaf_b200.h declares
