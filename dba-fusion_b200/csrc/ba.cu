@@ -475,7 +475,7 @@ constexpr int kLsMaxDeg = 20;                // out-edges per frame (120 operand
 __device__ __forceinline__ bool ls_eligible(const Ws& ws, int k, int min_m) {
   const int m = ws.srow_ptr[k + 1] - ws.srow_ptr[k];
   const int deg = ws.csr_ptr[k + 1] - ws.csr_ptr[k];
-  return m >= min_m && m <= kStcMaxM && deg >= 1 && deg <= kLsMaxDeg;
+  return m >= min_m && m <= kStcMaxM && deg >= 4 && deg <= kLsMaxDeg;
 }
 
 #include "ba_fast.cuh"

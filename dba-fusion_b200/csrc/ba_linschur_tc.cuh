@@ -42,9 +42,9 @@ struct LsEdge {          // 24 words, 16-byte aligned: what the per-pixel code n
 static_assert(sizeof(LsEdge) == 96, "LsEdge is read with 16-byte loads");
 
 constexpr size_t kLsPartBytes = (size_t)kLsProducers * kLsMaxDeg * 32 * 4;
-constexpr size_t kLsSmemBytes = (size_t)kLsProducers * kStcStageBytes + 1024 /*align*/ + kLsMaxDeg * sizeof(LsEdge) +
-                                kLsPartBytes + 256 /*barriers, tmem slot*/;
-static_assert(kLsSmemBytes <= 227 * 1024, "k_linschur_tc shared memory");
+constexpr size_t kLsSmemBytes = (size_t)kLsProducers * kStcStageBytes + 1024 /*align*/;      // dynamic part
+static_assert(kLsSmemBytes + kLsMaxDeg * sizeof(LsEdge) + kLsPartBytes + kLsMaxDeg * 8 + 256 <= 227 * 1024,
+              "k_linschur_tc shared memory (dynamic + static)");
 // epilogue scratch aliases the operand stages
 static_assert((size_t)128 * kLsSld * 4 + (size_t)kLsMaxDeg * (28 + 36) * 4 + (size_t)(kLsMaxDeg + 1) * 36 * 4 <=
               (size_t)kLsProducers * kStcStageBytes, "epilogue scratch");
@@ -214,10 +214,12 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
 
   extern __shared__ uint8_t ls_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(ls_raw) + 1023) & ~(uintptr_t)1023);
-  LsEdge* sx = reinterpret_cast<LsEdge*>(smem + kLsProducers * kStcStageBytes);
-  float* part = reinterpret_cast<float*>(sx + kLsMaxDeg);                   // [producer][edge][32]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(part + kLsProducers * kLsMaxDeg * 32);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 24);
+  // static shared arrays: the compiler sees the address space and emits LDS / STS (through a pointer derived from the
+  // re-aligned dynamic buffer it emits generic loads, which share a scoreboard with the global prefetches)
+  __shared__ __align__(16) LsEdge sx[kLsMaxDeg];
+  __shared__ __align__(16) float part[kLsProducers * kLsMaxDeg * 32];       // [producer][edge][32]
+  __shared__ uint64_t bars[24];
+  __shared__ uint32_t tmem_slot[1];
   __shared__ size_t eoff[kLsMaxDeg];                          // element offset of the edge's [2][HW] block
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -263,16 +265,20 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
     // ================================================================ producers
     const int p = warp - kLsFirstProducer;
     const int g = lane >> 3, l8 = lane & 7;
-    uint8_t* stage = smem + p * kStcStageBytes;
-    float* mypart = part + p * (kLsMaxDeg * 32);
+    const uint32_t stage = smem_u32(smem) + (uint32_t)p * kStcStageBytes;   // shared-window address of the hi tile
+    float* mypart = &part[p * (kLsMaxDeg * 32)];
     const int n_it = (deg + 3) >> 2;
     // byte offset of this thread's 16-byte chunk inside operand row r: r * 128 + ((l8 ^ (r & 7)) << 4)
     auto row_off = [&](int r) -> uint32_t { return (uint32_t)r * 128u + (((uint32_t)l8 ^ ((uint32_t)r & 7u)) << 4); };
-    auto store_split = [&](int r, const float* v) {            // v[4] -> TF32 hi / lo tiles
-      const uint32_t off = row_off(r);
-      const float4 hi = make_float4(tf32_rna(v[0]), tf32_rna(v[1]), tf32_rna(v[2]), tf32_rna(v[3]));
-      *reinterpret_cast<float4*>(stage + off) = hi;
-      *reinterpret_cast<float4*>(stage + kStcTile + off) = make_float4(v[0] - hi.x, v[1] - hi.y, v[2] - hi.z, v[3] - hi.w);
+    // x -> (hi, lo): hi = x rounded to TF32 (round to nearest, ties away from zero, as cvt.rna.tf32.f32 does; done on
+    // the bit pattern: two integer instructions instead of the conversion's five), lo = x - hi exactly
+    auto store_split_at = [&](uint32_t dst, const float* v) {
+      float hi[4];
+#pragma unroll
+      for (int s = 0; s < 4; ++s) hi[s] = __uint_as_float((__float_as_uint(v[s]) + 0x1000u) & 0xffffe000u);
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst), "f"(hi[0]), "f"(hi[1]), "f"(hi[2]), "f"(hi[3]) : "memory");
+      asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (uint32_t)kStcTile), "f"(v[0] - hi[0]), "f"(v[1] - hi[1]),
+                   "f"(v[2] - hi[2]), "f"(v[3] - hi[3]) : "memory");
     };
     // Loads are software-pipelined across every boundary: the next edge of the group is requested while the current
     // one is worked on, the pixel rows and first edge of the warp's next slice before this slice's tail.  eoff[a] =
@@ -281,11 +287,10 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
     const float* tbase = targets + s_lo + 4 * l8;
     auto ld4 = [](const float* q) { return __ldg(reinterpret_cast<const float4*>(q)); };
     auto edge_off = [&](int a) -> size_t { return eoff[min(a, deg - 1)]; };
-    float4 d4, s4, q4, wu_n, wv_n, tu_n, tv_n;
+    float4 d4, q4, wu_n, wv_n, tu_n, tv_n;
     auto slice_loads = [&](int c) {
       const int px0 = s_lo + 32 * c + 4 * l8;
       d4 = ld4(disps + (size_t)ix * HW + px0);
-      s4 = ld4(sens + (size_t)ix * HW + px0);
       q4 = *reinterpret_cast<const float4*>(ws.Q + (size_t)k * HW + px0);     // written by k_depth_diag
       const size_t o = edge_off(g) + 32 * c;
       wu_n = ld4(wbase + o);
@@ -307,12 +312,11 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
         X1[s] = ((float)i - cy) * inv_fy;
       }
       const float d0[4] = {d4.x, d4.y, d4.z, d4.w};
-      const float sd[4] = {s4.x, s4.y, s4.z, s4.w};
       const float sq[4] = {sqrtf(q4.x), sqrtf(q4.y), sqrtf(q4.z), sqrtf(q4.w)};
 
-      // the MMAs that read this stage one round ago have retired
+#ifdef LS_WAIT_EARLY
       mbar_wait(smem_u32(&bars[kLsBarOpEmpty + p]), (use + 1) & 1);
-
+#endif
       float W[4] = {0.f, 0.f, 0.f, 0.f};
       const int c_next = c + kLsProducers;
       for (int it = 0; it < n_it; ++it) {
@@ -369,8 +373,13 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
             for (int n = 0; n < 6; ++n)
               Es[n][s] = n == 0 ? zu * wJu[0] : n == 1 ? zv * wJv[1] : fmaf(zu, wJu[n], zv * wJv[n]);
           }
+          // the MMAs that read this stage one round ago have retired (asked only now: the first edge's arithmetic
+          // overlaps the wait; every group has an edge in round 0, frames here have at least seven)
+#ifndef LS_WAIT_EARLY
+          if (it == 0) mbar_wait(smem_u32(&bars[kLsBarOpEmpty + p]), (use + 1) & 1);
+#endif
 #pragma unroll
-          for (int n = 0; n < 6; ++n) store_split(6 * a + n, Es[n]);
+          for (int n = 0; n < 6; ++n) store_split_at(stage + row_off(6 * a + n), Es[n]);
         }
         // sums over the eight lanes of the group: lane l8 ends up with terms 4 l8 .. 4 l8 + 3
 #pragma unroll
@@ -391,6 +400,8 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
         }
       }
       // w of the frame: sum over the groups, sensor-depth prior, then its operand row and the global copy
+      const float4 s4 = ld4(sens + (size_t)ix * HW + px0);
+      const float sd[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
       for (int s = 0; s < 4; ++s) {
         W[s] += __shfl_xor_sync(0xffffffffu, W[s], 8);
@@ -399,7 +410,7 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
       }
       if (g == 0) {
         const float wsq[4] = {W[0] * sq[0], W[1] * sq[1], W[2] * sq[2], W[3] * sq[3]};
-        store_split(kLsWRow, wsq);
+        store_split_at(stage + row_off(kLsWRow), wsq);
         *reinterpret_cast<float4*>(ws.w + (size_t)k * HW + px0) = make_float4(W[0], W[1], W[2], W[3]);
       }
       fence_async_smem();                                      // generic-proxy stores -> visible to the MMA unit
