@@ -561,14 +561,16 @@ int launch_schur(Ws ws, const int64_t* jj, int E, int t0, int P, int HW, int k_l
     k_schur_tc<<<dim3(splits, k_cap), kStcThreads, kStcSmemBytes, st>>>(jj, t0, P, HW, St, tc_min_m, k_lo, k_hi, ws);
     DBAF_LAUNCH_CHECK("k_schur_tc");
   }
-  const int S = 256;
+  // (fused: only the few frames k_linschur_tc left -- short out-edge lists at the ends of the chain -- remain; one CTA
+  // walks all pixel tiles of such a frame, so that the ~1000 frames that return at once cost 1000 CTAs, not 16 000)
+  const int S = fused ? HW : 256;
   dim3 sgrid((HW + S - 1) / S, k_cap);
   k_schur_smem<<<sgrid, kThreads, kSchurSmemBytes, st>>>(jj, t0, P, HW, S, k_lo, k_hi, use_tc ? tc_min_m : 1,
                                                          use_tc ? kStcMaxM : 0, fused ? 1 : 0, ws);
   DBAF_LAUNCH_CHECK("k_schur_smem");
   if (E + 1 > kSchurMaxRows) {
     // a depth frame can only have more than kSchurMaxRows rows if the graph has that many edges
-    const int tile_px = 1024;
+    const int tile_px = fused ? HW : 1024;
     dim3 ogrid((HW + tile_px - 1) / tile_px, k_cap);
     k_schur<<<ogrid, kThreads, 0, st>>>(jj, t0, P, HW, tile_px, kSchurMaxRows + 1, k_lo, k_hi, ws);
     DBAF_LAUNCH_CHECK("k_schur");

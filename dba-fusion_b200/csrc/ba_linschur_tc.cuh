@@ -287,10 +287,11 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
     const float* tbase = targets + s_lo + 4 * l8;
     auto ld4 = [](const float* q) { return __ldg(reinterpret_cast<const float4*>(q)); };
     auto edge_off = [&](int a) -> size_t { return eoff[min(a, deg - 1)]; };
-    float4 d4, q4, wu_n, wv_n, tu_n, tv_n;
+    float4 d4, s4, q4, wu_n, wv_n, tu_n, tv_n;
     auto slice_loads = [&](int c) {
       const int px0 = s_lo + 32 * c + 4 * l8;
       d4 = ld4(disps + (size_t)ix * HW + px0);
+      s4 = ld4(sens + (size_t)ix * HW + px0);
       q4 = *reinterpret_cast<const float4*>(ws.Q + (size_t)k * HW + px0);     // written by k_depth_diag
       const size_t o = edge_off(g) + 32 * c;
       wu_n = ld4(wbase + o);
@@ -312,6 +313,7 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
         X1[s] = ((float)i - cy) * inv_fy;
       }
       const float d0[4] = {d4.x, d4.y, d4.z, d4.w};
+      const float sd[4] = {s4.x, s4.y, s4.z, s4.w};
       const float sq[4] = {sqrtf(q4.x), sqrtf(q4.y), sqrtf(q4.z), sqrtf(q4.w)};
 
 #ifdef LS_WAIT_EARLY
@@ -400,8 +402,6 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
         }
       }
       // w of the frame: sum over the groups, sensor-depth prior, then its operand row and the global copy
-      const float4 s4 = ld4(sens + (size_t)ix * HW + px0);
-      const float sd[4] = {s4.x, s4.y, s4.z, s4.w};
 #pragma unroll
       for (int s = 0; s < 4; ++s) {
         W[s] += __shfl_xor_sync(0xffffffffu, W[s], 8);

@@ -225,6 +225,7 @@ k_depth_filter(const float* __restrict__ poses, const float* __restrict__ disps,
 using namespace dbaf;
 
 extern "C" int dbaf_version(void) { return 100; }
+extern "C" int dbaf_ba_layout_bytes(void) { return (int)sizeof(dbaf_ba_layout); }
 
 extern "C" const char* dbaf_last_error(void) { return g_error.c_str(); }
 

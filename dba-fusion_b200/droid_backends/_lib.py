@@ -27,6 +27,7 @@ class BaLayout(ctypes.Structure):
 P = c_void_p
 SIGNATURES = {
     "dbaf_version": (c_int, []),
+    "dbaf_ba_layout_bytes": (c_int, []),
     "dbaf_last_error": (ctypes.c_char_p, []),
     "dbaf_set_option": (c_int, [ctypes.c_char_p, ctypes.c_char_p]),
     "dbaf_probe_fill": (c_int, [P, c_size_t, c_int, P]),
@@ -85,6 +86,9 @@ def load():
         fn = getattr(lib, name)        # AttributeError if the library lacks a declared symbol
         fn.restype = res
         fn.argtypes = args
+    if lib.dbaf_ba_layout_bytes() != ctypes.sizeof(BaLayout):
+        raise ImportError(f"droid_backends (B200): {LIB_PATH} was built from a different include/dbaf_b200.h "
+                          f"(dbaf_ba_layout is {lib.dbaf_ba_layout_bytes()} bytes there, {ctypes.sizeof(BaLayout)} here)")
     return lib
 
 

@@ -20,7 +20,8 @@ def build(force: bool = False) -> str:
     so = os.path.join(HERE, NAME + ".so")
     src = os.path.join(HERE, NAME + ".cpp")
     lib = os.path.join(ROOT, "dba-fusion_b200", "csrc", "libdbaf_b200.so")
-    if os.path.exists(so) and not force and os.path.getmtime(so) >= max(os.path.getmtime(src), os.path.getmtime(lib)):
+    hdr = os.path.join(ROOT, "include", "dbaf_b200.h")
+    if os.path.exists(so) and not force and os.path.getmtime(so) >= max(os.path.getmtime(src), os.path.getmtime(lib), os.path.getmtime(hdr)):
         return so
     import torch
     T = os.path.dirname(torch.__file__)

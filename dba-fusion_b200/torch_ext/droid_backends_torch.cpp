@@ -274,6 +274,9 @@ class BACore {
 using dbaf_torch::BACore;
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  TORCH_CHECK(dbaf_ba_layout_bytes() == (int)sizeof(dbaf_ba_layout),
+              "droid_backends_torch was compiled against another include/dbaf_b200.h than libdbaf_b200.so: rebuild it "
+              "(python dba-fusion_b200/torch_ext/build.py --force)");
   m.def("ba", &ba, "bundle adjustment");
   m.def("ba_extend", &ba_extend, "bundle adjustment (extended)");
   m.def("frame_distance", &frame_distance, "frame_distance");

@@ -34,6 +34,9 @@ extern "C" {
 #define DBAF_F32 1
 
 int dbaf_version(void);
+/* sizeof(dbaf_ba_layout) as the library was built: a binding compiled against an older header must refuse to load
+ * (the library writes the whole struct).  No counterpart in the reference. */
+int dbaf_ba_layout_bytes(void);
 const char* dbaf_last_error(void);
 
 /* Kernel-selection switches for tests and profiling (no counterpart in the reference).  Process-wide; the
