@@ -47,7 +47,7 @@ struct Ws {
   float* Eij;
   double* Lfac;
   int* fused;     // [Kcap] 1: the frame went through k_linschur_tc (no Eij; the back-substitution recomputes it)
-  float* exf;     // [E][24] relative-pose record of every edge of such a frame (LsEdge), read by k_backsub_rc
+  float* exf;     // [E][28] relative-pose record of every edge of such a frame (LsEdge), read by k_backsub_rc
   const float** rc_ptrs;  // [2] weights and intrinsics pointers of the last fused linearisation
   int Kcap;
 };
@@ -75,7 +75,7 @@ void fill_layout(int N, int E, int t0, int t1, int ht, int wd, dbaf_ba_layout* L
   L->Ei = take(P * 6 * HW * 4);
   L->Eij = take((int64_t)E * 6 * HW * 4);
   L->fused = take(Kcap * 4);
-  L->exf = take(std::max<int64_t>(1, E) * 24 * 4);
+  L->exf = take(std::max<int64_t>(1, E) * 28 * 4);
   L->rc_ptrs = take(2 * 8);
   L->Kcap = Kcap;
   L->total_bytes = off;
@@ -607,6 +607,7 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
   // ranges (dbaf_b200.global_ba) takes the same path in each.
   const auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   const bool fused = motion_only == 0 && P > 0 && dense_graph(E, ws.Kcap, HW) && options().eij_recompute != 0 &&
+                     ht <= kLsTabMax && wd <= kLsTabMax &&
                      al16(disps) && al16(disps_sens) && al16(targets) && al16(weights) && al16(eta);
   if (fused) {
     static bool ls_attr[64] = {};

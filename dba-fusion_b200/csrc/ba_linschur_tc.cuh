@@ -28,18 +28,21 @@ constexpr int kLsProducers = 6;                       // producer warps = operan
 constexpr int kLsDrainWarps = 4;
 constexpr int kLsFirstProducer = 6;                   // warps 0-3 drain, 4 MMA, 5 spare, 6.. producers
 constexpr int kLsThreads = (kLsFirstProducer + kLsProducers) * 32;
+constexpr int kLsTabMax = 512;                        // frames up to 512 x 512 (at 1/8 resolution) use the coordinate tables
 constexpr int kLsWRow = 126;                          // operand row that carries w sqrt(q)
 constexpr int kLsSld = 129;                           // leading dimension of S in shared memory (epilogue)
 
-struct LsEdge {          // 24 words, 16-byte aligned: what the per-pixel code needs of an edge
-  float Rt[9];           // R(q_ij)^T, row-major: R[r][c] = Rt[3 c + r]
+struct LsEdge {          // 28 words, 16-byte aligned: what the kernels need of an edge
+  float q[4];            // rotation of G_ij (x y z w)
   float t[3];            // translation of G_ij
+  int flags;             // bit 0: stereo edge (depth blocks only)
+  float Rt[9];           // R(q_ij)^T, row-major
   float Nm[9];           // -R^T [t]x: M = [[Rt, 0], [Nm, Rt]] carries a pose-j Jacobian to pose i (negated)
   int jx;                // target frame
-  int flags;             // bit 0: stereo edge (depth blocks only)
   int prow;              // pose index of the target (jx - t0) if inside the window, else -1
 };
-static_assert(sizeof(LsEdge) == 96, "LsEdge is read with 16-byte loads");
+constexpr int kLsEdgeWords = 28;
+static_assert(sizeof(LsEdge) == kLsEdgeWords * 4, "LsEdge is copied with 16-byte loads");
 
 constexpr size_t kLsPartBytes = (size_t)kLsProducers * kLsMaxDeg * 32 * 4;
 constexpr size_t kLsSmemBytes = (size_t)kLsProducers * kStcStageBytes + 1024 /*align*/;      // dynamic part
@@ -87,11 +90,39 @@ struct LsPix {
   float Jzu, Jzv;
   bool near;
 };
-__device__ __forceinline__ LsPix ls_project(const float* Rt, const float* t, float X0, float X1, float d0, float fx, float fy) {
+// Transformed points of a thread's four pixels.  Fast path: three FMAs per coordinate with the rotation matrix.  The
+// near-plane test z < 0.25 must fall the same way as in the reference for every pixel (a pixel on the other side of
+// the threshold changes its whole contribution), so whenever one of the four depths comes within 1e-3 of the
+// threshold the four points are redone with the reference's own formula (actSE3, src/droid_kernels.cu:73-80, through
+// `act`), whose z is bit-identical to the reference's.  Rt: R^T row-major, i.e. R[r][c] = Rt[3 c + r].
+__device__ __forceinline__ void ls_points4(const float* Rt, const float* q, const float* t, const float* X0, const float* X1,
+                                           const float* d0, float (*Y)[3]) {
+  bool close = false;
+#pragma unroll
+  for (int s = 0; s < 4; ++s) {
+    Y[s][0] = fmaf(Rt[0], X0[s], fmaf(Rt[3], X1[s], fmaf(t[0], d0[s], Rt[6])));
+    Y[s][1] = fmaf(Rt[1], X0[s], fmaf(Rt[4], X1[s], fmaf(t[1], d0[s], Rt[7])));
+    Y[s][2] = fmaf(Rt[2], X0[s], fmaf(Rt[5], X1[s], fmaf(t[2], d0[s], Rt[8])));
+    close = close || fabsf(Y[s][2] - kMinDepth) < 1e-3f;
+  }
+  if (close) {
+    Se3 G;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) G.t[c] = t[c];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) G.q[c] = q[c];
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+      const float Xi[4] = {X0[s], X1[s], 1.0f, d0[s]};
+      float Xj[4];
+      act(G, Xi, Xj);
+      Y[s][0] = Xj[0]; Y[s][1] = Xj[1]; Y[s][2] = Xj[2];
+    }
+  }
+}
+__device__ __forceinline__ LsPix ls_project(const float* Yp, const float* t, float fx, float fy) {
   LsPix o;
-  const float Y0 = fmaf(Rt[0], X0, fmaf(Rt[3], X1, fmaf(t[0], d0, Rt[6])));
-  const float Y1 = fmaf(Rt[1], X0, fmaf(Rt[4], X1, fmaf(t[1], d0, Rt[7])));
-  const float Y2 = fmaf(Rt[2], X0, fmaf(Rt[5], X1, fmaf(t[2], d0, Rt[8])));
+  const float Y0 = Yp[0], Y1 = Yp[1], Y2 = Yp[2];
   o.near = Y2 < kMinDepth;
   o.d = o.near ? 0.0f : __fdividef(1.0f, Y2);
   o.xd = Y0 * o.d;
@@ -132,16 +163,18 @@ k_depth_diag(const float* __restrict__ poses, const float* __restrict__ disps, c
     for (int q = 0; q < 9; ++q) { L.Rt[q] = X.Rt[q]; L.Nm[q] = X.Nm[q]; }
 #pragma unroll
     for (int q = 0; q < 3; ++q) L.t[q] = X.t[q];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) L.q[q] = X.q[q];
     L.jx = jx;
     L.flags = X.stereo;
     L.prow = (jx >= t0 && jx < t0 + P) ? jx - t0 : -1;
     sx[tid] = L;
     eoff[tid] = (size_t)e * 2 * HW;
     if (blockIdx.x == 0) {                 // k_linschur_tc reads the records; so does k_backsub_rc, after the poses have moved
-      float4* dst = reinterpret_cast<float4*>(ws.exf + (size_t)e * 24);
+      float4* dst = reinterpret_cast<float4*>(ws.exf + (size_t)e * kLsEdgeWords);
       const float4* src = reinterpret_cast<const float4*>(&L);
 #pragma unroll
-      for (int q = 0; q < 6; ++q) dst[q] = src[q];
+      for (int q = 0; q < kLsEdgeWords / 4; ++q) dst[q] = src[q];
     }
   }
   if (blockIdx.x == 0 && tid == 0) {
@@ -153,14 +186,13 @@ k_depth_diag(const float* __restrict__ poses, const float* __restrict__ disps, c
   __syncthreads();
   const int px0 = (blockIdx.x * 128 + tid) * 4;
   if (px0 >= HW) return;
-  const float inv_fx = 1.0f / fx, inv_fy = 1.0f / fy;
   float X0[4], X1[4];
 #pragma unroll
   for (int s = 0; s < 4; ++s) {
     const int pp = px0 + s;
     const int i = pp / wd, j = pp - i * wd;
-    X0[s] = ((float)j - cx) * inv_fx;
-    X1[s] = ((float)i - cy) * inv_fy;
+    X0[s] = ((float)j - cx) / fx;
+    X1[s] = ((float)i - cy) / fy;
   }
   const int er = eta_rows == 1 ? 0 : min(k, eta_rows - 1);
   const float4 d4 = __ldg(reinterpret_cast<const float4*>(disps + (size_t)ix * HW + px0));
@@ -181,9 +213,11 @@ k_depth_diag(const float* __restrict__ poses, const float* __restrict__ disps, c
     if (a + 2 < deg) { wu_b = __ldg(wptr(a + 2, 0)); wv_b = __ldg(wptr(a + 2, 1)); }
     const LsEdge& X = sx[a];
     const float wu[4] = {wu4.x, wu4.y, wu4.z, wu4.w}, wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+    float Y[4][3];
+    ls_points4(X.Rt, X.q, X.t, X0, X1, d0, Y);
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
-      const LsPix o = ls_project(X.Rt, X.t, X0[s], X1[s], d0[s], fx, fy);
+      const LsPix o = ls_project(Y[s], X.t, fx, fy);
       const float a_u = o.near ? 0.f : 0.001f * wu[s], a_v = o.near ? 0.f : 0.001f * wv[s];
       C[s] = fmaf(a_u * o.Jzu, o.Jzu, fmaf(a_v * o.Jzv, o.Jzv, C[s]));
     }
@@ -220,20 +254,22 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
   __shared__ __align__(16) float part[kLsProducers * kLsMaxDeg * 32];       // [producer][edge][32]
   __shared__ uint64_t bars[24];
   __shared__ uint32_t tmem_slot[1];
+  __shared__ float xtab[kLsTabMax], ytab[kLsTabMax];         // (j - cx) / fx and (i - cy) / fy, divided once per CTA like the reference does per pixel
   __shared__ size_t eoff[kLsMaxDeg];                          // element offset of the edge's [2][HW] block
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n_chunks = (s_hi - s_lo) / 32;
   const float fx = __ldg(intr), fy = __ldg(intr + 1), cx = __ldg(intr + 2), cy = __ldg(intr + 3);
-  const float inv_fx = 1.0f / fx, inv_fy = 1.0f / fy;
 
   // ---------------------------------------------------------------- prologue
+  for (int q = tid; q < wd; q += kLsThreads) xtab[q] = ((float)q - cx) / fx;
+  for (int q = tid; q < HW / wd; q += kLsThreads) ytab[q] = ((float)q - cy) / fy;
   if (tid < deg) {
     const int e = ws.csr_idx[e_lo + tid];
-    const float4* src = reinterpret_cast<const float4*>(ws.exf + (size_t)e * 24);   // written by k_depth_diag
+    const float4* src = reinterpret_cast<const float4*>(ws.exf + (size_t)e * kLsEdgeWords);   // written by k_depth_diag
     float4* dst = reinterpret_cast<float4*>(&sx[tid]);
 #pragma unroll
-    for (int q = 0; q < 6; ++q) dst[q] = src[q];
+    for (int q = 0; q < kLsEdgeWords / 4; ++q) dst[q] = src[q];
     eoff[tid] = (size_t)e * 2 * HW;
   }
   // operand rows that no producer writes (beyond 6 deg, except the w row) must read as zero
@@ -309,8 +345,8 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
       for (int s = 0; s < 4; ++s) {
         const int pp = px0 + s;
         const int i = pp / wd, j = pp - i * wd;
-        X0[s] = ((float)j - cx) * inv_fx;
-        X1[s] = ((float)i - cy) * inv_fy;
+        X0[s] = xtab[j];
+        X1[s] = ytab[i];
       }
       const float d0[4] = {d4.x, d4.y, d4.z, d4.w};
       const float sd[4] = {s4.x, s4.y, s4.z, s4.w};
@@ -340,9 +376,11 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
           const float wu[4] = {wu4.x, wu4.y, wu4.z, wu4.w}, wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
           const float tu[4] = {tu4.x, tu4.y, tu4.z, tu4.w}, tv[4] = {tv4.x, tv4.y, tv4.z, tv4.w};
           float Es[6][4];
+          float Y[4][3];
+          ls_points4(X.Rt, X.q, X.t, X0, X1, d0, Y);
 #pragma unroll
           for (int s = 0; s < 4; ++s) {
-            const LsPix o = ls_project(X.Rt, X.t, X0[s], X1[s], d0[s], fx, fy);
+            const LsPix o = ls_project(Y[s], X.t, fx, fy);
             float a_u = o.near ? 0.f : 0.001f * wu[s], a_v = o.near ? 0.f : 0.001f * wv[s];
             const float bu = fx * o.xd, bv = fy * o.yd;
             const float ru = tu[s] - (bu + cx), rv = tv[s] - (bv + cy);
@@ -598,7 +636,7 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
 // Ei = -sum_e M_e Ej_e folded in).  Rows whose pose index is 0 or outside the window are skipped like in the
 // reference (src/droid_kernels.cu:1150).  The pose update of the iteration stays in k_backsub_fused, which
 // skips these frames.  grid (HW / 512, K), 128 threads, four pixels per thread.
-struct RcEdge { float Rt[9]; float t[3]; float g[6]; int eid; int live; };
+struct RcEdge { float q[4]; float t[3]; int live; float Rt[9]; float g[6]; int eid; };
 __global__ void __launch_bounds__(128)
 k_backsub_rc(const float* __restrict__ dx, float* __restrict__ disps, float* __restrict__ dz_out, int t0, int P, int HW,
              int wd, int k_lo, int k_hi, Ws ws) {
@@ -616,12 +654,14 @@ k_backsub_rc(const float* __restrict__ dx, float* __restrict__ disps, float* __r
   const float fx = __ldg(intr), fy = __ldg(intr + 1), cx = __ldg(intr + 2), cy = __ldg(intr + 3);
   if (tid < deg) {
     const int e = ws.csr_idx[e_lo + tid];
-    const LsEdge* L = reinterpret_cast<const LsEdge*>(ws.exf + (size_t)e * 24);
+    const LsEdge* L = reinterpret_cast<const LsEdge*>(ws.exf + (size_t)e * kLsEdgeWords);
     RcEdge R;
 #pragma unroll
-    for (int q = 0; q < 9; ++q) R.Rt[q] = L->Rt[q];
+    for (int q = 0; q < 4; ++q) R.q[q] = L->q[q];
 #pragma unroll
     for (int q = 0; q < 3; ++q) R.t[q] = L->t[q];
+#pragma unroll
+    for (int q = 0; q < 9; ++q) R.Rt[q] = L->Rt[q];
     const int pj = L->prow;
     float xi[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, g[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     if (pj > 0 && pj < P) {
@@ -669,9 +709,11 @@ k_backsub_rc(const float* __restrict__ dx, float* __restrict__ disps, float* __r
     const RcEdge& X = se[a];
     if (!X.live) continue;
     const float wu[4] = {wu4.x, wu4.y, wu4.z, wu4.w}, wv[4] = {wv4.x, wv4.y, wv4.z, wv4.w};
+    float Y[4][3];
+    ls_points4(X.Rt, X.q, X.t, X0, X1, d0, Y);
 #pragma unroll
     for (int s = 0; s < 4; ++s) {
-      const LsPix o = ls_project(X.Rt, X.t, X0[s], X1[s], d0[s], fx, fy);
+      const LsPix o = ls_project(Y[s], X.t, fx, fy);
       const float a_u = o.near ? 0.f : 0.001f * wu[s], a_v = o.near ? 0.f : 0.001f * wv[s];
       const float bu = fx * o.xd, bv = fy * o.yd;
       const float Ju0 = o.gu * d0[s], Jv1 = o.gv * d0[s];

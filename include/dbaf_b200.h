@@ -221,7 +221,7 @@ typedef struct dbaf_ba_layout {
   int64_t Ei;        /* float32[P,6,HW] */
   int64_t Eij;       /* float32[E,6,HW] */
   int64_t fused;     /* int32[Kcap]   1 = the frame's pose-depth blocks are recomputed, not stored (see "eij" option) */
-  int64_t exf;       /* float32[E,24] per-edge relative-pose record of such frames */
+  int64_t exf;       /* float32[E,28] per-edge relative-pose record of such frames */
   int64_t rc_ptrs;   /* 2 device pointers: the weights and intrinsics of the last such linearisation */
   int64_t Kcap;      /* capacity of the depth-frame tables = min(N, P+E) */
 } dbaf_ba_layout;
