@@ -52,6 +52,15 @@ static_assert(kLsSmemBytes + kLsMaxDeg * sizeof(LsEdge) + kLsPartBytes + kLsMaxD
 static_assert((size_t)128 * kLsSld * 4 + (size_t)kLsMaxDeg * (28 + 36) * 4 + (size_t)(kLsMaxDeg + 1) * 36 * 4 <=
               (size_t)kLsProducers * kStcStageBytes, "epilogue scratch");
 
+// Slices are dealt to the producers in a fixed round of 14: producers 2 and 3 (warps 8, 9) sit on schedulers that
+// hold no second producer and run ~1.4x faster than the other four, so they take three slices per round, the others
+// two.  Fixed, so that the sums do not depend on timing.
+constexpr int kLsRound = 14;
+__constant__ int c_ls_order[kLsRound] = {2, 3, 0, 1, 2, 3, 4, 5, 2, 3, 0, 1, 4, 5};      // slice position -> producer
+__constant__ int c_ls_rank[kLsRound] = {0, 0, 0, 0, 1, 1, 0, 0, 2, 2, 1, 1, 1, 1};       // how many earlier positions of the round it had
+__constant__ int c_ls_count[kLsProducers] = {2, 2, 3, 3, 2, 2};                          // slices per round
+__constant__ int c_ls_pos[kLsProducers][3] = {{2, 10, 0}, {3, 11, 0}, {0, 4, 8}, {1, 5, 9}, {6, 12, 0}, {7, 13, 0}};
+
 constexpr int kLsBarOpFull = 0, kLsBarOpEmpty = 6, kLsBarAccFull = 12, kLsBarAccRead = 16;
 
 // waiting roles (MMA issuer, drain warps) back off between polls: a spinning warp takes issue slots from the producers
@@ -335,9 +344,15 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
       tu_n = ld4(tbase + o);
       tv_n = ld4(tbase + o + HW);
     };
-    if (p < n_chunks) slice_loads(p);
+    const int my_count = c_ls_count[p];
+    const int my_pos[3] = {c_ls_pos[p][0], c_ls_pos[p][1], c_ls_pos[p][2]};
+    auto my_slice = [&](int use) -> int {                       // this producer's use-th slice
+      const int r = use / my_count, k = use - r * my_count;
+      return kLsRound * r + (k == 0 ? my_pos[0] : k == 1 ? my_pos[1] : my_pos[2]);
+    };
+    if (my_slice(0) < n_chunks) slice_loads(my_slice(0));
     int use = 0;
-    for (int c = p; c < n_chunks; c += kLsProducers, ++use) {
+    for (int c = my_slice(0); c < n_chunks; c = my_slice(++use)) {
       const int px0 = s_lo + 32 * c + 4 * l8;
       const int pc = 32 * c;
       float X0[4], X1[4];
@@ -356,7 +371,7 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
       mbar_wait(smem_u32(&bars[kLsBarOpEmpty + p]), (use + 1) & 1);
 #endif
       float W[4] = {0.f, 0.f, 0.f, 0.f};
-      const int c_next = c + kLsProducers;
+      const int c_next = my_slice(use + 1);
       for (int it = 0; it < n_it; ++it) {
         const int a = 4 * it + g;
         const float4 wu4 = wu_n, wv4 = wv_n, tu4 = tu_n, tv4 = tv_n;
@@ -460,9 +475,11 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
       // ============================================================== MMA issuer
       const uint64_t desc0 = umma_desc_k128(smem_u32(smem));
       for (int c = 0; c < n_chunks; ++c) {
-        const int st = c % kLsProducers, acc_i = c & 3;
+        const int rr = c / kLsRound, pos = c - rr * kLsRound;
+        const int st = c_ls_order[pos], acc_i = c & 3;
+        const int fill = rr * c_ls_count[st] + c_ls_rank[pos];        // how often stage st has been filled before
         if (c >= 4) mbar_wait_sleep(smem_u32(&bars[kLsBarAccRead + acc_i]), ((c - 4) >> 2) & 1, 200);
-        mbar_wait_sleep(smem_u32(&bars[kLsBarOpFull + st]), (c / kLsProducers) & 1, 200);
+        mbar_wait_sleep(smem_u32(&bars[kLsBarOpFull + st]), fill & 1, 200);
         tc_fence_after();
         const uint64_t dhi = desc0 + (uint64_t)((st * kStcStageBytes) >> 4);
         const uint64_t dlo = dhi + (uint64_t)(kStcTile >> 4);
