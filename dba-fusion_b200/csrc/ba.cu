@@ -868,6 +868,87 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
 }
 }  // namespace
 
+namespace dbaf {
+namespace {
+// one CTA per scalar row: the entries of H within `B` pose blocks of the diagonal, and v (row n)
+__global__ void __launch_bounds__(128) k_zero_band(double* __restrict__ H, double* __restrict__ v, int n, int B) {
+  const int r = blockIdx.x;
+  if (r == n) {
+    for (int c = threadIdx.x; c < n; c += 128) v[c] = 0.0;
+    return;
+  }
+  const int blk = r / 6;
+  const int c_lo = max(0, (blk - B) * 6), c_hi = min(n, (blk + B + 1) * 6);
+  double* row = H + (size_t)r * n;
+  for (int c = c_lo + threadIdx.x; c < c_hi; c += 128) row[c] = 0.0;
+}
+}  // namespace
+}  // namespace dbaf
+
+namespace dbaf {
+namespace {
+// H rows <-> a dense [n][6 (2B + 1)] strip (row r keeps the columns of pose blocks r/6 - B .. r/6 + B), v behind it
+template <bool PACK>
+__global__ void __launch_bounds__(256) k_band_strip(double* __restrict__ H, double* __restrict__ v, int n, int B,
+                                                    double* __restrict__ strip) {
+  const int r = blockIdx.x;
+  const int W = 6 * (2 * B + 1);
+  if (r == n) {
+    for (int c = threadIdx.x; c < n; c += 256) {
+      if (PACK) strip[(size_t)n * W + c] = v[c]; else v[c] = strip[(size_t)n * W + c];
+    }
+    return;
+  }
+  const int c0 = (r / 6 - B) * 6;
+  double* row = H + (size_t)r * n;
+  double* srow = strip + (size_t)r * W;
+  for (int j = threadIdx.x; j < W; j += 256) {
+    const int c = c0 + j;
+    const bool in = c >= 0 && c < n;
+    if (PACK) srow[j] = in ? row[c] : 0.0;
+    else if (in) row[c] = srow[j];
+  }
+}
+}  // namespace
+}  // namespace dbaf
+
+extern "C" size_t dbaf_ba_band_strip_doubles(int n_poses, int band_blocks) {
+  const size_t n = 6 * (size_t)n_poses;
+  return n * 6 * (2 * (size_t)band_blocks + 1) + n;
+}
+
+extern "C" int dbaf_ba_band_strip(void* workspace, int t0, int t1, int band_blocks, double* strip, int pack, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr && strip != nullptr, "null pointer");
+  DBAF_REQUIRE(t1 >= t0 && band_blocks >= 0, "bad sizes");
+  dbaf_ba_layout L;
+  fill_layout(1, 0, 0, t1 - t0, 1, 1, &L);
+  Ws ws = view(workspace, L);
+  const int n = 6 * (t1 - t0);
+  if (n == 0) return DBAF_OK;
+  if (pack) k_band_strip<true><<<n + 1, 256, 0, (cudaStream_t)stream>>>(ws.H, ws.v, n, band_blocks, strip);
+  else k_band_strip<false><<<n + 1, 256, 0, (cudaStream_t)stream>>>(ws.H, ws.v, n, band_blocks, strip);
+  DBAF_LAUNCH_CHECK("k_band_strip");
+  return DBAF_OK;
+}
+
+extern "C" int dbaf_ba_zero_system(void* workspace, int t0, int t1, int band_blocks, void* stream) {
+  DBAF_REQUIRE(workspace != nullptr, "null workspace");
+  DBAF_REQUIRE(t1 >= t0, "t1 < t0");
+  dbaf_ba_layout L;
+  fill_layout(1, 0, 0, t1 - t0, 1, 1, &L);
+  Ws ws = view(workspace, L);
+  const int P = t1 - t0, n = 6 * P;
+  if (n == 0) return DBAF_OK;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (band_blocks <= 0 || 2 * band_blocks + 1 >= P) {
+    DBAF_CUDA(cudaMemsetAsync(ws.H, 0, ((size_t)n * n + n) * 8, st));
+    return DBAF_OK;
+  }
+  k_zero_band<<<n + 1, 128, 0, st>>>(ws.H, ws.v, n, band_blocks);
+  DBAF_LAUNCH_CHECK("k_zero_band");
+  return DBAF_OK;
+}
+
 extern "C" int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep, const double* prior,
                              int prior_rows, int prior_cols, void* stream) {
   DBAF_REQUIRE(workspace != nullptr, "null workspace");

@@ -73,8 +73,10 @@ class CudaEngine:
         self.w = db._Window(poses, disps, intrinsics, disps_sens, targets, weights, eta, ii, jj, t0, t1)
         self.w.prepare()
 
-    def linearize(self, alpha, k_lo, k_hi):
-        self.w.linearize(alpha, zero_first=True, k_lo=k_lo, k_hi=k_hi)
+    def linearize(self, alpha, k_lo, k_hi, band=0):
+        # every block of the reduced system lies within `band` pose blocks of the diagonal: clear only that
+        self.w.zero_system(band)
+        self.w.linearize(alpha, zero_first=False, k_lo=k_lo, k_hi=k_hi)
 
     def system(self):
         return self.w.Hv()
@@ -103,7 +105,7 @@ class GlobalBA:
 
     def iterate(self, lm=1e-4, ep=0.1, alpha=0.05):
         e = self.engine
-        e.linearize(alpha, self.k_lo, self.k_hi)
+        e.linearize(alpha, self.k_lo, self.k_hi, self.band)
         if self.world > 1:
             self.reduce_system(e.system())
         e.solve(lm, ep, self.band)
@@ -127,6 +129,13 @@ class GlobalBA:
         """Sum the reduced camera system over the ranks (the one exchange step of the path).  Every rank's
         contribution lies inside the band of the frame graph, so only the band travels: 12 MB instead of the
         288 MB of the dense 6000 x 6000 float64 H at the 1000-keyframe size."""
+        w = getattr(self.engine, "w", None)
+        if w is not None and hasattr(w, "band_strip") and 0 < self.band and 2 * self.band + 1 < 0.6 * self.P:
+            # the CUDA engine packs / unpacks the band with its own kernels (dbaf_ba_band_strip)
+            self._strip = w.band_strip(self.band, getattr(self, "_strip", None), pack=True)
+            dist.all_reduce(self._strip, op=dist.ReduceOp.SUM, group=self.group)
+            w.band_strip(self.band, self._strip, pack=False)
+            return
         idx = self.band_index(sys_flat.device)
         if idx is None:
             dist.all_reduce(sys_flat, op=dist.ReduceOp.SUM, group=self.group)
@@ -136,11 +145,11 @@ class GlobalBA:
         sys_flat.index_copy_(0, idx, packed)
 
     def launches_per_iteration(self):
-        """Kernels of this library enqueued by one `iterate` on a dense graph: k_depth_diag, k_linschur_tc, then
+        """Kernels of this library enqueued by one `iterate` on a dense graph: k_zero_band, k_depth_diag, k_linschur_tc, then
         k_linearize2 / k_schur_smem / k_schur for the frames those left, the banded solve's kernels (sweeps, spike,
         separator chain, back-substitutions), k_backsub_fused, k_backsub_rc."""
         import droid_backends as db
-        return 5 + db.banded_solve_launches(self.P, self.band) + 2
+        return 6 + db.banded_solve_launches(self.P, self.band) + 2
 
     def run(self, iterations, lm=1e-4, ep=0.1):
         for _ in range(iterations):
@@ -312,7 +321,7 @@ def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
     step_ms = statistics.mean(ms)
     # stage breakdown on this rank
     stages = {}
-    for name, fn in (("linearize+schur", lambda: eng.linearize(0.05, gba.k_lo, gba.k_hi)),
+    for name, fn in (("linearize+schur", lambda: eng.linearize(0.05, gba.k_lo, gba.k_hi, gba.band)),
                      ("allreduce", (lambda: gba.reduce_system(eng.system())) if world > 1 else (lambda: None)),
                      ("solve", lambda: eng.solve(1e-4, 0.1, gba.band)),
                      ("retract", lambda: eng.retract(gba.k_lo, gba.k_hi))):
@@ -381,7 +390,7 @@ def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
                 warmup=max(3, args.warmup), ms_per_step=step_ms, higher_is_better=False, scaling="strong",
                 vs_baseline=None, dtype="f32", data="synthetic", config=c5_config(),
                 shard=dict(depth_frame_ranges=[list(r) for r in gba.ranges], band_blocks=gba.band,
-                           solve_launches=gba.launches_per_iteration() - 7),
+                           solve_launches=gba.launches_per_iteration() - 8),
                 roofline=roof, stages_ms=stages, parity_vs_1gpu=parity,
                 e2e=dict(value=float(e2e[0]), unit="ms/iter", h2d_bytes_per_step=int(e2e[1]),
                          d2h_bytes_per_step=int(e2e[2]), ms_per_step=float(e2e[0]),

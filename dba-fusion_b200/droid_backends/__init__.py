@@ -237,6 +237,18 @@ class _Window:
                                     self.t1, self.ht, self.wd, float(alpha), int(motion_only),
                                     int(zero_first), int(k_lo), int(k_hi), _stream()), "dbaf_ba_linearize")
 
+    def zero_system(self, band=0):
+        """H, v = 0 ahead of linearize(zero_first=False); with a band hint only the band of H is cleared."""
+        check(lib.dbaf_ba_zero_system(_p(self.ws), self.t0, self.t1, int(band), _stream()), "dbaf_ba_zero_system")
+
+    def band_strip(self, band, strip=None, pack=True):
+        """The band of H, and v, as one dense float64 strip (pack) or back from it (pack=False)."""
+        if strip is None:
+            strip = torch.empty(lib.dbaf_ba_band_strip_doubles(self.P, int(band)), dtype=torch.float64, device=self.ws.device)
+        check(lib.dbaf_ba_band_strip(_p(self.ws), self.t0, self.t1, int(band), _p(strip), int(pack), _stream()),
+              "dbaf_ba_band_strip")
+        return strip
+
     def solve(self, lm, ep, prior=None, band=0, prior_shape=None):
         if band and prior is None:
             check(lib.dbaf_ba_solve_banded(_p(self.ws), self.t0, self.t1, float(lm), float(ep), int(band),

@@ -68,6 +68,9 @@ SIGNATURES = {
     "dbaf_ba_solve": (c_int, [P, c_int, c_int, c_float, c_float, P, c_int, c_int, P]),
     "dbaf_ba_solve_banded": (c_int, [P, c_int, c_int, c_float, c_float, c_int, P]),
     "dbaf_ba_solve_banded_launches": (c_int, [c_int, c_int]),
+    "dbaf_ba_zero_system": (c_int, [P, c_int, c_int, c_int, P]),
+    "dbaf_ba_band_strip_doubles": (c_size_t, [c_int, c_int]),
+    "dbaf_ba_band_strip": (c_int, [P, c_int, c_int, c_int, P, c_int, P]),
     "dbaf_ba_retract": (c_int, [P, P, P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                 c_int, c_int, P, P, P]),
     "dbaf_ba": (c_int, [P, P, P, P, P, P, P, P, c_int, P, P, c_int, c_int, c_int, c_int, c_int, c_int,

@@ -289,6 +289,18 @@ int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep,
  * The workspace must have gone through dbaf_ba_prepare (it zeroes the failure counter info[1]).
  * Replaces Eigen::SimplicialLLT on the host (src/droid_kernels.cu:1248-1269). */
 int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, int band_blocks, void* stream);
+/* Zeroes the reduced camera system before a dbaf_ba_linearize(..., zero_first = 0): only the entries within
+ * `band_blocks` pose blocks of the diagonal, and v, when the caller promises (as for dbaf_ba_solve_banded) that
+ * nothing else is ever written -- 12 MB instead of the 288 MB of the dense float64 matrix at 1000 poses.
+ * band_blocks <= 0 clears everything.  The reference allocates fresh zero tensors every iteration
+ * (src/droid_kernels.cu:1440-1447). */
+int dbaf_ba_zero_system(void* workspace, int t0, int t1, int band_blocks, void* stream);
+/* The band of H (row r: the columns of pose blocks r/6 - band_blocks .. r/6 + band_blocks) and v as one dense strip
+ * of dbaf_ba_band_strip_doubles() float64 values: pack = 1 copies workspace -> strip, pack = 0 strip -> workspace.
+ * This is what edge-sharded global BA sums over the GPUs (one NCCL all-reduce on the strip) instead of the dense
+ * matrix.  No counterpart in the reference (it has no multi-GPU path). */
+size_t dbaf_ba_band_strip_doubles(int n_poses, int band_blocks);
+int dbaf_ba_band_strip(void* workspace, int t0, int t1, int band_blocks, double* strip, int pack, void* stream);
 /* how many kernels dbaf_ba_solve_banded enqueues for that many poses and that band (bench.py counts launches with it) */
 int dbaf_ba_solve_banded_launches(int n_poses, int band_blocks);
 

