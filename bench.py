@@ -44,7 +44,7 @@ import torch  # noqa: E402
 
 # ----------------------------------------------------------------------------- helpers
 # DRAM bytes per launch read from committed ncu captures (profiles/), keyed by (workload, kernel)
-NCU_TRAFFIC_BYTES = {("c2", "k_linearize2"): 3.79e6, ("c2", "k_volume_tc"): 2.137e9, ("c2", "k_corr_lookup"): 3.67e8}
+NCU_TRAFFIC_BYTES = {("c2", "k_linearize2"): 3.79e6, ("c2", "k_volume_tc"): 2.116e9, ("c2", "k_corr_lookup"): 4.14e8}   # profiles/r2_ncu_c2.md
 
 
 def write_only_peak(dev):
@@ -211,7 +211,7 @@ def bench_local(args, dev, rank, world):
     lin_ms = stage["linearize"]
     lin_bytes = E * HW * 20 + K * HW * 12          # algorithmic bytes of the linearise kernel
     # traffic: dram__bytes_read.sum + dram__bytes_write.sum of one k_linearize2 launch on this workload from the
-    # committed `ncu --set full` capture (profiles/r1_ncu_ba_c2.md); it cannot be measured outside a profiler
+    # committed `ncu --set full` capture (profiles/r2_ncu_c2.md); it cannot be measured outside a profiler
     traffic = NCU_TRAFFIC_BYTES.get((cfg, "k_linearize2"))
     roof = dict(bound="hbm", kernel="k_linearize2", achieved=lin_bytes / (lin_ms * 1e-3) / 1e9, peak=peaks["hbm"],
                 unit="GB/s", peak_source=peaks["src"] + " (burst, kernel timed alone)", traffic=traffic,

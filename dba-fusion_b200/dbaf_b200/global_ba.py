@@ -271,6 +271,11 @@ C5_WORKLOAD = ("c5 global BA: 1000-frame banded keyframe graph (999 window poses
 C5_L2 = "512 MB read+write between steps (the 1.4 GB of inputs are also larger than the 126 MB L2)"
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum of k_depth_diag (0.721 GB) + k_linschur_tc (1.399 GB) for the whole
+# window, from the committed `ncu --set full` capture (profiles/r2_ncu_c5.md)
+C5_NCU_TRAFFIC_BYTES = 2.120e9
+
+
 def c5_config():
     """`config` of the bench line; the reference arm prints the identical dict."""
     return dict(workload=C5_WORKLOAD, l2=C5_L2)
@@ -383,7 +388,7 @@ def bench(args, dev, rank, world, ClockSampler, L2Flusher, peaks):
     lin_bytes = n_edges * HW * 20 + K * HW * 12
     roof = dict(bound="hbm", kernel="k_depth_diag + k_linschur_tc (this rank's shard: linearisation and Schur complement)",
                 unit="GB/s", peak=peaks["hbm"],
-                achieved=lin_bytes / world / (stages["linearize+schur"] * 1e-3) / 1e9, traffic=None,
+                achieved=lin_bytes / world / (stages["linearize+schur"] * 1e-3) / 1e9, traffic=C5_NCU_TRAFFIC_BYTES / world,
                 peak_source=peaks["src"], algorithmic_bytes=lin_bytes // world, ms=stages["linearize+schur"])
     roof["frac"] = roof["achieved"] / roof["peak"]
     line = dict(metric="dense-BA ms/iter", value=step_ms, unit="ms/iter", n_gpus=world, steps=args.steps,
