@@ -186,7 +186,18 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
   }
   __syncthreads();
   const int nwork = nt - 32;                           // the last warp runs the look-ahead chain
+#ifdef DBAF_SOLVE6_PROFILE
+  long long la[4] = {0, 0, 0, 0}, wk[4] = {0, 0, 0, 0}, c0_, c1_;
+#define LA_TICK(i) do { c1_ = clock64(); la[i] += c1_ - c0_; c0_ = c1_; } while (0)
+#define WK_TICK(i) do { c1_ = clock64(); wk[i] += c1_ - c0_; c0_ = c1_; } while (0)
+#else
+#define LA_TICK(i) do {} while (0)
+#define WK_TICK(i) do {} while (0)
+#endif
   for (int J = 0; J < P; ++J) {
+#ifdef DBAF_SOLVE6_PROFILE
+    c0_ = clock64();
+#endif
     const int j0 = 6 * J;
     // the diagonal block of this column was factorised during the previous step (look-ahead, see below)
     if (*fail) return false;
@@ -215,6 +226,7 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
       if (mrows > 1 && ln < 6) panel_row(r0 + ln);
       __syncwarp();
       asm volatile("bar.arrive 1, %0;" ::"r"(nt) : "memory");
+      LA_TICK(0);
       if (mrows > 1) {
         if (ln < 21) {
           int r, c;
@@ -227,46 +239,68 @@ __device__ bool cholesky6_factor(double* L, int ld, int P, double* dinv, int* fa
           L[(size_t)(r0 + r) * ld + r0 + c] -= sum;
         }
         __syncwarp();
+        LA_TICK(1);
         if (ln == 0) factor_diag6(L, ld, r0, dinv, fail);
+        __syncwarp();
+        LA_TICK(2);
       }
     } else {
       // (1) the rest of the panel (the next block's six rows are the look-ahead warp's), row n = right-hand side
       for (int r = (mrows > 1 ? r0 + 6 : r0) + tid; r <= n; r += nwork) panel_row(r);
+      WK_TICK(0);
       asm volatile("bar.sync 1, %0;" ::"r"(nt) : "memory");      // the whole panel, the look-ahead warp's rows included
+      WK_TICK(1);
       // (2) trailing update A[r][c] -= sum_k L[r][j0+k] L[c][j0+k] for j0+6 <= c <= min(r, n-1), r <= n; the next
       //     diagonal block is the look-ahead warp's
       if (mrows > 1) {
-        // 15 x 16 thread grid over the (rows x cols) triangle: no integer division, the row's six panel
-        // values are loaded once per row and reused along it
+        // 15 x 16 thread grid over the (rows x cols) triangle: no integer division.  A thread takes two rows and two
+        // columns per pass: four independent dot products (24 DFMAs in flight against a 9-cycle dependent latency)
+        // from 24 loads; with one row per pass the update was a chain of ~10 dependent 6-DFMA dots per thread
         const int ty = tid >> 4, tx = tid & 15;
-        for (int ro = ty; ro < mrows; ro += (nwork >> 4)) {
-          const double* lr = L + (size_t)(r0 + ro) * ld + j0;
-          double a[6];
+        const int rstep = nwork >> 4;
+        for (int ro = ty; ro < mrows; ro += 2 * rstep) {
+          const int rb = ro + rstep;
+          const bool has_b = rb < mrows;
+          const double* lra = L + (size_t)(r0 + ro) * ld + j0;
+          const double* lrb = L + (size_t)(r0 + (has_b ? rb : ro)) * ld + j0;
+          double a[6], b[6];
 #pragma unroll
-          for (int kk = 0; kk < 6; ++kk) a[kk] = lr[kk];
-          const int cmax = min(ro, mrows - 2);
-          double* out = L + (size_t)(r0 + ro) * ld + r0;
-          // two columns per pass: independent dot products keep the fp64 pipe busy while the loads are in flight
-          for (int co = tx; co <= cmax; co += 32) {
+          for (int kk = 0; kk < 6; ++kk) { a[kk] = lra[kk]; b[kk] = lrb[kk]; }
+          const int cmax_a = min(ro, mrows - 2), cmax_b = has_b ? min(rb, mrows - 2) : -1;
+          double* out_a = L + (size_t)(r0 + ro) * ld + r0;
+          double* out_b = L + (size_t)(r0 + (has_b ? rb : ro)) * ld + r0;
+          for (int co = tx; co <= max(cmax_a, cmax_b); co += 32) {
             const int c2 = co + 16;
-            const bool do1 = !(ro < 6 && co < 6);      // next diagonal block: look-ahead warp
-            const bool do2 = c2 <= cmax;
             const double* lc1 = L + (size_t)(r0 + co) * ld + j0;
-            const double* lc2 = L + (size_t)(r0 + (do2 ? c2 : co)) * ld + j0;
-            double s1 = 0.0, s2 = 0.0;
+            const double* lc2 = L + (size_t)(r0 + min(c2, mrows - 2)) * ld + j0;
+            double sa1 = 0.0, sa2 = 0.0, sb1 = 0.0, sb2 = 0.0;
 #pragma unroll
             for (int kk = 0; kk < 6; ++kk) {
-              s1 = fma(a[kk], lc1[kk], s1);
-              s2 = fma(a[kk], lc2[kk], s2);
+              const double x1 = lc1[kk], x2 = lc2[kk];
+              sa1 = fma(a[kk], x1, sa1);
+              sa2 = fma(a[kk], x2, sa2);
+              sb1 = fma(b[kk], x1, sb1);
+              sb2 = fma(b[kk], x2, sb2);
             }
-            if (do1) out[co] -= s1;
-            if (do2) out[c2] -= s2;
+            // (the next diagonal block, rows and columns 0..5, is the look-ahead warp's)
+            if (co <= cmax_a && !(ro < 6 && co < 6)) out_a[co] -= sa1;
+            if (c2 <= cmax_a) out_a[c2] -= sa2;
+            if (co <= cmax_b && !(rb < 6 && co < 6)) out_b[co] -= sb1;
+            if (c2 <= cmax_b) out_b[c2] -= sb2;
           }
         }
       }
+      WK_TICK(2);
     }
     __syncthreads();
+#ifdef DBAF_SOLVE6_PROFILE
+    if (tid >= nwork) LA_TICK(3); else WK_TICK(3);
+#endif
   }
+#ifdef DBAF_SOLVE6_PROFILE
+  if (tid == nwork) printf("  look-ahead warp per step: panel %lld, diag update %lld, diag factor %lld, barrier %lld\n", la[0] / P, la[1] / P, la[2] / P, la[3] / P);
+  if (tid == 0) printf("  worker warp 0 per step: panel %lld, wait panel %lld, trailing update %lld, barrier %lld\n", wk[0] / P, wk[1] / P, wk[2] / P, wk[3] / P);
+#endif
   return *fail == 0;
 }
 
