@@ -819,7 +819,7 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       const int gt = (NS + kGramTile - 1) / kGramTile;
       k_spike_gram<<<dim3(gt * (gt + 1) / 2, n_mid), 256, 0, st>>>(B, plan, sp, ws);
       DBAF_LAUNCH_CHECK("k_spike_gram");
-      const size_t asm_ = ((size_t)(NS + 1) * ld + NS + (size_t)5 * 8 * ld) * sizeof(double);
+      const size_t asm_ = ((size_t)(NS + 1) * ld + NS + (size_t)2 * (kSpikeThreads / 32) * ld) * sizeof(double);   // L, 1/diag, per warp: x row + A row
       const size_t bsm = (size_t)NS * ld * sizeof(double);
       for (int level = 0; level < sp.nlev; ++level) {
         k_red_a<<<dim3(sp.G, 2), kSpikeThreads, asm_, st>>>(P, B, lm, ep, level, plan, sp, ws);

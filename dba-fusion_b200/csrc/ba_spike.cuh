@@ -238,34 +238,47 @@ __device__ __forceinline__ SepAsm sep_asm(int s, const BandPlan& plan, const Spi
 __device__ void sep_assemble(const SepAsm& a, double* L, int ld, int B, int n, float lm, float ep, const Ws& ws) {
   const int tid = threadIdx.x, nt = blockDim.x;
   const int NS = 6 * B;
-  // blocks (bi >= bj) of the top-down sweep's view of the separator, 36 consecutive doubles each; four elements per
-  // pass so that four loads are in flight per thread
-  for (int e0 = tid; e0 < B * B * 36; e0 += 4 * nt) {
-    double v[4];
-    int dst[4];
+  // blocks (bi >= bj) of the top-down sweep's view of the separator, 36 consecutive doubles each.  One CTA pulls
+  // ~115 KB per term through a ~1 us latency: what counts is the number of bytes in flight, so every thread issues
+  // eight 16-byte loads (pairs of one block row) before it touches the first value
+  const int n_pairs = B * B * 18;
+  for (int q0 = tid; q0 < n_pairs; q0 += 8 * nt) {
+    double2 v[8];
+    int dst[8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
-      const int e = e0 + u * nt;
+    for (int u = 0; u < 8; ++u) {
+      const int q = q0 + u * nt;
       dst[u] = -1;
-      v[u] = 0.0;
-      if (e >= B * B * 36) continue;
+      v[u] = make_double2(0.0, 0.0);
+      if (q >= n_pairs) continue;
+      const int e = 2 * q;
       const int blk = e / 36, rc = e - blk * 36, bi = blk / B, bj = blk - bi * B;
-      const int r = rc / 6, c = rc - 6 * r;
-      if (bi < bj || (bi == bj && c > r)) continue;
+      const int r = rc / 6, c = rc - 6 * r;          // c even: (c, c + 1) lie in one block row
+      if (bi < bj || (bi == bj && c > r)) continue;  // (strictly above the diagonal; c == r keeps the first of the pair)
       dst[u] = (6 * bi + r) * ld + 6 * bj + c;
-      v[u] = a.dumpA[e];
+      v[u] = *reinterpret_cast<const double2*>(a.dumpA + e);
       if (a.dumpR) {
         // the bottom-up sweep works on the block-reversed ordering: physical block (bi, bj), bi >= bj, is the transpose
         // of its logical block (B-1-bj, B-1-bi); both sweeps carry the damped A_ss, counted once
-        const int brc = bi == bj ? r * 6 + c : c * 6 + r;
-        double h = ws.H[(size_t)(6 * (a.m + bi) + r) * n + 6 * (a.m + bj) + c];
-        if (bi == bj && r == c) h += (double)ep + (double)lm * h;
-        v[u] += a.dumpR[(size_t)((B - 1 - bj) * B + (B - 1 - bi)) * 36 + brc] - h;
+        const double* dr = a.dumpR + (size_t)((B - 1 - bj) * B + (B - 1 - bi)) * 36;
+        const double* hr = ws.H + (size_t)(6 * (a.m + bi) + r) * n + 6 * (a.m + bj) + c;
+        double h0 = hr[0], h1 = hr[1];
+        if (bi == bj && r == c) h0 += (double)ep + (double)lm * h0;
+        if (bi == bj && r == c + 1) h1 += (double)ep + (double)lm * h1;
+        v[u].x += dr[bi == bj ? r * 6 + c : c * 6 + r] - h0;
+        v[u].y += dr[bi == bj ? r * 6 + c + 1 : (c + 1) * 6 + r] - h1;
       }
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u)
-      if (dst[u] >= 0) L[dst[u]] = v[u];
+    for (int u = 0; u < 8; ++u)
+      if (dst[u] >= 0) {
+        L[dst[u]] = v[u].x;
+        // second element of the pair: inside the lower triangle unless the pair straddles the diagonal of a diagonal block
+        const int e = 2 * (q0 + u * nt);
+        const int blk = e / 36, rc = e - blk * 36, bi = blk / B, bj = blk - bi * B;
+        const int r = rc / 6, c = rc - 6 * r;
+        if (!(bi == bj && c + 1 > r)) L[dst[u] + 1] = v[u].y;
+      }
   }
   for (int i = tid; i < NS; i += nt) {
     double v = a.dumpA[(size_t)B * B * 36 + i];
@@ -324,7 +337,7 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
   const int NS = 6 * B, n = 6 * Pphys, ld = spike_ld(NS);
   double* L = smr;                                   // (NS + 1) x ld
   double* dinv = L + (size_t)(NS + 1) * ld;          // NS
-  double* xs = dinv + NS;                            // rows of X of this CTA: [rps][ld]
+  double* xs = dinv + NS;                            // per warp: the row of X being built and the row of A, [2][ld]
   const SepAsm as = sep_asm(s, plan, sp, ws);
   sep_assemble(as, L, ld, B, n, lm, ep, ws);
   const bool ok = cholesky6_factor(L, ld, B, dinv, &fail);
@@ -339,61 +352,62 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
     for (int e = tid; e < (NS + 1) * ld; e += nt) Lf[e] = L[e];   // (the unused upper triangle travels along)
     for (int i = tid; i < NS; i += nt) Lf[(size_t)(NS + 1) * ld + i] = dinv[i];
   }
-  // rows [i_lo, i_hi) of X: x L^T = a, a = row of R(t,s).  Five rows per warp, six lanes per row (one per column of
-  // the current 6-wide block): the lanes of a row split the dot products, lane c == 0 finishes the block.
+  // rows [i_lo, i_hi) of X: x L^T = a, a = row of R(t,s).  One warp per row.  The row of A is brought into shared
+  // memory up front (one exposed latency instead of one per 6-wide block); for block J the 24 lanes (part, column)
+  // split the dot products  sum_k x[k] L[c][k]  four ways, lanes 0..5 finish the 6x6 triangular solve through
+  // shuffles.  (Five rows per warp with one lane per column and a global load per block took 40 of the 79 us.)
   const int rps = (NS + gridDim.x - 1) / gridDim.x;
   const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
   const double* Rts = side == 0 ? ws.Lfac + sp.Roff[s] : ws.Lfac + sp.Roff[t];
-  const int rw = lane / 6, cw = lane - 6 * rw;       // row within the warp (0..4), column within the block
-  constexpr int kRowWarps = 8;                       // warps that hold row buffers (shared-memory budget)
-  const int rows_per_pass = 5 * kRowWarps;
-  if (wid >= kRowWarps) return;
-  for (int base = i_lo; base < i_hi; base += rows_per_pass) {
-    const int li = wid * 5 + rw;                     // local row of this pass
-    const int i = base + li;
-    const bool act = rw < 5 && i < i_hi;
-    double* xr = xs + (size_t)(act ? li : 0) * ld;
+  const int nw = nt >> 5;
+  const int part = lane / 6, cw = lane - 6 * part;   // part 0..3 take part in the dots (lanes 0..23)
+  double* Xg = ws.Lfac + sp.X[s];
+  double* Ug = ws.Lfac + sp.U[t][side];
+  for (int i = i_lo + wid; i < i_hi; i += nw) {
+    double* xr = xs + (size_t)wid * 2 * ld;            // x (being built), then the row of A behind it
+    double* ar = xr + ld;
+    // A(t,s)[i][c]: side 0 reads Roff[s] as stored (rows: S_{s+1}), side 1 the transpose of Roff[t] (rows: S_s)
+    for (int c = lane; c < NS; c += 32) ar[c] = side == 0 ? Rts[(size_t)i * NS + c] : Rts[(size_t)c * NS + i];
+    __syncwarp();
     for (int J = 0; J < B; ++J) {
+      const int c = 6 * J + cw;
       double sum = 0.0;
-      if (act) {
-        const int c = 6 * J + cw;
-        // A(t,s)[i][c]: side 0 reads Roff[s] as stored (rows: S_{s+1}), side 1 the transpose of Roff[t] (rows: S_s)
-        sum = side == 0 ? Rts[(size_t)i * NS + c] : Rts[(size_t)c * NS + i];
+      if (part < 4) {
         const double* lc = L + (size_t)c * ld;
         double s0 = 0.0, s1 = 0.0;
-        int k = 0;
-        for (; k + 1 < 6 * J; k += 2) {
+        int k = part;
+        for (; k + 4 < 6 * J; k += 8) {
           s0 = fma(xr[k], lc[k], s0);
-          s1 = fma(xr[k + 1], lc[k + 1], s1);
+          s1 = fma(xr[k + 4], lc[k + 4], s1);
         }
-        sum -= s0 + s1;
+        if (k < 6 * J) s0 = fma(xr[k], lc[k], s0);
+        sum = s0 + s1;
       }
-      // finish the 6x6 triangular solve of the block on the lanes of the row: column sweep through shuffles
+      // lanes 0..5 collect the four parts (sources 6, 12, 18 lanes up)
+      sum += __shfl_down_sync(0xffffffffu, sum, 12);
+      sum += __shfl_down_sync(0xffffffffu, sum, 6);
+      const bool act = lane < 6;
+      sum = act ? ar[c] - sum : 0.0;
+      // finish the 6x6 triangular solve of the block on lanes 0..5: column sweep through shuffles
 #pragma unroll
       for (int c2 = 0; c2 < 6; ++c2) {
-        const int srcl = rw * 6 + c2;
         double xc = sum * (act ? dinv[6 * J + c2] : 0.0);
-        xc = __shfl_sync(0xffffffffu, xc, srcl);                    // x[c2] of this row, final
+        xc = __shfl_sync(0xffffffffu, xc, c2);                       // x[c2] of this row, final
         if (act && cw > c2) sum = fma(-xc, L[(size_t)(6 * J + cw) * ld + 6 * J + c2], sum);
-        if (act && cw == c2) { sum = xc; }
+        if (act && cw == c2) sum = xc;
       }
       if (act) xr[6 * J + cw] = sum;
       __syncwarp();
     }
-    // rows of this pass: X to global, and their entry of X y_s
-    double* Xg = ws.Lfac + sp.X[s];
-    double* Ug = ws.Lfac + sp.U[t][side];
+    // the row of X to global, and its entry of X y_s
     double dot = 0.0;
-    if (act) {
-      for (int k = cw; k < NS; k += 6) {
-        Xg[(size_t)i * NS + k] = xr[k];
-        dot = fma(xr[k], L[(size_t)NS * ld + k], dot);
-      }
+    for (int k = lane; k < NS; k += 32) {
+      const double x = xr[k];
+      Xg[(size_t)i * NS + k] = x;
+      dot = fma(x, L[(size_t)NS * ld + k], dot);
     }
-    double tot = 0.0;                                 // sum over the six lanes of the row (all lanes take part)
-#pragma unroll
-    for (int q = 0; q < 6; ++q) tot += __shfl_sync(0xffffffffu, dot, (rw * 6 + q) & 31);
-    if (act && cw == 0) Ug[(size_t)NS * NS + i] = tot;
+    dot = warp_sum_d(dot);
+    if (lane == 0) Ug[(size_t)NS * NS + i] = dot;
     __syncwarp();
   }
 }
