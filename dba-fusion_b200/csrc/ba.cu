@@ -617,8 +617,19 @@ extern "C" int dbaf_ba_linearize(void* workspace, const float* poses, const floa
       DBAF_CUDA(cudaFuncSetAttribute(k_linschur_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kLsSmemBytes));
       ls_attr[dev_id & 63] = true;
     }
-    // one CTA per frame when there are enough frames to fill the machine, else split the pixels
-    int splits = std::max(1, std::min((2 * 148 + k_cap - 1) / k_cap, (HW + 255) / 256));
+    // Pixel ranges per frame: the kernel runs one CTA per SM, in rounds of 148; a CTA that takes 1/s of a frame costs
+    // 1/s + ~0.07 of a whole-frame CTA (prologue, epilogue sums and atomics), so the split that minimises
+    // rounds x cost per round is taken.  It is derived from the WINDOW's frame count, not from this call's range: the
+    // per-CTA sums then do not depend on how the window is sharded, and N ranks reproduce one rank bit for bit.
+    int splits = 1;
+    {
+      double best = 1e30;
+      const int s_max = std::max(1, std::min(8, HW / 256));
+      for (int s_ = 1; s_ <= s_max; ++s_) {
+        const double cost = (double)((ws.Kcap * s_ + 147) / 148) * (1.0 / s_ + 0.07);
+        if (cost < best - 1e-9) { best = cost; splits = s_; }
+      }
+    }
     const int St = (((HW + splits - 1) / splits) + 31) & ~31;
     splits = (HW + St - 1) / St;
     k_depth_diag<<<dim3((HW / 4 + 127) / 128, k_cap), 128, 0, st>>>(poses, disps, intrinsics, disps_sens, weights, eta,
