@@ -514,7 +514,22 @@ k_red_back(int B, BandPlan plan, SpikePlan sp, Ws ws) {
     const double* Xg = ws.Lfac + sp.X[s];
     const double* xt_g = ws.Lfac + sp.xsep + (size_t)t * NS;
     __syncthreads();
-    for (int e = tid; e < NS * ld; e += nt) L[e] = Lf[e];
+    // 117 KB through one CTA: eight 16-byte loads in flight per thread (the offsets of Lf are even, ld is odd: the
+    // factor is copied as a flat array)
+    {
+      const int n2 = (NS * ld) >> 1;
+      const double2* src = reinterpret_cast<const double2*>(Lf);
+      for (int q0 = tid; q0 < n2; q0 += 8 * nt) {
+        double2 v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (q0 + u * nt < n2) v[u] = src[q0 + u * nt];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (q0 + u * nt < n2) { L[2 * (q0 + u * nt)] = v[u].x; L[2 * (q0 + u * nt) + 1] = v[u].y; }
+      }
+      if (((NS * ld) & 1) && tid == 0) L[NS * ld - 1] = Lf[NS * ld - 1];
+    }
     for (int i = tid; i < NS; i += nt) {
       dinv[i] = Lf[(size_t)(NS + 1) * ld + i];
       xt[i] = xt_g[i];
