@@ -825,7 +825,20 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       const int n_mid = D - 2;
       const int ncg = (NS + 29) / 30;
       const size_t fsm = ((size_t)kSpikeRing * ((B + 1) * 36 + 6) + (size_t)(B + 1) * 192 + 4 * 192) * sizeof(double);
-      k_spike_fwd<<<dim3(ncg, n_mid), 128, fsm, st>>>(P, B, plan, sp, ws);
+      {
+        // may start while the sweeps are still running and follows them through their progress words
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(ncg, n_mid);
+        cfg.blockDim = dim3(128);
+        cfg.dynamicSmemBytes = fsm;
+        cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        DBAF_CUDA(cudaLaunchKernelEx(&cfg, k_spike_fwd, P, B, plan, sp, ws));
+      }
       DBAF_LAUNCH_CHECK("k_spike_fwd");
       const int gt = (NS + kGramTile - 1) / kGramTile;
       k_spike_gram<<<dim3(gt * (gt + 1) / 2, n_mid), 256, 0, st>>>(B, plan, sp, ws);

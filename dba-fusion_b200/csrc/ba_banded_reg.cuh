@@ -42,6 +42,12 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   double* Lband = ws.Lfac + pt.store;
   double* dinv_g = Lband + (size_t)P * (B + 1) * 36;
   double* y_g = dinv_g + 6 * P;
+  // Domain-decomposed solve: the spike kernel of this domain (k_spike_fwd, launched with programmatic stream
+  // serialisation) may start now and follow this sweep row by row: progress[d] = number of finished block rows of the
+  // band store (the flag words were cleared by a memset ahead of this kernel).
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  volatile int* progress = (plan.twisted && gridDim.x >= 3)      // (D = gridDim.x domains; flag words: see ba_spike.cuh)
+                               ? reinterpret_cast<volatile int*>(ws.Lfac + plan.flags) + gridDim.x + 2 + blockIdx.x : nullptr;
   const int p0 = pt.base, sd = pt.rev ? -1 : 1;
   const double epd = (double)ep, lmd = (double)lm;
 
@@ -286,6 +292,12 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
     RP_TICK(0);
     __syncthreads();
     RP_TICK(1);
+    // block row J of the band store is complete (its diagonal block and 1/diag were the last pieces): tell the
+    // spike kernel.  The last warp has no task in the trailing update.
+    if (progress != nullptr && tid == nt - 32) {
+      __threadfence();
+      *progress = J + 1;
+    }
     // (2) trailing update, look-ahead factorisation of (J+1, J+1), requests for the block row two steps ahead
     int oi = -1, ok = -1, ri = 0, rk = 0, oa = -1;
     if (ta >= 0) {
@@ -354,6 +366,10 @@ k_solve_banded_reg(int Pphys, int B, float lm, float ep, BandPlan plan, Ws ws) {
   if (tid < 6 && pt.rev == 0) ws.info[10 + tid] = (int)(prof[tid] >> 10);
 #endif
   const bool ok_all = fail == 0;
+  if (progress != nullptr && tid == 0) {         // a failed sweep must not leave its spike kernel waiting
+    __threadfence();
+    *progress = 1 << 30;
+  }
   if (plan.twisted) {
     // this sweep's view of the separator [n_elim, Plog): window blocks and rhs, for k_band_sep
     double* dump = ws.Lfac + pt.dump;

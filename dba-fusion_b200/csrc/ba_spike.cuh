@@ -39,7 +39,7 @@ struct SpikePlan {
   long long U[kSpikeMaxD][2];     // separator s: update received from side 0 / side 1, [NS][NS] then rhs part [NS]
   long long xsep;                 // [D][NS]: separator solutions, entry s
 };
-// flags (int32, at plan.flags): [0, D) sweeps, [D] reduced system, [D + 1] overall
+// flags (int32, at plan.flags): [0, D) sweeps, [D] reduced system, [D + 1] overall, [D + 2, 2 D + 2) progress of the sweeps
 
 __host__ __device__ inline int spike_ld(int NS) { return NS | 1; }
 
@@ -73,8 +73,14 @@ k_spike_fwd(int Pphys, int B, BandPlan plan, SpikePlan sp, Ws ws) {
   double* Ro = ws.Lfac + sp.Roff[d];
   const int mL = sp.m[d];                           // first physical block of the separator on the left
 
+  // The sweep of this domain may still be running (this kernel is launched with programmatic stream serialisation):
+  // block row I of its band store is complete once its progress word has passed min(I, nd - 1).
+  const volatile int* progress = reinterpret_cast<const volatile int*>(ws.Lfac + plan.flags) + sp.D + 2 + d;
   auto request = [&](int I) {
     if (I < rows) {
+      const int need = min(I, nd - 1) + 1;
+      while (*progress < need) __nanosleep(100);
+      __threadfence();
       const unsigned dst = (unsigned)__cvta_generic_to_shared(ring + (I % kSpikeRing) * SD);
       const double* src = Lband + (size_t)I * RD;
       for (int q = tid; q < RD / 2; q += 128)
