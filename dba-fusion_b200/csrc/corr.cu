@@ -110,10 +110,14 @@ k_corr_lookup(LevelPtrs lv, const float* __restrict__ coords, int n, int HW1, in
   const float y0 = __ldg(coords + ((size_t)e * 2 + 1) * HW1 + p) * scale;
   const float fx0 = floorf(x0), fy0 = floorf(y0);
   const float dx = x0 - fx0, dy = y0 - fy0;
-  const int bx = window_base(fx0, R), by = window_base(fy0, R);
+  int bx = window_base(fx0, R), by = window_base(fy0, R);
 
-  const long long slab = ((long long)(slot ? slot[e] : e) * HW1 + p) * (long long)(h2 * w2);
+  // a slot outside the pool (a caller's bookkeeping error) reads as an all-zero volume instead of foreign memory
+  const int vslot = slot ? min(max(slot[e], 0), n_vol - 1) : e;
+  const bool bad_slot = slot != nullptr && slot[e] != vslot;
+  const long long slab = ((long long)vslot * HW1 + p) * (long long)(h2 * w2);
   const long long total = (long long)n_vol * HW1 * (long long)(h2 * w2);
+  if (bad_slot) { bx = 1 << 24; by = 1 << 24; }      // every tap out of bounds: zeros
   // selected with compares so that the pointer table stays in the parameter bank (no local copy)
   const void* volp = lv.vol[0];
 #pragma unroll
