@@ -10,16 +10,18 @@
 // alone (8 B per pixel-edge).  What the reference does in projective_transform_kernel, accum_cuda and
 // EEt6x6 / Ev6x1 (src/droid_kernels.cu:220-468, 993-1043, 1046-1138).
 //
-// Roles (384 threads, one CTA per SM): warps 0-3 drain the TMEM accumulators into fp32 running sums (one thread per
-// row of S), warp 4 issues the MMAs, warps 6-11 are producers.  Producer p owns operand stage p and the 32-pixel
-// slices c = p, p+6, ...; inside the warp, lane = (group g = lane / 8, quad l8 = lane % 8): a thread works on the
-// four consecutive pixels 4 l8 .. 4 l8 + 3 of the slice (one 16-byte chunk of an operand row) and group g on the
-// edges a = g, g + 4, ... of the frame, so every load and every shared-memory store is 128 bits wide.
-//   pass 1: C = sum_e w Jz^2 over the edges (weights only), summed over the four groups -> q = 1 / C, sqrt(q);
-//   pass 2: residuals and Jacobians again, E sqrt(q) split into TF32 hi / lo and stored into the operand rows
-//           6 a .. 6 a + 5, the 21 + 6 terms of Hjj / vj summed over the thread's four pixels, reduced over the
-//           eight lanes of the group (transposed butterfly, 28 shuffles for 4 edges x 32 pixels) and added to the
-//           warp's own partial sums in shared memory.
+// Two kernels.  k_depth_diag first forms the depth diagonal C = sum_e w Jz^2 (+ prior / eta) and q = 1 / C from the
+// weights alone and writes the per-edge relative-pose records: q scales the operand tiles, so it has to be complete
+// before the first tile is written (as a pass inside the producer warps it could not hide its loads: DESIGN.md 3).
+// k_linschur_tc (384 threads, one CTA per SM): warps 0-3 drain the TMEM accumulators into fp32 running sums (one
+// thread per row of S), warp 4 issues the MMAs, warps 6-11 are producers.  Producer p owns operand stage p; the
+// 32-pixel slices are dealt to the producers in a fixed round of 14 (see c_ls_order).  Inside the warp, lane =
+// (group g = lane / 8, quad l8 = lane % 8): a thread works on the four consecutive pixels 4 l8 .. 4 l8 + 3 of the
+// slice (one 16-byte chunk of an operand row) and group g on the edges a = g, g + 4, ... of the frame, so every
+// global load and every shared-memory store is 128 bits wide.  Per edge: residuals and Jacobians, E sqrt(q) split
+// into TF32 hi / lo and stored into the operand rows 6 a .. 6 a + 5, the 21 + 6 terms of Hjj / vj summed over the
+// thread's four pixels, reduced over the eight lanes of the group (transposed butterfly, 28 shuffles for 4 edges x
+// 32 pixels) and added to the warp's own partial sums in shared memory.
 // The self rows (pose-i side of every edge, Ei = -sum_e M_e Ej_e) are not multiplied: their blocks of S are linear
 // images of the edge blocks, S[self][f] = -sum_e M_e S[e][f], formed from the finished S in the epilogue.
 #pragma once
@@ -367,9 +369,6 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
       const float sd[4] = {s4.x, s4.y, s4.z, s4.w};
       const float sq[4] = {sqrtf(q4.x), sqrtf(q4.y), sqrtf(q4.z), sqrtf(q4.w)};
 
-#ifdef LS_WAIT_EARLY
-      mbar_wait(smem_u32(&bars[kLsBarOpEmpty + p]), (use + 1) & 1);
-#endif
       float W[4] = {0.f, 0.f, 0.f, 0.f};
       const int c_next = my_slice(use + 1);
       for (int it = 0; it < n_it; ++it) {
@@ -430,9 +429,7 @@ k_linschur_tc(const float* __restrict__ disps, const float* __restrict__ intr, c
           }
           // the MMAs that read this stage one round ago have retired (asked only now: the first edge's arithmetic
           // overlaps the wait; every group has an edge in round 0, frames here have at least seven)
-#ifndef LS_WAIT_EARLY
           if (it == 0) mbar_wait(smem_u32(&bars[kLsBarOpEmpty + p]), (use + 1) & 1);
-#endif
 #pragma unroll
           for (int n = 0; n < 6; ++n) store_split_at(stage + row_off(6 * a + n), Es[n]);
         }
