@@ -685,7 +685,8 @@ int banded_domains(int P, int B) {
   if (!single && !options().band_twisted && !smem_sweep && B >= 1) {
     const int n_min = B + 2;                                   // interiors longer than the band
     const int d_max = (P + B) / (B + n_min);
-    const int d_want = options().band_domains > 0 ? options().band_domains : (P + B) / (5 * std::max(B, 4));
+    // (cyclic reduction over the separators: the chain costs log2(D) levels, so interiors of ~2 bands are long enough)
+    const int d_want = options().band_domains > 0 ? options().band_domains : (P + B) / (3 * std::max(B, 4));
     D = std::min({d_want, d_max, kSpikeMaxD});
     if (D < 3) D = 1;
   }
@@ -739,8 +740,12 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       auto take = [&](long long doubles) { const long long o = off; off = even(off + doubles); return o; };
       const int interior = P - (D - 1) * B;
       int first = 0;
-      sp.D = D; sp.B = B; sp.mid = D / 2; sp.G = std::max(1, std::min(8, NS / 6));
-      sp.nlev = std::max(sp.mid - 1, D - 1 - sp.mid);
+      sp.D = D; sp.B = B; sp.G = std::max(1, std::min(8, NS / 6));
+      // cyclic reduction over the separators 1 .. D-1: level l eliminates s with s mod 2^(l+1) == 2^l while more than
+      // one multiple of 2^l is left; the last one (sp.mid) is solved densely
+      sp.nlev = 0;
+      while ((D - 1) >> sp.nlev > 1) ++sp.nlev;      // multiples of 2^l in [1, D-1]: (D-1) >> l
+      sp.mid = 1 << sp.nlev;
       for (int d = 0; d < D; ++d) {
         const int nd = interior / D + (d < interior % D ? 1 : 0);
         BandPart& pt = plan.part[d];
@@ -767,10 +772,18 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       }
       for (int q = 1; q <= D - 1; ++q) {
         sp.Lf[q] = take((long long)(NS + 2) * ld);
-        sp.X[q] = take((long long)NS * NS);
-        sp.U[q][0] = take((long long)NS * NS + NS);
-        sp.U[q][1] = take((long long)NS * NS + NS);
+        sp.X[q][0] = take((long long)NS * NS);
+        sp.X[q][1] = take((long long)NS * NS);
       }
+      const long long ublk = (long long)NS * NS + NS;            // (even)
+      sp.Ubase = take(2 * (long long)(D - 1) * ublk);
+      sp.Ubytes = 2 * (long long)(D - 1) * ublk * 8;
+      for (int q = 1; q <= D - 1; ++q) {
+        sp.U[q][0] = sp.Ubase + (2 * (long long)(q - 1)) * ublk;
+        sp.U[q][1] = sp.Ubase + (2 * (long long)(q - 1) + 1) * ublk;
+      }
+      for (int l = 1; l <= sp.nlev && l < kSpikeMaxLev; ++l)
+        for (int a = 1 << l; a + (1 << l) <= D - 1; a += 1 << l) sp.Cl[l][a] = take((long long)NS * NS);
       sp.xsep = take((long long)D * NS);
       plan.flags = take(D + 4);
       plan.twisted = 1;
@@ -794,7 +807,10 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
         D = 1;
       }
     }
-    if (D >= 3) DBAF_CUDA(cudaMemsetAsync(ws.Lfac + plan.flags, 0, (size_t)(D + 4) * 8, st));
+    if (D >= 3) {
+      DBAF_CUDA(cudaMemsetAsync(ws.Lfac + plan.flags, 0, (size_t)(D + 4) * 8, st));
+      DBAF_CUDA(cudaMemsetAsync(ws.Lfac + sp.Ubase, 0, (size_t)sp.Ubytes, st));     // the separators' update accumulators
+    }
     // B <= 20: the sweep that keeps the window in registers; option band_sweep=smem keeps the shared-memory window
     if (smem_sweep) {
       k_solve_banded<<<D, kBandThreads, smem, st>>>(P, B, lm, ep, rezero, plan, ws);
@@ -815,10 +831,10 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       static bool spike_attr[64] = {};
       if (!spike_attr[dev_id & 63]) {
         DBAF_CUDA(cudaFuncSetAttribute(k_spike_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        DBAF_CUDA(cudaFuncSetAttribute(k_red_a, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        DBAF_CUDA(cudaFuncSetAttribute(k_red_b, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_cr_a, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_cr_b, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         DBAF_CUDA(cudaFuncSetAttribute(k_red_mid, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        DBAF_CUDA(cudaFuncSetAttribute(k_red_back, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        DBAF_CUDA(cudaFuncSetAttribute(k_cr_back, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         DBAF_CUDA(cudaFuncSetAttribute(k_spike_back, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
         spike_attr[dev_id & 63] = true;
       }
@@ -844,19 +860,21 @@ int launch_solve(void* workspace, int t0, int t1, float lm, float ep, const doub
       k_spike_gram<<<dim3(gt * (gt + 1) / 2, n_mid), 256, 0, st>>>(B, plan, sp, ws);
       DBAF_LAUNCH_CHECK("k_spike_gram");
       const size_t asm_ = ((size_t)(NS + 1) * ld + NS + (size_t)2 * (kSpikeThreads / 32) * ld) * sizeof(double);   // L, 1/diag, per warp: x row + A row
-      const size_t bsm = (size_t)NS * ld * sizeof(double);
+      const int rps = (NS + sp.G - 1) / sp.G;
+      const size_t bsm = ((size_t)NS * ld + (size_t)NS * (rps | 1)) * sizeof(double);   // Q^T and this CTA's rows of P, transposed
+      auto n_elim = [&](int level) { const int h = 1 << level; return (D - 1 + h) / (2 * h); };   // s = h, 3h, 5h, ... <= D-1
       for (int level = 0; level < sp.nlev; ++level) {
-        k_red_a<<<dim3(sp.G, 2), kSpikeThreads, asm_, st>>>(P, B, lm, ep, level, plan, sp, ws);
-        DBAF_LAUNCH_CHECK("k_red_a");
-        k_red_b<<<dim3(sp.G, 2), kSpikeThreads, bsm, st>>>(B, level, plan, sp, ws);
-        DBAF_LAUNCH_CHECK("k_red_b");
+        k_cr_a<<<dim3(sp.G, 2 * n_elim(level)), kSpikeThreads, asm_, st>>>(P, B, lm, ep, level, plan, sp, ws);
+        DBAF_LAUNCH_CHECK("k_cr_a");
+        k_cr_b<<<dim3(sp.G, 3 * n_elim(level)), kSpikeThreads, bsm, st>>>(B, level, plan, sp, ws);
+        DBAF_LAUNCH_CHECK("k_cr_b");
       }
       const size_t msm = ((size_t)(NS + 1) * ld + 2 * NS) * sizeof(double);
       k_red_mid<<<1, kSpikeThreads, msm, st>>>(P, B, lm, ep, plan, sp, ws);
       DBAF_LAUNCH_CHECK("k_red_mid");
-      if (sp.nlev > 0) {
-        k_red_back<<<2, kSpikeThreads, ((size_t)NS * ld + 3 * NS) * sizeof(double), st>>>(B, plan, sp, ws);
-        DBAF_LAUNCH_CHECK("k_red_back");
+      for (int level = sp.nlev - 1; level >= 0; --level) {
+        k_cr_back<<<n_elim(level), kSpikeThreads, ((size_t)NS * ld + 4 * NS) * sizeof(double), st>>>(B, level, plan, sp, ws);
+        DBAF_LAUNCH_CHECK("k_cr_back");
       }
       int nd_max = 0;
       for (int d = 1; d <= D - 2; ++d) nd_max = std::max(nd_max, plan.part[d].n_elim);
@@ -996,8 +1014,9 @@ extern "C" int dbaf_ba_solve_banded_launches(int n_poses, int band_blocks) {
   const int D = banded_domains(P, B);
   if (D == 1) return 1;
   if (D == 2) return 3;                                        // two sweeps, separator, two back-substitutions
-  const int mid = D / 2, nlev = std::max(mid - 1, D - 1 - mid);
-  return 1 + 2 + 2 * nlev + 1 + (nlev > 0 ? 1 : 0) + 1 + 1;      // sweeps, spike + Gram, levels, middle, chain back, apply, back
+  int nlev = 0;
+  while ((D - 1) >> nlev > 1) ++nlev;
+  return 1 + 2 + 2 * nlev + 1 + nlev + 1 + 1;      // sweeps, spike + Gram, levels, last block, level back-substitutions, apply, back
 }
 
 extern "C" int dbaf_ba_retract(void* workspace, float* poses, float* disps, const float* dx_in,

@@ -15,28 +15,35 @@
 // the sweep; continuing that substitution through the rows of S_{d+1} yields the coupling block
 //     R(S_{d+1}, S_d) = - L(S_{d+1}, I_d) W_d,
 // a third kernel forms  W_d^T W_d  and  W_d^T y_d.  What is left is a block-tridiagonal SPD system over the
-// separators (6B x 6B dense blocks), eliminated from both ends towards the middle separator: per level every CTA of
-// a side factorises the current diagonal block redundantly in shared memory (no communication), solves its slice
-// of rows of X = R(t,s) L_s^-T, and after one kernel boundary forms its slice of the update X X^T of the next
-// diagonal block.  The middle block is solved densely, the chain is back-substituted, the interiors' right-hand
-// sides are corrected by  y_d -= W_d x(S_d), and D back-substitutions (k_spike_back, the streaming two-warp
-// routine of ba_banded.cuh) finish the solve.  Same arithmetic as a sequential Cholesky, reordered; replaces
-// Eigen::SimplicialLLT of the reference (src/droid_kernels.cu:1248-1269).
+// separators (6B x 6B dense blocks), solved by block cyclic reduction: at level l every separator s with
+// s mod 2^(l+1) == 2^l is eliminated at the same time (its neighbours s -+ 2^l survive): every CTA of a group
+// factorises the diagonal block redundantly in shared memory (no communication) and solves its slice of rows of
+//     Xa = A(a,s) L_s^-T,   Xb = A(b,s) L_s^-T;
+// after one kernel boundary the updates  Xa Xa^T, Xb Xb^T  of the neighbours' diagonal blocks and their new coupling
+// -Xb Xa^T are formed.  log2(D) levels instead of D/2, so the chain can be cut into 16 domains at the depth 10 had
+// with an elimination from both ends.  The last separator is solved densely, the levels are back-substituted in
+// reverse, the interiors' right-hand sides are corrected by  y_d -= W_d x(S_d), and D back-substitutions
+// (k_spike_back, the streaming two-warp routine of ba_banded.cuh) finish the solve.  Same arithmetic as a sequential
+// Cholesky of a reordered matrix; replaces Eigen::SimplicialLLT of the reference (src/droid_kernels.cu:1248-1269).
 #pragma once
 
 constexpr int kSpikeMaxD = kBandMaxParts;
 constexpr int kSpikeThreads = 512;   // 4 warps per scheduler: the dense kernels are chains of short shared-memory round trips
 
+constexpr int kSpikeMaxLev = 5;   // cyclic-reduction levels (16 domains: 15 separators, 3 elimination levels + the last block)
 struct SpikePlan {
-  int D, B, mid, G;               // domains, band, middle separator, CTAs per side in the reduced levels
-  int nlev;                       // levels of the two-sided elimination of the separator chain
+  int D, B, mid, G;               // domains, band, LAST separator of the cyclic reduction, CTAs per group in the reduced levels
+  int nlev;                       // elimination levels of the cyclic reduction over the separators
   int m[kSpikeMaxD];              // first physical block of separator s, s = 1 .. D-1
   long long W[kSpikeMaxD];        // middle domain d: spike [n_d][6][NS] doubles
-  long long Roff[kSpikeMaxD];     // middle domain d: coupling block rows S_{d+1}, cols S_d, [NS][NS]
+  long long Roff[kSpikeMaxD];     // middle domain d: coupling block rows S_{d+1}, cols S_d, [NS][NS] (level-0 coupling of s = d)
   long long SLL[kSpikeMaxD];      // middle domain d: W^T W [NS][NS], then W^T y [NS]
   long long Lf[kSpikeMaxD];       // separator s: factor [NS][ld], then y [NS], then 1/diag [NS]
-  long long X[kSpikeMaxD];        // separator s: X_s = R(t,s) L_s^-T, [NS][NS] (rows: unknowns of the next separator t)
-  long long U[kSpikeMaxD][2];     // separator s: update received from side 0 / side 1, [NS][NS] then rhs part [NS]
+  long long X[kSpikeMaxD][2];     // eliminated separator s: Xa = A(s-h,s) L_s^-T and Xb = A(s+h,s) L_s^-T, [NS][NS] each
+  long long U[kSpikeMaxD][2];     // separator s: updates received from its left / right neighbours (accumulated over the
+                                  // levels; cleared by a memset per solve), [NS][NS] then rhs part [NS]
+  long long Cl[kSpikeMaxLev][kSpikeMaxD];   // level l >= 1, separator a: coupling A(a + 2^l, a), [NS][NS] (rows: a + 2^l)
+  long long Ubase, Ubytes;        // the U blocks as one span (offset in doubles, size in bytes)
   long long xsep;                 // [D][NS]: separator solutions, entry s
 };
 // flags (int32, at plan.flags): [0, D) sweeps, [D] reduced system, [D + 1] overall, [D + 2, 2 D + 2) progress of the sweeps
@@ -96,7 +103,9 @@ k_spike_fwd(int Pphys, int B, BandPlan plan, SpikePlan sp, Ws ws) {
     asm volatile("cp.async.wait_group 3;" ::: "memory");          // everything but the 3 newest groups: row I is in
     // right-hand side of this block row: A(I, S_left), non-zero only within the band (I < B)
     double a[6] = {0.0, 0.0, 0.0, 0.0, 0.0, 0.0};
-    if (wq == 0 && live && I < B && I < nd) {
+    // (block row I of the domain lies B + I - cb blocks below column block cb of the separator: only the blocks
+    //  within the band exist -- what lies beyond it is never written, nor cleared by dbaf_ba_zero_system)
+    if (wq == 0 && live && I < B && I < nd && B + I - (c0 + lane) / 6 <= B) {
       const int pr = pt.rev ? pt.base - I : pt.base + I;
       const double* src = ws.H + (size_t)(6 * pr) * n + 6 * mL + c0 + lane;
 #pragma unroll
@@ -235,8 +244,8 @@ __device__ __forceinline__ SepAsm sep_asm(int s, const BandPlan& plan, const Spi
   a.dumpA = ws.Lfac + plan.part[s - 1].dump;
   a.dumpR = s == sp.D - 1 ? ws.Lfac + plan.part[sp.D - 1].dump : nullptr;
   a.sll = s <= sp.D - 2 ? ws.Lfac + sp.SLL[s] : nullptr;
-  a.u0 = (s > 1 && s <= sp.mid) ? ws.Lfac + sp.U[s][0] : nullptr;
-  a.u1 = (s < sp.D - 1 && s >= sp.mid) ? ws.Lfac + sp.U[s][1] : nullptr;
+  a.u0 = ws.Lfac + sp.U[s][0];                         // (zero until a neighbour has been eliminated)
+  a.u1 = ws.Lfac + sp.U[s][1];
   a.m = sp.m[s];
   return a;
 }
@@ -323,22 +332,31 @@ __device__ void sep_assemble(const SepAsm& a, double* L, int ld, int B, int n, f
   __syncthreads();
 }
 
-// which separator a side works on at a level, and its neighbour towards the middle
-__device__ __forceinline__ bool chain_step(const SpikePlan& sp, int level, int side, int& s, int& t) {
-  if (side == 0) { s = 1 + level; t = s + 1; return s <= sp.mid - 1; }
-  s = sp.D - 1 - level; t = s - 1;
-  return s >= sp.mid + 1;
+// cyclic reduction, level l (h = 2^l): the e-th separator eliminated at this level and its two neighbours
+__device__ __forceinline__ void cr_step(const SpikePlan& sp, int level, int e, int& s, int& a, int& b) {
+  const int h = 1 << level;
+  s = h + e * 2 * h;
+  a = s - h >= 1 ? s - h : 0;                 // 0: no such neighbour
+  b = s + h <= sp.D - 1 ? s + h : 0;
+}
+// coupling block A(x + 2^l, x) at level l: rows = unknowns of x + 2^l, columns = unknowns of x
+__device__ __forceinline__ const double* cr_coupling(const SpikePlan& sp, const Ws& ws, int level, int x) {
+  return ws.Lfac + (level == 0 ? sp.Roff[x] : sp.Cl[level][x]);
 }
 
-// level, part a: factor the diagonal block (every CTA of the side, redundantly), then this CTA's rows of
-// X = R(t,s) L_s^-T and of the right-hand-side update X y_s.  grid (G, 2)
+// level, part a: factor the diagonal block of an eliminated separator s (every CTA of its two groups, redundantly),
+// then this CTA's rows of X = A(t,s) L_s^-T for the group's neighbour t and of the right-hand-side update X y_s.
+// grid (G, 2 * eliminated separators): y = 2 e + side, side 0: t = s - h, side 1: t = s + h
 __global__ void __launch_bounds__(kSpikeThreads)
-k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePlan sp, Ws ws) {
+k_cr_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePlan sp, Ws ws) {
   extern __shared__ double smr[];
   __shared__ int fail;
-  int s, t;
-  if (!chain_step(sp, level, blockIdx.y, s, t)) return;
-  const int side = blockIdx.y;
+  const int side = blockIdx.y & 1;
+  int s, na, nb;
+  cr_step(sp, level, blockIdx.y >> 1, s, na, nb);
+  const int t = side == 0 ? na : nb;
+  if (t == 0) return;                                // this neighbour does not exist
+  const bool keeper = blockIdx.x == 0 && (side == 0 || na == 0);   // the one CTA that stores the factor
   const int tid = threadIdx.x, nt = blockDim.x, lane = tid & 31, wid = tid >> 5;
   const int NS = 6 * B, n = 6 * Pphys, ld = spike_ld(NS);
   double* L = smr;                                   // (NS + 1) x ld
@@ -354,26 +372,26 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
     return;
   }
   double* Lf = ws.Lfac + sp.Lf[s];
-  if (blockIdx.x == 0) {                              // keep the factor, y and 1/diag for the back-substitution
+  if (keeper) {                                       // keep the factor, y and 1/diag for the back-substitution
     for (int e = tid; e < (NS + 1) * ld; e += nt) Lf[e] = L[e];   // (the unused upper triangle travels along)
     for (int i = tid; i < NS; i += nt) Lf[(size_t)(NS + 1) * ld + i] = dinv[i];
   }
-  // rows [i_lo, i_hi) of X: x L^T = a, a = row of R(t,s).  One warp per row.  The row of A is brought into shared
+  // rows [i_lo, i_hi) of X: x L^T = a, a = row of A(t,s).  One warp per row.  The row of A is brought into shared
   // memory up front (one exposed latency instead of one per 6-wide block); for block J the 24 lanes (part, column)
   // split the dot products  sum_k x[k] L[c][k]  four ways, lanes 0..5 finish the 6x6 triangular solve through
-  // shuffles.  (Five rows per warp with one lane per column and a global load per block took 40 of the 79 us.)
+  // shuffles.
   const int rps = (NS + gridDim.x - 1) / gridDim.x;
   const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
-  const double* Rts = side == 0 ? ws.Lfac + sp.Roff[s] : ws.Lfac + sp.Roff[t];
+  // A(t,s)[i][c]: t = s + h reads the coupling of s as stored (rows: t), t = s - h the transpose of the coupling of t
+  const double* Cts = cr_coupling(sp, ws, level, side == 1 ? s : t);
   const int nw = nt >> 5;
   const int part = lane / 6, cw = lane - 6 * part;   // part 0..3 take part in the dots (lanes 0..23)
-  double* Xg = ws.Lfac + sp.X[s];
-  double* Ug = ws.Lfac + sp.U[t][side];
+  double* Xg = ws.Lfac + sp.X[s][side];
+  double* Ug = ws.Lfac + sp.U[t][side == 0 ? 1 : 0];  // t = s - h receives from its right, t = s + h from its left
   for (int i = i_lo + wid; i < i_hi; i += nw) {
     double* xr = xs + (size_t)wid * 2 * ld;            // x (being built), then the row of A behind it
     double* ar = xr + ld;
-    // A(t,s)[i][c]: side 0 reads Roff[s] as stored (rows: S_{s+1}), side 1 the transpose of Roff[t] (rows: S_s)
-    for (int c = lane; c < NS; c += 32) ar[c] = side == 0 ? Rts[(size_t)i * NS + c] : Rts[(size_t)c * NS + i];
+    for (int c = lane; c < NS; c += 32) ar[c] = side == 1 ? Cts[(size_t)i * NS + c] : Cts[(size_t)c * NS + i];
     __syncwarp();
     for (int J = 0; J < B; ++J) {
       const int c = 6 * J + cw;
@@ -405,7 +423,7 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
       if (act) xr[6 * J + cw] = sum;
       __syncwarp();
     }
-    // the row of X to global, and its entry of X y_s
+    // the row of X to global, and its entry of the right-hand-side update X y_s (accumulated: one writer per level)
     double dot = 0.0;
     for (int k = lane; k < NS; k += 32) {
       const double x = xr[k];
@@ -413,59 +431,79 @@ k_red_a(int Pphys, int B, float lm, float ep, int level, BandPlan plan, SpikePla
       dot = fma(x, L[(size_t)NS * ld + k], dot);
     }
     dot = warp_sum_d(dot);
-    if (lane == 0) Ug[(size_t)NS * NS + i] = dot;
+    if (lane == 0) Ug[(size_t)NS * NS + i] += dot;
     __syncwarp();
   }
 }
 
-// level, part b: this CTA's rows of the update  U(t) = X_s X_s^T  (lower triangle).  grid (G, 2)
+// level, part b: this CTA's rows of one of the three products of an eliminated separator s:
+//   which 0:  U(a)[right] += Xa Xa^T (lower triangle)      which 1:  U(b)[left] += Xb Xb^T (lower triangle)
+//   which 2:  coupling A(b,a) of the next level = -Xb Xa^T (all of it)
+// grid (G, 3 * eliminated separators): y = 3 e + which
 __global__ void __launch_bounds__(kSpikeThreads)
-k_red_b(int B, int level, BandPlan plan, SpikePlan sp, Ws ws) {
+k_cr_b(int B, int level, BandPlan plan, SpikePlan sp, Ws ws) {
   extern __shared__ double smx[];
-  int s, t;
-  if (!chain_step(sp, level, blockIdx.y, s, t)) return;
-  const int side = blockIdx.y;
+  const int which = blockIdx.y % 3;
+  int s, na, nb;
+  cr_step(sp, level, blockIdx.y / 3, s, na, nb);
+  if ((which == 0 && na == 0) || (which == 1 && nb == 0) || (which == 2 && (na == 0 || nb == 0))) return;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int NS = 6 * B, ld = spike_ld(NS);
   const int* flags = reinterpret_cast<const int*>(ws.Lfac + plan.flags);
   if (flags[sp.D] != 0) return;
-  const double* Xg = ws.Lfac + sp.X[s];
-  double* Ug = ws.Lfac + sp.U[t][side];
-  // X transposed: smx[k][i], so that the lanes of a warp (consecutive columns j) read consecutive words
+  const double* Qg = ws.Lfac + sp.X[s][which == 1 ? 1 : 0];    // right factor (transposed in the product)
+  const double* Pg = ws.Lfac + sp.X[s][which == 0 ? 0 : 1];    // left factor: rows of the result
+  // Q transposed: smx[k][j], so that the lanes of a warp (consecutive columns j) read consecutive words
   for (int e = tid; e < NS * NS; e += nt) {
     const int i = e / NS, k = e - i * NS;
-    smx[(size_t)k * ld + i] = Xg[e];
+    smx[(size_t)k * ld + i] = Qg[e];
   }
-  __syncthreads();
   const int rps = (NS + gridDim.x - 1) / gridDim.x;
   const int i_lo = blockIdx.x * rps, i_hi = min(NS, i_lo + rps);
-  // a warp task = 3 rows x 32 columns: per k two wavefronts for the columns, three broadcasts for the rows, 96 FMAs
+  // this CTA's rows of P, transposed as well: prow[k][r], r = local row
+  double* prow = smx + (size_t)NS * ld;
+  const int pld = rps | 1;
+  for (int e = tid; e < (i_hi - i_lo) * NS; e += nt) {
+    const int r = e / NS, k = e - r * NS;
+    prow[(size_t)k * pld + r] = Pg[(size_t)(i_lo + r) * NS + k];
+  }
+  __syncthreads();
+  const bool full = which == 2;
+  double* Og = which == 0 ? ws.Lfac + sp.U[na][1] : which == 1 ? ws.Lfac + sp.U[nb][0] : ws.Lfac + sp.Cl[level + 1][na];
+  // a warp task = 3 rows x 32 columns: per k one wavefront for the columns, three broadcasts for the rows, 96 FMAs
   const int lane = tid & 31, wid = tid >> 5, nw = nt >> 5;
   const int n_rt = (i_hi - i_lo + 2) / 3, n_ct = (NS + 31) / 32;
   for (int task = wid; task < n_rt * n_ct; task += nw) {
     const int rt = task / n_ct, ct = task - rt * n_ct;
     const int i0 = i_lo + 3 * rt, j = ct * 32 + lane;
-    if (ct * 32 > min(i0 + 2, i_hi - 1)) continue;               // the whole tile lies above the diagonal
-    const int ia = i0, ib = min(i0 + 1, i_hi - 1), ic = min(i0 + 2, i_hi - 1);
+    if (!full && ct * 32 > min(i0 + 2, i_hi - 1)) continue;      // the whole tile lies above the diagonal
+    const int ra = i0 - i_lo, rb = min(i0 + 1, i_hi - 1) - i_lo, rc = min(i0 + 2, i_hi - 1) - i_lo;
     const int jj = min(j, NS - 1);
     double s0 = 0.0, s1 = 0.0, s2 = 0.0;
 #pragma unroll 4
     for (int k = 0; k < NS; ++k) {
-      const double* row = smx + (size_t)k * ld;
-      const double xj = row[jj];
-      s0 = fma(row[ia], xj, s0);
-      s1 = fma(row[ib], xj, s1);
-      s2 = fma(row[ic], xj, s2);
+      const double xj = smx[(size_t)k * ld + jj];
+      const double* pr = prow + (size_t)k * pld;
+      s0 = fma(pr[ra], xj, s0);
+      s1 = fma(pr[rb], xj, s1);
+      s2 = fma(pr[rc], xj, s2);
     }
     if (j < NS) {
-      if (j <= ia) Ug[(size_t)ia * NS + j] = s0;
-      if (i0 + 1 < i_hi && j <= ib) Ug[(size_t)ib * NS + j] = s1;
-      if (i0 + 2 < i_hi && j <= ic) Ug[(size_t)ic * NS + j] = s2;
+      const int ia = i0, ib = i0 + 1, ic = i0 + 2;
+      if (full) {
+        Og[(size_t)ia * NS + j] = -s0;
+        if (ib < i_hi) Og[(size_t)ib * NS + j] = -s1;
+        if (ic < i_hi) Og[(size_t)ic * NS + j] = -s2;
+      } else {
+        if (j <= ia) Og[(size_t)ia * NS + j] += s0;
+        if (ib < i_hi && j <= ib) Og[(size_t)ib * NS + j] += s1;
+        if (ic < i_hi && j <= ic) Og[(size_t)ic * NS + j] += s2;
+      }
     }
   }
 }
 
-// the middle separator: dense solve; decides whether the whole step is kept.  one CTA
+// the last separator of the cyclic reduction (sp.mid): dense solve; decides whether the whole step is kept.  one CTA
 __global__ void __launch_bounds__(kSpikeThreads)
 k_red_mid(int Pphys, int B, float lm, float ep, BandPlan plan, SpikePlan sp, Ws ws) {
   extern __shared__ double smm[];
@@ -492,78 +530,81 @@ k_red_mid(int Pphys, int B, float lm, float ep, BandPlan plan, SpikePlan sp, Ws 
   }
 }
 
-// back-substitution of the separator chain, outwards from the middle: x_s = L_s^-T (y_s - X_s^T x_t).  grid 2
+// back-substitution of one level of the cyclic reduction: x_s = L_s^-T (y_s - Xa^T x_a - Xb^T x_b) for every
+// separator eliminated at that level (its neighbours are solved already).  grid: eliminated separators, one CTA each
 __global__ void __launch_bounds__(kSpikeThreads)
-k_red_back(int B, BandPlan plan, SpikePlan sp, Ws ws) {
+k_cr_back(int B, int level, BandPlan plan, SpikePlan sp, Ws ws) {
   extern __shared__ double smk2[];
-  const int side = blockIdx.x;
   const int tid = threadIdx.x, nt = blockDim.x;
   const int NS = 6 * B, ld = spike_ld(NS);
   const int* flags = reinterpret_cast<const int*>(ws.Lfac + plan.flags);
   const bool ok = flags[sp.D + 1] == 0;
+  int s, na, nb;
+  cr_step(sp, level, blockIdx.x, s, na, nb);
   double* L = smk2;                                  // NS x ld
   double* x = L + (size_t)NS * ld;
   double* dinv = x + NS;
-  double* xt = dinv + NS;
-  const int first = side == 0 ? sp.mid - 1 : sp.mid + 1, step = side == 0 ? -1 : 1;
-  for (int s = first; s >= 1 && s <= sp.D - 1; s += step) {
-    const int t = s - step;                           // the neighbour towards the middle, already solved
-    double* xs_g = ws.Lfac + sp.xsep + (size_t)s * NS;
-    if (!ok) {
-      for (int i = tid; i < NS; i += nt) {
-        xs_g[i] = 0.0;
-        ws.dx[6 * sp.m[s] + i] = 0.0f;
-      }
-      continue;
-    }
-    const double* Lf = ws.Lfac + sp.Lf[s];
-    const double* Xg = ws.Lfac + sp.X[s];
-    const double* xt_g = ws.Lfac + sp.xsep + (size_t)t * NS;
-    __syncthreads();
-    // 117 KB through one CTA: eight 16-byte loads in flight per thread (the offsets of Lf are even, ld is odd: the
-    // factor is copied as a flat array)
-    {
-      const int n2 = (NS * ld) >> 1;
-      const double2* src = reinterpret_cast<const double2*>(Lf);
-      for (int q0 = tid; q0 < n2; q0 += 8 * nt) {
-        double2 v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          if (q0 + u * nt < n2) v[u] = src[q0 + u * nt];
-#pragma unroll
-        for (int u = 0; u < 8; ++u)
-          if (q0 + u * nt < n2) { L[2 * (q0 + u * nt)] = v[u].x; L[2 * (q0 + u * nt) + 1] = v[u].y; }
-      }
-      if (((NS * ld) & 1) && tid == 0) L[NS * ld - 1] = Lf[NS * ld - 1];
-    }
+  double* xa = dinv + NS;                            // solutions of the two neighbours
+  double* xb = xa + NS;
+  double* xs_g = ws.Lfac + sp.xsep + (size_t)s * NS;
+  if (!ok) {
     for (int i = tid; i < NS; i += nt) {
-      dinv[i] = Lf[(size_t)(NS + 1) * ld + i];
-      xt[i] = xt_g[i];
-      x[i] = Lf[(size_t)NS * ld + i];
+      xs_g[i] = 0.0;
+      ws.dx[6 * sp.m[s] + i] = 0.0f;
     }
-    __syncthreads();
-    {
-      // z = y - X^T x_t: thread (k, part) sums a slice of the rows, partial sums meet in shared memory
-      const int parts = max(1, nt / NS), k = tid % NS, part = tid / NS;
-      double sum = 0.0;
-      if (part < parts) {
-        const int per = (NS + parts - 1) / parts;
-        const int a0 = part * per, a1 = min(NS, a0 + per);
+    return;
+  }
+  const double* Lf = ws.Lfac + sp.Lf[s];
+  // 117 KB through one CTA: eight 16-byte loads in flight per thread (the offsets of Lf are even, ld is odd: the
+  // factor is copied as a flat array)
+  {
+    const int n2 = (NS * ld) >> 1;
+    const double2* src = reinterpret_cast<const double2*>(Lf);
+    for (int q0 = tid; q0 < n2; q0 += 8 * nt) {
+      double2 v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (q0 + u * nt < n2) v[u] = src[q0 + u * nt];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (q0 + u * nt < n2) { L[2 * (q0 + u * nt)] = v[u].x; L[2 * (q0 + u * nt) + 1] = v[u].y; }
+    }
+    if (((NS * ld) & 1) && tid == 0) L[NS * ld - 1] = Lf[NS * ld - 1];
+  }
+  for (int i = tid; i < NS; i += nt) {
+    dinv[i] = Lf[(size_t)(NS + 1) * ld + i];
+    x[i] = Lf[(size_t)NS * ld + i];
+    xa[i] = na ? (ws.Lfac + sp.xsep + (size_t)na * NS)[i] : 0.0;
+    xb[i] = nb ? (ws.Lfac + sp.xsep + (size_t)nb * NS)[i] : 0.0;
+  }
+  __syncthreads();
+  {
+    // z = y - Xa^T x_a - Xb^T x_b: thread (k, part) sums a slice of the rows, partial sums meet in shared memory
+    const double* Xa = ws.Lfac + sp.X[s][0];
+    const double* Xb = ws.Lfac + sp.X[s][1];
+    const int parts = max(1, nt / NS), k = tid % NS, part = tid / NS;
+    double sum = 0.0;
+    if (part < parts) {
+      const int per = (NS + parts - 1) / parts;
+      const int a0 = part * per, a1 = min(NS, a0 + per);
+      if (na) {
 #pragma unroll 8
-        for (int i = a0; i < a1; ++i) sum = fma(Xg[(size_t)i * NS + k], xt[i], sum);
+        for (int i = a0; i < a1; ++i) sum = fma(Xa[(size_t)i * NS + k], xa[i], sum);
       }
-      for (int q = 0; q < parts; ++q) {
-        if (part == q) x[k] -= sum;
-        __syncthreads();
+      if (nb) {
+#pragma unroll 8
+        for (int i = a0; i < a1; ++i) sum = fma(Xb[(size_t)i * NS + k], xb[i], sum);
       }
     }
-    cholesky6_back(L, ld, B, x, dinv);
-    for (int i = tid; i < NS; i += nt) {
-      xs_g[i] = x[i];
-      ws.dx[6 * sp.m[s] + i] = (float)x[i];
+    for (int q = 0; q < parts; ++q) {
+      if (part == q) x[k] -= sum;
+      __syncthreads();
     }
-    __syncthreads();                                  // xs_g is read as x_t by the next separator of this side
-    __threadfence_block();
+  }
+  cholesky6_back(L, ld, B, x, dinv);
+  for (int i = tid; i < NS; i += nt) {
+    xs_g[i] = x[i];
+    ws.dx[6 * sp.m[s] + i] = (float)x[i];
   }
 }
 
