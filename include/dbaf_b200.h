@@ -284,8 +284,8 @@ int dbaf_ba_solve(void* workspace, int t0, int t1, float lm, float ep,
  * Windows up to 6P = 160 ignore the hint and use the dense shared-memory solver; beyond that a band of
  * 1..25 blocks selects the sliding-window factorisation, anything else the slow dense fallback.
  * Chains of 64 or more poses are factorised from both ends at once (two thread blocks meeting at a separator);
- * long chains with a band of at most 20 blocks are cut into up to 16 domains that are swept concurrently, with a
- * block-tridiagonal system over the separators solved afterwards (csrc/ba_spike.cuh).
+ * long chains with a band of at most 20 blocks are cut into up to 16 domains that are swept concurrently, with the
+ * block-tridiagonal system over the separators solved afterwards by block cyclic reduction (csrc/ba_spike.cuh).
  * The workspace must have gone through dbaf_ba_prepare (it zeroes the failure counter info[1]).
  * Replaces Eigen::SimplicialLLT on the host (src/droid_kernels.cu:1248-1269). */
 int dbaf_ba_solve_banded(void* workspace, int t0, int t1, float lm, float ep, int band_blocks, void* stream);
