@@ -350,6 +350,57 @@ def damped_solve(A, b, lm, ep):
     return x.astype(np.float32), True
 
 
+def block_tridiagonal_cyclic_reduction(D, C, y):
+    """Solves the symmetric positive definite block-tridiagonal system with diagonal blocks D[1..m], couplings
+    C[a] = A(a+1, a) (rows: unknowns of a+1) and right-hand sides y[1..m] by block cyclic reduction, in the order the
+    domain-decomposed banded solve works (csrc/ba_spike.cuh): at level l (h = 2^l) every s with s mod 2h == h is
+    eliminated -- L_s = chol(D_s), Xa = A(s-h, s) L_s^-T, Xb = A(s+h, s) L_s^-T, D_{s-h} -= Xa Xa^T,
+    D_{s+h} -= Xb Xb^T, A(s+h, s-h) = -Xb Xa^T, same for y -- until one block is left, then back through the levels.
+    No counterpart in the reference (it hands the whole reduced camera system to Eigen::SimplicialLLT,
+    src/droid_kernels.cu:1248-1269); pinned against a dense solve in tests/test_oracle_cpu.py.
+    D, C, y: dicts keyed 1..m / 1..m-1 / 1..m of float64 arrays.  Returns {s: x_s} and the number of factor levels."""
+    m = len(D)
+    D = {s: np.array(D[s], np.float64) for s in D}
+    y = {s: np.array(y[s], np.float64) for s in y}
+    coup = {(0, a): np.array(C[a], np.float64) for a in C}
+    L, z, Xa, Xb = {}, {}, {}, {}
+    h, lev = 1, 0
+    while True:
+        active = [s for s in range(1, m + 1) if s % h == 0]
+        if len(active) == 1:
+            last = active[0]
+            L[last] = np.linalg.cholesky(D[last])
+            z[last] = np.linalg.solve(L[last], y[last])
+            break
+        for s in [s for s in range(1, m + 1) if s % (2 * h) == h]:
+            L[s] = np.linalg.cholesky(D[s])
+            z[s] = np.linalg.solve(L[s], y[s])
+            a, b = s - h, s + h
+            if a >= 1:
+                Xa[s] = np.linalg.solve(L[s], coup[(lev, a)]).T          # A(a,s) = A(s,a)^T
+                D[a] -= Xa[s] @ Xa[s].T
+                y[a] -= Xa[s] @ z[s]
+            if b <= m:
+                Xb[s] = np.linalg.solve(L[s], coup[(lev, s)].T).T
+                D[b] -= Xb[s] @ Xb[s].T
+                y[b] -= Xb[s] @ z[s]
+            if a >= 1 and b <= m:
+                coup[(lev + 1, a)] = -Xb[s] @ Xa[s].T
+        h, lev = 2 * h, lev + 1
+    x = {last: np.linalg.solve(L[last].T, z[last])}
+    levels = lev + 1
+    while lev > 0:
+        lev, h = lev - 1, h // 2
+        for s in [s for s in range(1, m + 1) if s % (2 * h) == h]:
+            r = z[s].copy()
+            if s - h >= 1:
+                r -= Xa[s].T @ x[s - h]
+            if s + h <= m:
+                r -= Xb[s].T @ x[s + h]
+            x[s] = np.linalg.solve(L[s].T, r)
+    return x, levels
+
+
 def back_substitute(E, Q, w, dx, tab, t0, t1, dtype):
     """EvT6x1_kernel + dz.  src/droid_kernels.cu:1140-1160, 1486-1495.
     Rows whose pose index is <= 0 or >= P contribute nothing (:1150)."""

@@ -374,3 +374,40 @@ def test_ba2gtsam_matrix_is_the_row_swapped_negative_adjoint(db):
         for _ in range(3):
             xi = rng.normal(size=6)
             assert np.allclose(Ti @ hat(xi) @ T, hat(A0 @ xi), atol=1e-12)
+
+
+@pytest.mark.parametrize("m,levels", [(1, 1), (2, 2), (3, 2), (5, 3), (7, 3), (9, 4), (12, 4), (15, 4)])
+def test_block_cyclic_reduction_matches_dense_solve(oracle, m, levels):
+    """The elimination order of the domain-decomposed banded solve's separator system (csrc/ba_spike.cuh) restated
+    in numpy: same solution as a dense solve, log2 depth."""
+    rng = np.random.default_rng(m)
+    ns = 6
+    n = m * ns
+    M = rng.normal(size=(n, n))
+    A = M @ M.T
+    for i in range(m):
+        for j in range(m):
+            if abs(i - j) > 1:
+                A[i * ns:(i + 1) * ns, j * ns:(j + 1) * ns] = 0.0
+    A += 2 * n * np.eye(n)
+    b = rng.normal(size=n)
+    D = {s: A[(s - 1) * ns:s * ns, (s - 1) * ns:s * ns] for s in range(1, m + 1)}
+    C = {a: A[a * ns:(a + 1) * ns, (a - 1) * ns:a * ns] for a in range(1, m)}
+    y = {s: b[(s - 1) * ns:s * ns] for s in range(1, m + 1)}
+    x, lev = oracle.block_tridiagonal_cyclic_reduction(D, C, y)
+    got = np.concatenate([x[s] for s in range(1, m + 1)])
+    want = np.linalg.solve(A, b)
+    assert np.abs(got - want).max() <= 1e-12 * np.abs(want).max()
+    assert lev == levels
+
+
+def test_banded_solve_plan_host_side(db):
+    """Host-side plan of dbaf_ba_solve_banded (no device work): launch counts per path, strip size of the band."""
+    assert db.banded_solve_launches(11, 0) == 1                     # dense shared-memory solve
+    assert db.banded_solve_launches(40, 20) == 1                    # one sweep: chain too short to cut
+    assert db.banded_solve_launches(100, 20) == 3                   # two sweeps, separator, back-substitutions
+    # 16 domains, 15 separators: sweeps, spike + Gram, 3 x (eliminate, update), last block, 3 x back, apply, back
+    assert db.banded_solve_launches(999, 20) == 1 + 2 + 6 + 1 + 3 + 1 + 1
+    from droid_backends import _lib
+    assert _lib.lib.dbaf_ba_band_strip_doubles(999, 20) == 5994 * 6 * 41 + 5994
+    assert _lib.lib.dbaf_ba_layout_bytes() == _lib.ctypes.sizeof(_lib.BaLayout)
