@@ -4,8 +4,9 @@ Everything upstream of the pose solve is a sum over edges grouped by their SOURC
 (SURVEY.md 8e): the Jacobian kernel reads only the source frame's disparity, and C_k, w_k and every
 Schur term of depth frame k come from the edges leaving k.  So each rank owns a contiguous range of
 depth frames together with all their out-edges, linearises them into its own copy of the reduced
-camera system, and ONE all-reduce (sum, float64, in place on the contiguous H|v span of the
-workspace) gives every rank the identical full system.  The solve is replicated (bit-identical dx on
+camera system, and ONE all-reduce (sum, float64; of the band of H and v packed into one dense strip
+when the frame graph is banded, else in place on the contiguous H|v span of the workspace) gives every
+rank the identical full system.  The solve is replicated (bit-identical dx on
 every rank, no broadcast), poses are updated everywhere, disparities only by their owner -- no
 per-pixel data ever crosses GPUs.
 
