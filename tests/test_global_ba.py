@@ -450,8 +450,8 @@ def test_banded_solvers_on_random_band_systems(dev, db, oracle, synth, P, B):
 @pytest.mark.parametrize("P,B,D", [(128, 20, 3), (203, 13, 5), (300, 5, 12), (400, 20, 8), (999, 20, 8), (999, 20, 16),
                                    (999, 20, 0), (96, 1, 16), (64, 3, 7), (250, 10, 4), (130, 6, 3)])
 def test_domain_decomposed_banded_solve(dev, db, oracle, synth, P, B, D):
-    """The banded solve cut into D domains (ba_spike.cuh: D sweeps, spikes of the middle domains, two-sided
-    elimination of the separator chain): dx against numpy's dense float64 solve on random block-banded SPD systems,
+    """The banded solve cut into D domains (ba_spike.cuh: D sweeps, spikes of the middle domains, block cyclic
+    reduction over the separators): dx against numpy's dense float64 solve on random block-banded SPD systems,
     at the size and band of the global-BA workload (P = 999, B = 20) among others; D = 0 is the automatic choice.
     A non-positive pivot anywhere (interior, separator) drops the whole step."""
     rng = np.random.default_rng(1000 * P + 10 * B + D)
