@@ -68,6 +68,48 @@ def build(force: bool = False) -> str | None:
     return so
 
 
+def build_lietorch(force: bool = False) -> str | None:
+    """The reference's lietorch extension (thirdparty/lietorch, unmodified, compiled where it lies) into
+    oracle/_ref/lietorch_backends.so: what the reference's pure-PyTorch CPU path (dbaf/geom/ba.py) needs.  Used by
+    scripts/time_geom_ba_cpu.py in the dev container only -- the Python half of that path lives under /root/reference
+    and does not exist on the GPU box.  ~5 minutes (nvcc on lietorch_gpu.cu; the CPU path links against it)."""
+    so = os.path.join(OUT, "lietorch_backends.so")
+    if os.path.exists(so) and not force:
+        return so
+    lt = os.path.join(REF, "thirdparty", "lietorch")
+    if not os.path.isdir(lt):
+        return None
+    import torch
+    T = os.path.dirname(torch.__file__)
+    os.makedirs(os.path.join(OUT, "obj"), exist_ok=True)
+    inc = [f"-I{T}/include", f"-I{T}/include/torch/csrc/api/include", f"-I{sysconfig.get_paths()['include']}",
+           f"-I{lt}/lietorch/include", f"-I{lt}/eigen", "-I/usr/local/cuda/include",
+           "-DTORCH_EXTENSION_NAME=lietorch_backends", "-DTORCH_API_INCLUDE_EXTENSION_H",
+           "-include", os.path.join(HERE, "ref_shim.h")]
+    nvcc = ["/usr/local/cuda/bin/nvcc", "-O2", "-std=c++17", "-Xcompiler", "-fPIC", "-w",
+            "-gencode=arch=compute_100a,code=sm_100a", "--expt-relaxed-constexpr"]
+    cxx = ["g++", "-O2", "-std=c++17", "-fPIC", "-w"]
+    jobs = []
+    for src, tool in (("lietorch_gpu.cu", nvcc), ("lietorch_cpu.cpp", cxx), ("lietorch.cpp", cxx)):
+        obj = os.path.join(OUT, "obj", src + ".o")
+        jobs.append((tool + inc + ["-c", os.path.join(lt, "lietorch", "src", src), "-o", obj], obj))
+
+    def run(job):
+        r = subprocess.run(job[0], capture_output=True, text=True)
+        if r.returncode != 0:
+            raise RuntimeError("lietorch build failed:\n" + " ".join(job[0]) + "\n" + r.stderr[-4000:])
+
+    with ThreadPoolExecutor(3) as ex:
+        list(ex.map(run, jobs))
+    link = ["g++", "-shared", "-o", so] + [o for _, o in jobs] + [
+        f"-L{T}/lib", "-L/usr/local/cuda/lib64", "-lc10", "-ltorch", "-ltorch_cpu", "-ltorch_python",
+        "-lc10_cuda", "-ltorch_cuda", "-lcudart", f"-Wl,-rpath,{T}/lib"]
+    r = subprocess.run(link, capture_output=True, text=True)
+    if r.returncode != 0:
+        raise RuntimeError("lietorch link failed:\n" + r.stderr[-4000:])
+    return so
+
+
 def load():
     """Imports oracle/_ref/droid_backends_ref.so (None if it was never built)."""
     so = os.path.join(OUT, NAME + ".so")
